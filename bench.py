@@ -1,0 +1,184 @@
+#!/usr/bin/env python
+"""Headline benchmark: frames/sec of MobileNet-SSD 300x300 video inference, batch 64 per GPU.
+
+    python bench.py --gpus N --steps K --warmup W            # this framework (sm_100a kernels)
+    python bench.py --impl reference --gpus N ...            # unmodified reference (cv2.dnn + TCP)
+    python bench.py --impl torch ...                         # baseline (b): torch cuDNN (+NCCL) model
+
+One step = one batch of 64 synthetic 300x300 BGR frames per GPU through the whole worker
+path of the reference (worker.py:243-280): resize to 400 wide -> 300x300 -> normalise ->
+MobileNet-SSD -> softmax/decode/NMS -> person filter -> box/text overlay.  Random-init weights
+of the exact architecture (the caffemodel blob is absent from the reference mount).
+
+Prints ONE JSON line on rank 0 (see README/DESIGN for the field contract).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "frames/sec MobileNet-SSD 300x300"
+BATCH_PER_GPU = 64
+POOL = 8   # distinct input batches rotated through: 8 * 64 * 270 KB = 138 MB > 126 MB of L2
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="native", choices=["native", "reference", "torch"])
+    ap.add_argument("--batch", type=int, default=BATCH_PER_GPU)
+    ap.add_argument("--frame-h", type=int, default=300)
+    ap.add_argument("--frame-w", type=int, default=300)
+    ap.add_argument("--sub-batch", type=int, default=0)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--ingest", default="scatter", choices=["scatter", "local"])
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def synth_frames(n, h, w, seed):
+    """Synthetic video frames: smooth random content (more realistic for the resizers than white noise)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    small = rng.integers(0, 256, (n, h // 8 + 1, w // 8 + 1, 3), dtype=np.uint8)
+    out = np.repeat(np.repeat(small, 8, axis=1), 8, axis=2)[:, :h, :w]
+    noise = rng.integers(0, 32, (n, h, w, 3), dtype=np.uint8)
+    return (out // 2 + noise + 48).astype(np.uint8)
+
+
+def run_native(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from distributedvolunteercomputing_b200.config import Config
+    from distributedvolunteercomputing_b200.engine import NativeEngine
+    from distributedvolunteercomputing_b200.models.mobilenet_ssd import SSDGraph
+    from distributedvolunteercomputing_b200.ops import lib
+    from distributedvolunteercomputing_b200.utils.clocks import ClockSampler
+
+    rank, world, local = dist_env()
+    assert world == args.gpus or world == 1, f"WORLD_SIZE={world} but --gpus {args.gpus}"
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    multi = world > 1
+    if multi:
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    B, H, W = args.batch, args.frame_h, args.frame_w
+    cfg = Config(batch=B, sub_batch=args.sub_batch, use_cuda_graph=not args.no_graph)
+    graph = SSDGraph.random(seed=1, conf_gain=2.5)
+    eng = NativeEngine(graph, dev, cfg, requester_id="127.0.0.1:5554")
+    st = eng.state(B, H, W)
+
+    # ---- inputs: POOL distinct batches per rank, on the device (kernel timing) and pinned on the host (e2e)
+    host_pool = torch.from_numpy(synth_frames(POOL * B, H, W, seed=100 + rank)).view(POOL, B, H, W, 3).pin_memory()
+    dev_pool = host_pool.to(dev)
+    host_det = torch.empty((B, 100, 7), dtype=torch.float32).pin_memory()
+    host_cnt = torch.empty((B,), dtype=torch.int32).pin_memory()
+
+    def barrier():
+        if multi:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-timed region
+    for i in range(args.warmup):
+        eng.run(st, src=dev_pool[i % POOL])
+    barrier()
+    sampler = ClockSampler(local).start() if rank == 0 else None
+    l0 = lib.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(args.steps):
+        eng.run(st, src=dev_pool[i % POOL])
+    ev1.record()
+    barrier()
+    dev_ms = ev0.elapsed_time(ev1)
+    launches_eager = lib.launch_count() - l0
+    det_sum = int(st.det_count.sum().item())
+
+    # ---- end-to-end region through the public API: pinned host frames in, detections out, every step
+    for i in range(min(3, args.warmup)):
+        eng.process(host_pool[i % POOL])
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        r = eng.process(host_pool[i % POOL])
+        host_det.copy_(r.det, non_blocking=True)
+        host_cnt.copy_(r.det_count, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if multi:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    frames_total = world * B * args.steps
+    value = frames_total / (dev_ms / 1e3)
+    e2e = frames_total / (e2e_ms / 1e3)
+    per_step_launches = eng.launches_per_batch(st)
+    out = {
+        "metric": METRIC, "value": round(value, 1), "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "fp16", "data": "synthetic", "impl": "native",
+        "config": {"model": "MobileNet-SSD 300x300 (random-init caffemodel architecture, 5.78M params)",
+                   "global_batch": world * B, "seq_len": None, "frame_hw": [H, W], "parallelism": f"dp{world}",
+                   "l2_policy": f"inputs rotate over {POOL} distinct batches ({POOL * B * H * W * 3 / 1e6:.0f} MB > 126 MB L2)",
+                   "cuda_graph": not args.no_graph, "sub_batch": cfg.sub_batch or 16,
+                   "p50_frame_latency_ms": round(dev_ms / args.steps, 4)},
+        "e2e": {"value": round(e2e, 1), "unit": "frames/s", "h2d_bytes_per_step": int(B * H * W * 3),
+                "d2h_bytes_per_step": int(B * 100 * 7 * 4 + B * 4), "ms_per_step": round(e2e_ms / args.steps, 4)},
+        "gpu_launches": int(per_step_launches * args.steps),
+        "gpu_launches_counted_by_library": int(launches_eager),
+        "clocks": clocks, "detections_last_batch": det_sum,
+    }
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if multi:
+        dist.destroy_process_group()
+
+
+def run_torch(args):
+    from baseline.torch_nccl.run import run as run_torch_baseline
+    run_torch_baseline(args, METRIC)
+
+
+def run_reference(args):
+    try:
+        from baseline.ref_harness.run_ref import run as run_ref
+    except Exception as e:  # harness missing
+        print(json.dumps({"impl": "reference", "unavailable": f"reference harness not importable: {e}"}))
+        return
+    run_ref(args, METRIC)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    elif args.impl == "torch":
+        run_torch(args)
+    else:
+        run_native(args)
+
+
+if __name__ == "__main__":
+    main()

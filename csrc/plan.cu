@@ -1,0 +1,167 @@
+// Native plan executor: the whole MobileNet-SSD forward pass as one pre-planned launch
+// sequence (TMA descriptors encoded once, launch geometry frozen), replayed on a stream.
+// This replaces cv2.dnn's net.forward() graph walk (reference worker.py:248-249).
+#include <vector>
+
+#include "common.cuh"
+
+namespace dvc {
+
+// launch descriptors defined in the kernel translation units
+struct GemmArgs;
+struct GemmLaunch;
+struct PreprocLaunch;
+struct DetLaunch;
+
+int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda, int out_mode,
+                 void* out, int ldc, int relu, const dvc_head_out* head, int block_n);
+int gemm_launch(const GemmLaunch* L, cudaStream_t st);
+GemmLaunch* gemm_alloc();
+void gemm_free(GemmLaunch*);
+
+int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B, int sh,
+                    int sw, const int* xs, const int* xq, const int* ys, const int* yq, const float* w0, const float* b0,
+                    const float* h_mean3, float scale, void* out, int band_rows_max);
+int preproc_launch(const PreprocLaunch* L, cudaStream_t st);
+PreprocLaunch* preproc_alloc();
+void preproc_free(PreprocLaunch*);
+void preproc_set_source(PreprocLaunch*, const uint8_t* src, long long stride, const int* frame_index);
+
+int det_prepare(DetLaunch* L, const float* loc, const float* conf, const float* priors, const float* variances, int B,
+                const dvc_det_params* p, const int* slot_index, float* det, int* det_count, int* boxes_i, int* box_count,
+                uint32_t* flags, uint32_t flag_value, void* scratch, size_t scratch_bytes);
+int det_launch(const DetLaunch* L, cudaStream_t st);
+DetLaunch* det_alloc();
+void det_free(DetLaunch*);
+void det_set_flag_value(DetLaunch*, uint32_t);
+void det_set_sinks(DetLaunch*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index);
+
+int dwconv_launch(const void* in, int B, int H, int W, int C, int stride, const float* w, const float* b, int relu, void* out,
+                  cudaStream_t st);
+int im2col_launch(const void* in, int B, int H, int W, int C, void* out, cudaStream_t st);
+
+enum OpKind { OP_PREPROC, OP_DW, OP_GEMM, OP_IM2COL, OP_DET };
+
+struct Op {
+  OpKind kind;
+  GemmLaunch* gemm = nullptr;
+  PreprocLaunch* pre = nullptr;
+  DetLaunch* det = nullptr;
+  // dw / im2col
+  const void* in = nullptr; void* out = nullptr; const float* w = nullptr; const float* b = nullptr;
+  int B = 0, H = 0, W = 0, C = 0, stride = 1, relu = 0;
+};
+
+}  // namespace dvc
+
+struct dvc_plan {
+  std::vector<dvc::Op> ops;
+};
+
+using namespace dvc;
+
+extern "C" dvc_plan* dvc_plan_create(void) { return new dvc_plan(); }
+
+extern "C" void dvc_plan_destroy(dvc_plan* p) {
+  if (!p) return;
+  for (auto& op : p->ops) {
+    if (op.gemm) gemm_free(op.gemm);
+    if (op.pre) preproc_free(op.pre);
+    if (op.det) det_free(op.det);
+  }
+  delete p;
+}
+
+extern "C" int dvc_plan_num_ops(const dvc_plan* p) { return p ? (int)p->ops.size() : 0; }
+
+extern "C" int dvc_plan_add_preproc_conv0(dvc_plan* p, const uint8_t* src400, long long src_frame_stride, const int* frame_index,
+                                          int B, int sh, int sw, const int* xs, const int* xq, const int* ys, const int* yq,
+                                          const float* w0, const float* b0, const float* h_mean3, float scale, void* out_f16) {
+  DVC_REQUIRE(p, "plan is null");
+  Op op; op.kind = OP_PREPROC; op.pre = preproc_alloc();
+  int rc = preproc_prepare(op.pre, src400, src_frame_stride, frame_index, B, sh, sw, xs, xq, ys, yq, w0, b0, h_mean3, scale, out_f16, 0);
+  if (rc) { preproc_free(op.pre); return rc; }
+  p->ops.push_back(op);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_add_dwconv(dvc_plan* p, const void* in_f16, int B, int H, int W, int C, int stride, const float* w,
+                                   const float* b, int relu, void* out_f16) {
+  DVC_REQUIRE(p, "plan is null");
+  DVC_REQUIRE(C % 8 == 0 && (stride == 1 || stride == 2), "dwconv: C=%d stride=%d unsupported", C, stride);
+  Op op; op.kind = OP_DW; op.in = in_f16; op.out = out_f16; op.w = w; op.b = b;
+  op.B = B; op.H = H; op.W = W; op.C = C; op.stride = stride; op.relu = relu;
+  p->ops.push_back(op);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_add_gemm(dvc_plan* p, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
+                                 int out_mode, void* out_f16, int ldc, int relu, const dvc_head_out* head, int block_n) {
+  DVC_REQUIRE(p, "plan is null");
+  Op op; op.kind = OP_GEMM; op.gemm = gemm_alloc();
+  int rc = gemm_prepare(op.gemm, A, Wt, bias, M, N, K, lda, out_mode, out_f16, ldc, relu, head, block_n);
+  if (rc) { gemm_free(op.gemm); return rc; }
+  p->ops.push_back(op);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_add_im2col(dvc_plan* p, const void* in_f16, int B, int H, int W, int C, void* out_f16) {
+  DVC_REQUIRE(p, "plan is null");
+  DVC_REQUIRE(C % 8 == 0, "im2col: C=%d unsupported", C);
+  Op op; op.kind = OP_IM2COL; op.in = in_f16; op.out = out_f16; op.B = B; op.H = H; op.W = W; op.C = C;
+  p->ops.push_back(op);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_add_detection(dvc_plan* p, const float* loc, const float* conf, const float* priors,
+                                      const float* variances, int B, const dvc_det_params* prm, const int* slot_index, float* det,
+                                      int* det_count, int* boxes_i, int* box_count, uint32_t* flags, uint32_t flag_value,
+                                      void* scratch, size_t scratch_bytes) {
+  DVC_REQUIRE(p, "plan is null");
+  Op op; op.kind = OP_DET; op.det = det_alloc();
+  int rc = det_prepare(op.det, loc, conf, priors, variances, B, prm, slot_index, det, det_count, boxes_i, box_count, flags,
+                       flag_value, scratch, scratch_bytes);
+  if (rc) { det_free(op.det); return rc; }
+  p->ops.push_back(op);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_set_source(dvc_plan* p, const uint8_t* src400, long long src_frame_stride, const int* frame_index) {
+  DVC_REQUIRE(p, "plan is null");
+  DVC_REQUIRE(src_frame_stride % 16 == 0 && (reinterpret_cast<uintptr_t>(src400) & 15) == 0, "set_source: unaligned frames");
+  for (auto& op : p->ops)
+    if (op.kind == OP_PREPROC) preproc_set_source(op.pre, src400, src_frame_stride, frame_index);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_set_sinks(dvc_plan* p, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags,
+                                  const int* slot_index) {
+  DVC_REQUIRE(p, "plan is null");
+  for (auto& op : p->ops)
+    if (op.kind == OP_DET) det_set_sinks(op.det, det, det_count, boxes_i, box_count, flags, slot_index);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_set_flag_value(dvc_plan* p, uint32_t flag_value) {
+  DVC_REQUIRE(p, "plan is null");
+  for (auto& op : p->ops)
+    if (op.kind == OP_DET) det_set_flag_value(op.det, flag_value);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_run(dvc_plan* p, void* stream) {
+  DVC_REQUIRE(p, "plan is null");
+  cudaStream_t st = (cudaStream_t)stream;
+  for (const auto& op : p->ops) {
+    int rc = DVC_OK;
+    switch (op.kind) {
+      case OP_PREPROC: rc = preproc_launch(op.pre, st); break;
+      case OP_DW: rc = dwconv_launch(op.in, op.B, op.H, op.W, op.C, op.stride, op.w, op.b, op.relu, op.out, st); break;
+      case OP_GEMM: rc = gemm_launch(op.gemm, st); break;
+      case OP_IM2COL: rc = im2col_launch(op.in, op.B, op.H, op.W, op.C, op.out, st); break;
+      case OP_DET: rc = det_launch(op.det, st); break;
+    }
+    if (rc) return rc;
+  }
+  return DVC_OK;
+}

@@ -1,0 +1,309 @@
+// K1a: u8 resize (imutils.resize(width=400), worker.py:243) and
+// K1b: fused frame fetch + 300x300 bilinear resize + normalise + conv0 (worker.py:245-246,
+//      prototxt:9-41).
+//
+// K1b is the receiving half of the frame scatter: `src400` may point into the ingest GPU's
+// memory (peer-mapped over NVLink).  Each CTA owns a band of 8 conv0 output rows of one
+// frame; it pulls exactly the source rows that band needs with coalesced 16-byte loads
+// (the only bytes that cross the link: ~1.06x the frame), resamples them in shared memory
+// with cv2's Q11 fixed-point bilinear arithmetic, applies (x - mean_c) * scale, and runs the
+// 3x3/s2 convolution + bias + ReLU from shared memory, writing NHWC fp16.
+#include "common.cuh"
+
+namespace dvc {
+
+// ------------------------------------------------------------------------------- K1a
+struct ResizeArgs {
+  const uint8_t* src; long long src_stride; int B, sh, sw;
+  uint8_t* dst; long long dst_stride; int dh, dw; int mode;
+  const int *xs, *xc; const float* xa; int x_taps;
+  const int *ys, *yc; const float* ya; int y_taps;
+  const int *xq, *yq; int ix, iy;
+};
+
+__global__ void __launch_bounds__(256) resize_u8_kernel(const ResizeArgs a) {
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long per = (long long)a.dh * a.dw;
+  if (idx >= per * a.B) return;
+  const int b = (int)(idx / per);
+  const int rem = (int)(idx - (long long)b * per);
+  const int dy = rem / a.dw, dx = rem - dy * a.dw;
+  const uint8_t* s = a.src + (size_t)b * a.src_stride;
+  uint8_t* d = a.dst + (size_t)b * a.dst_stride + ((size_t)dy * a.dw + dx) * 3;
+  if (a.mode == 0) {
+    float o0 = 0.f, o1 = 0.f, o2 = 0.f;
+    const int x0 = a.xs[dx], xn = a.xc[dx], y0 = a.ys[dy], yn = a.yc[dy];
+    for (int ky = 0; ky < yn; ++ky) {
+      const uint8_t* row = s + (size_t)(y0 + ky) * a.sw * 3;
+      float h0 = 0.f, h1 = 0.f, h2 = 0.f;
+      for (int kx = 0; kx < xn; ++kx) {
+        const float al = a.xa[dx * a.x_taps + kx];
+        const uint8_t* p = row + (size_t)(x0 + kx) * 3;
+        // unfused multiply/add on purpose: matches cv2's (and numpy's) float op order bit for bit
+        h0 = __fadd_rn(h0, __fmul_rn((float)p[0], al));
+        h1 = __fadd_rn(h1, __fmul_rn((float)p[1], al));
+        h2 = __fadd_rn(h2, __fmul_rn((float)p[2], al));
+      }
+      const float be = a.ya[dy * a.y_taps + ky];
+      o0 = __fadd_rn(o0, __fmul_rn(h0, be));
+      o1 = __fadd_rn(o1, __fmul_rn(h1, be));
+      o2 = __fadd_rn(o2, __fmul_rn(h2, be));
+    }
+    d[0] = (uint8_t)min(max(__float2int_rn(o0), 0), 255);
+    d[1] = (uint8_t)min(max(__float2int_rn(o1), 0), 255);
+    d[2] = (uint8_t)min(max(__float2int_rn(o2), 0), 255);
+  } else if (a.mode == 1) {
+    int s0 = 0, s1 = 0, s2 = 0;
+    for (int ky = 0; ky < a.iy; ++ky) {
+      const uint8_t* row = s + ((size_t)(dy * a.iy + ky) * a.sw + (size_t)dx * a.ix) * 3;
+      for (int kx = 0; kx < a.ix; ++kx) {
+        s0 += row[kx * 3]; s1 += row[kx * 3 + 1]; s2 += row[kx * 3 + 2];
+      }
+    }
+    if (a.ix == 2 && a.iy == 2) {
+      d[0] = (uint8_t)((s0 + 2) >> 2); d[1] = (uint8_t)((s1 + 2) >> 2); d[2] = (uint8_t)((s2 + 2) >> 2);
+    } else {
+      const float sc = 1.0f / (float)(a.ix * a.iy);
+      d[0] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s0, sc)), 255);
+      d[1] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s1, sc)), 255);
+      d[2] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s2, sc)), 255);
+    }
+  } else {
+    const int sx0 = a.xs[dx], sx1 = min(sx0 + 1, a.sw - 1);
+    const int sy0 = a.ys[dy], sy1 = min(sy0 + 1, a.sh - 1);
+    const int a0 = a.xq[dx * 2], a1 = a.xq[dx * 2 + 1], b0 = a.yq[dy * 2], b1 = a.yq[dy * 2 + 1];
+    const uint8_t* r0 = s + (size_t)sy0 * a.sw * 3;
+    const uint8_t* r1 = s + (size_t)sy1 * a.sw * 3;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
+      const int h1 = r1[sx0 * 3 + c] * a0 + r1[sx1 * 3 + c] * a1;
+      const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+      d[c] = (uint8_t)min(max(v, 0), 255);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------- K1b
+constexpr int PC_BAND = 8;                  // conv0 output rows per CTA
+constexpr int PC_PROWS = 2 * PC_BAND + 1;   // 17 rows of the 300x300 image
+constexpr int PC_NET = 300;
+constexpr int PC_OUT = 150;
+constexpr int PC_PCOLS = PC_NET + 1;        // image columns -1 .. 299
+constexpr int PC_THREADS = 256;
+
+struct PreprocArgs {
+  const uint8_t* src; long long src_stride; const int* frame_index; int B, sh, sw;
+  const int *xs, *xq, *ys, *yq;
+  const float *w0, *b0;
+  float mean0, mean1, mean2, scale;
+  __half* out;
+  int band_bytes;     // smem bytes reserved for the staged source rows
+};
+
+__global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const PreprocArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  float* s_w = reinterpret_cast<float*>(smem);                   // [27][32]
+  float* s_b = s_w + 27 * 32;                                    // [32]
+  float* s_patch = s_b + 32;                                     // [17][301][3]
+  int* s_xs = reinterpret_cast<int*>(s_patch + PC_PROWS * PC_PCOLS * 3);   // [300]
+  int* s_xq = s_xs + PC_NET;                                     // [300][2]
+  uint8_t* s_band = reinterpret_cast<uint8_t*>(s_xq + 2 * PC_NET);
+
+  const int band = blockIdx.x, b = blockIdx.y;
+  const int tid = threadIdx.x;
+  const int oy0 = band * PC_BAND;
+  const int iy_first = max(2 * oy0 - 1, 0);
+  const int iy_last = min(2 * oy0 + 2 * PC_BAND - 1, PC_NET - 1);
+  const int slot = a.frame_index ? a.frame_index[b] : b;
+  const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
+  const int row_bytes = a.sw * 3;
+
+  // ---- stage the source rows this band needs (the NVLink pull when src is a peer pointer)
+  const int r_lo = a.ys[iy_first];
+  const int r_hi = min(a.ys[iy_last] + 1, a.sh - 1);
+  const long long start = (long long)r_lo * row_bytes;
+  const long long end = (long long)(r_hi + 1) * row_bytes;
+  const long long start_al = start & ~15LL;
+  const int skew = (int)(start - start_al);
+  const int nvec = (int)((end - start_al + 15) >> 4);
+  {
+    const uint4* gsrc = reinterpret_cast<const uint4*>(frame + start_al);
+    uint4* sdst = reinterpret_cast<uint4*>(s_band);
+    for (int i = tid; i < nvec; i += PC_THREADS) sdst[i] = ldg_nc_v4(gsrc + i);
+  }
+  for (int i = tid; i < 27 * 32; i += PC_THREADS) s_w[i] = a.w0[i];
+  if (tid < 32) s_b[tid] = a.b0[tid];
+  for (int i = tid; i < PC_NET; i += PC_THREADS) {
+    s_xs[i] = a.xs[i];
+    s_xq[2 * i] = a.xq[2 * i];
+    s_xq[2 * i + 1] = a.xq[2 * i + 1];
+  }
+  __syncthreads();
+
+  // ---- bilinear resample (cv2 Q11 fixed point) + normalise into the conv patch
+  const uint8_t* bandp = s_band + skew;
+  for (int i = tid; i < PC_PROWS * PC_PCOLS; i += PC_THREADS) {
+    const int pr = i / PC_PCOLS, pc = i - pr * PC_PCOLS;
+    const int iy = 2 * oy0 - 1 + pr, ix = pc - 1;
+    float v0 = 0.f, v1 = 0.f, v2 = 0.f;   // zero padding of the normalised blob (pad: 1)
+    if (iy >= 0 && iy < PC_NET && ix >= 0) {
+      const int sy0 = a.ys[iy], sy1 = min(sy0 + 1, a.sh - 1);
+      const int b0 = a.yq[2 * iy], b1 = a.yq[2 * iy + 1];
+      const int sx0 = s_xs[ix], sx1 = min(sx0 + 1, a.sw - 1);
+      const int a0 = s_xq[2 * ix], a1 = s_xq[2 * ix + 1];
+      const uint8_t* r0 = bandp + (size_t)(sy0 - r_lo) * row_bytes;
+      const uint8_t* r1 = bandp + (size_t)(sy1 - r_lo) * row_bytes;
+      int px[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
+        const int h1 = r1[sx0 * 3 + c] * a0 + r1[sx1 * 3 + c] * a1;
+        px[c] = min(max((((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2, 0), 255);
+      }
+      v0 = __fmul_rn(__fsub_rn((float)px[0], a.mean0), a.scale);
+      v1 = __fmul_rn(__fsub_rn((float)px[1], a.mean1), a.scale);
+      v2 = __fmul_rn(__fsub_rn((float)px[2], a.mean2), a.scale);
+    }
+    s_patch[i * 3 + 0] = v0;
+    s_patch[i * 3 + 1] = v1;
+    s_patch[i * 3 + 2] = v2;
+  }
+  __syncthreads();
+
+  // ---- conv0 3x3 stride 2 + bias + ReLU.  Register tile: 4 adjacent output pixels x 16 channels
+  // per work item (64 fp32 accumulators), weights broadcast from shared memory.
+  const int rows_here = min(PC_BAND, PC_OUT - oy0);
+  constexpr int XG = (PC_OUT + 3) / 4;   // 38 pixel groups per output row
+  const int groups = rows_here * XG;
+  const int items = ((groups + 31) / 32) * 64;   // (32 groups) x (2 channel halves), half is warp-uniform
+  for (int it = tid; it < items; it += PC_THREADS) {
+    asm volatile("" ::: "memory");   // keep the weight loads inside the loop (no hoisting into spills)
+    const int half = (it >> 5) & 1;
+    const int g = ((it >> 6) << 5) | (it & 31);
+    if (g >= groups) continue;
+    const int oy = g / XG, ox0 = (g - oy * XG) * 4;
+    float acc[4][16];
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+#pragma unroll
+      for (int j = 0; j < 16; ++j) acc[t][j] = s_b[half * 16 + j];
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      // 9 input pixels x 3 channels feed the 4 outputs of this row of the window
+      const float* prow = s_patch + ((2 * oy + ky) * PC_PCOLS + 2 * ox0) * 3;
+      float in[27];
+#pragma unroll
+      for (int k = 0; k < 27; ++k) in[k] = (2 * ox0 + k / 3 < PC_PCOLS) ? prow[k] : 0.f;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {   // tap = kx*3 + c
+        const float4* wv = reinterpret_cast<const float4*>(s_w + (ky * 9 + tap) * 32 + half * 16);
+        const float4 w0 = wv[0], w1 = wv[1], w2 = wv[2], w3 = wv[3];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const float x = in[6 * t + tap];   // pixel (2t + kx), channel c
+          acc[t][0] = fmaf(x, w0.x, acc[t][0]);   acc[t][1] = fmaf(x, w0.y, acc[t][1]);
+          acc[t][2] = fmaf(x, w0.z, acc[t][2]);   acc[t][3] = fmaf(x, w0.w, acc[t][3]);
+          acc[t][4] = fmaf(x, w1.x, acc[t][4]);   acc[t][5] = fmaf(x, w1.y, acc[t][5]);
+          acc[t][6] = fmaf(x, w1.z, acc[t][6]);   acc[t][7] = fmaf(x, w1.w, acc[t][7]);
+          acc[t][8] = fmaf(x, w2.x, acc[t][8]);   acc[t][9] = fmaf(x, w2.y, acc[t][9]);
+          acc[t][10] = fmaf(x, w2.z, acc[t][10]); acc[t][11] = fmaf(x, w2.w, acc[t][11]);
+          acc[t][12] = fmaf(x, w3.x, acc[t][12]); acc[t][13] = fmaf(x, w3.y, acc[t][13]);
+          acc[t][14] = fmaf(x, w3.z, acc[t][14]); acc[t][15] = fmaf(x, w3.w, acc[t][15]);
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int ox = ox0 + t;
+      if (ox < PC_OUT) {
+        uint4* dst = reinterpret_cast<uint4*>(a.out + (((size_t)b * PC_OUT + (oy0 + oy)) * PC_OUT + ox) * 32 + half * 16);
+        const float* v = acc[t];
+        dst[0] = make_uint4(pack_half2(fmaxf(v[0], 0.f), fmaxf(v[1], 0.f)), pack_half2(fmaxf(v[2], 0.f), fmaxf(v[3], 0.f)),
+                            pack_half2(fmaxf(v[4], 0.f), fmaxf(v[5], 0.f)), pack_half2(fmaxf(v[6], 0.f), fmaxf(v[7], 0.f)));
+        dst[1] = make_uint4(pack_half2(fmaxf(v[8], 0.f), fmaxf(v[9], 0.f)), pack_half2(fmaxf(v[10], 0.f), fmaxf(v[11], 0.f)),
+                            pack_half2(fmaxf(v[12], 0.f), fmaxf(v[13], 0.f)), pack_half2(fmaxf(v[14], 0.f), fmaxf(v[15], 0.f)));
+      }
+    }
+  }
+}
+
+struct PreprocLaunch {
+  PreprocArgs args;
+  dim3 grid;
+  int smem;
+};
+
+int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B,
+                    int sh, int sw, const int* xs, const int* xq, const int* ys, const int* yq, const float* w0,
+                    const float* b0, const float* h_mean3, float scale, void* out, int band_rows_max) {
+  DVC_REQUIRE(B > 0 && sh > 1 && sw > 1, "preproc: bad shape B=%d %dx%d", B, sh, sw);
+  DVC_REQUIRE(src_frame_stride % 16 == 0 && (reinterpret_cast<uintptr_t>(src400) & 15) == 0,
+              "preproc: frames must be 16-byte aligned (stride %lld)", src_frame_stride);
+  DVC_REQUIRE(src_frame_stride >= (((long long)sh * sw * 3 + 15) & ~15LL), "preproc: frame stride %lld too small", src_frame_stride);
+  PreprocArgs& a = L->args;
+  a.src = src400; a.src_stride = src_frame_stride; a.frame_index = frame_index; a.B = B; a.sh = sh; a.sw = sw;
+  a.xs = xs; a.xq = xq; a.ys = ys; a.yq = yq; a.w0 = w0; a.b0 = b0;
+  a.mean0 = h_mean3[0]; a.mean1 = h_mean3[1]; a.mean2 = h_mean3[2]; a.scale = scale;
+  a.out = reinterpret_cast<__half*>(out);
+  // worst-case staged rows for one band: 17 net rows span at most ceil(17*sh/300)+2 source rows
+  if (band_rows_max <= 0) band_rows_max = (PC_PROWS * sh + PC_NET - 1) / PC_NET + 3;
+  if (band_rows_max > sh) band_rows_max = sh;
+  a.band_bytes = ((band_rows_max * sw * 3 + 31) & ~15) + 16;
+  L->smem = (27 * 32 + 32 + PC_PROWS * PC_PCOLS * 3) * 4 + 3 * PC_NET * 4 + a.band_bytes;
+  DVC_REQUIRE(L->smem <= 227 * 1024, "preproc: source band of %d rows x %d px does not fit shared memory", band_rows_max, sw);
+  L->grid = dim3((PC_OUT + PC_BAND - 1) / PC_BAND, B);
+  return DVC_OK;
+}
+
+int preproc_launch(const PreprocLaunch* L, cudaStream_t st) {
+  static bool attr_set[64] = {};
+  int dev = 0;
+  DVC_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev & 63] = true;
+  }
+  preproc_conv0_kernel<<<L->grid, PC_THREADS, L->smem, st>>>(L->args);
+  count_launch();
+  DVC_CHECK_CUDA(cudaGetLastError());
+  return DVC_OK;
+}
+
+PreprocLaunch* preproc_alloc() { return new PreprocLaunch(); }
+void preproc_free(PreprocLaunch* L) { delete L; }
+void preproc_set_source(PreprocLaunch* L, const uint8_t* src, long long stride, const int* frame_index) {
+  L->args.src = src;
+  L->args.src_stride = stride;
+  L->args.frame_index = frame_index;
+}
+
+}  // namespace dvc
+
+extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int B, int sh, int sw, uint8_t* dst,
+                             long long dst_frame_stride, int dh, int dw, int mode, const int* xs, const int* xc,
+                             const float* xa, int x_taps, const int* ys, const int* yc, const float* ya, int y_taps,
+                             const int* xq, const int* yq, int ix, int iy, void* stream) {
+  using namespace dvc;
+  DVC_REQUIRE(B > 0 && sh > 0 && sw > 0 && dh > 0 && dw > 0 && mode >= 0 && mode <= 2, "resize: bad arguments");
+  if (mode == 0) DVC_REQUIRE(xs && xc && xa && ys && yc && ya, "resize: area tables missing");
+  if (mode == 1) DVC_REQUIRE(ix > 0 && iy > 0 && dw * ix <= sw && dh * iy <= sh, "resize: bad integer ratio");
+  if (mode == 2) DVC_REQUIRE(xs && ys && xq && yq, "resize: bilinear tables missing");
+  ResizeArgs a{src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps,
+               ys, yc, ya, y_taps, xq, yq, ix, iy};
+  const long long total = (long long)B * dh * dw;
+  resize_u8_kernel<<<(int)ceil_div64(total, 256), 256, 0, (cudaStream_t)stream>>>(a);
+  count_launch();
+  DVC_CHECK_CUDA(cudaGetLastError());
+  return DVC_OK;
+}
+
+extern "C" int dvc_preproc_conv0(const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B, int sh,
+                                 int sw, const int* xs, const int* xq, const int* ys, const int* yq, const float* w0,
+                                 const float* b0, const float* mean3, float scale, void* out_f16, void* stream) {
+  dvc::PreprocLaunch L;
+  int rc = dvc::preproc_prepare(&L, src400, src_frame_stride, frame_index, B, sh, sw, xs, xq, ys, yq, w0, b0, mean3, scale,
+                                out_f16, 0);
+  if (rc) return rc;
+  return dvc::preproc_launch(&L, (cudaStream_t)stream);
+}

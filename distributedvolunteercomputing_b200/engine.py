@@ -1,0 +1,350 @@
+"""Per-GPU inference engine: raw frames in, detections + annotated 400-wide frames out.
+
+Replaces the body of the reference worker's `request` branch (worker.py:241-280:
+imutils.resize -> cv2.resize -> blobFromImage -> net.forward -> filter -> draw).
+
+Two implementations behind one interface:
+  * ``NativeEngine`` – B200 path.  Static device buffers, weights packed once, the network
+    lowered to a native plan (csrc/plan.cu: tcgen05/TMA GEMMs, depthwise, fused preproc+conv0,
+    fused softmax/decode/NMS) replayed with ONE native call per batch and optionally captured
+    in a CUDA graph.  Early (large-activation) layers run in L2-sized sub-batches.
+  * ``CpuEngine``    – numpy/torch restatement for machines without a GPU (CI, remote CPU
+    volunteers); also the oracle in tests.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from .config import Config
+from .models import detection as D
+from .models import preprocess as P
+from .models.mobilenet_ssd import SSDGraph, TorchSSD, packed_weights
+from .utils import annotate as A
+
+
+@dataclass
+class BatchResult:
+    """Per-batch outputs. Tensors (native) or numpy arrays (cpu)."""
+    det: "np.ndarray | torch.Tensor"          # [B,100,7]
+    det_count: "np.ndarray | torch.Tensor"    # [B]
+    boxes_i: "np.ndarray | torch.Tensor"      # [B,100,4]
+    box_count: "np.ndarray | torch.Tensor"    # [B]
+    frames400: "np.ndarray | torch.Tensor"    # [B,h',w',3] annotated
+
+    def numpy(self) -> "BatchResult":
+        f = lambda t: t.detach().cpu().numpy() if isinstance(t, torch.Tensor) else t
+        return BatchResult(f(self.det), f(self.det_count), f(self.boxes_i), f(self.box_count), f(self.frames400))
+
+
+def consider_ids(names: Sequence[str]) -> Tuple[int, ...]:
+    return tuple(D.VOC_CLASSES.index(n) for n in names if n in D.VOC_CLASSES)
+
+
+# ======================================================================================= CPU
+class CpuEngine:
+    def __init__(self, graph: SSDGraph, cfg: Optional[Config] = None, requester_id: str = ""):
+        self.graph = graph
+        self.cfg = cfg or Config()
+        self.model = TorchSSD(graph).eval()
+        self.requester_id = requester_id
+        self.device = torch.device("cpu")
+
+    def infer_blob(self, blob: np.ndarray):
+        with torch.no_grad():
+            loc, conf = self.model(torch.from_numpy(blob))
+        return loc.numpy(), conf.numpy()
+
+    def process(self, frames, requester_id: Optional[str] = None, annotate: bool = True) -> BatchResult:
+        frames = np.asarray(frames)
+        B = frames.shape[0]
+        rid = self.requester_id if requester_id is None else requester_id
+        f400s, blobs = [], []
+        for f in frames:
+            f400 = P.resize_width_400(f, self.cfg.out_width)
+            img = P.resize_linear_u8(f400, P.NET_SIZE, P.NET_SIZE)
+            f400s.append(f400)
+            blobs.append(P.blob_from_image(img, self.cfg.mean, self.cfg.scale)[0])
+        loc, conf = self.infer_blob(np.stack(blobs))
+        g = self.graph
+        det = np.zeros((B, 100, 7), np.float32)
+        det_count = np.zeros((B,), np.int32)
+        boxes_i = np.zeros((B, 100, 4), np.int32)
+        box_count = np.zeros((B,), np.int32)
+        ids = consider_ids(self.cfg.consider)
+        for b in range(B):
+            d = D.detection_output(loc[b], D.softmax(conf[b]), g.priors, g.variances, g.det)
+            det[b, : len(d)] = d
+            det_count[b] = len(d)
+            h, w = f400s[b].shape[:2]
+            bx, n = D.app_filter(d, w, h, self.cfg.confidence, ids)
+            boxes_i[b, :n] = bx
+            box_count[b] = n
+            if annotate:
+                label = A.label_text({self.cfg.consider[0]: n}) if len(self.cfg.consider) == 1 else \
+                    A.label_text({c: sum(1 for r in d if r[2] > self.cfg.confidence and int(r[1]) == D.VOC_CLASSES.index(c))
+                                  for c in self.cfg.consider})
+                A.annotate_cpu(f400s[b], bx, rid, label)
+        return BatchResult(det, det_count, boxes_i, box_count, np.stack(f400s))
+
+
+# ==================================================================================== native
+class _ShapeState:
+    """Everything that depends on (batch, source frame size): buffers, tables, plan, graph."""
+    pass
+
+
+class NativeEngine:
+    def __init__(self, graph: SSDGraph, device="cuda:0", cfg: Optional[Config] = None, requester_id: str = "",
+                 max_batch: Optional[int] = None):
+        from .ops import kernels as K
+        from .ops import lib as L
+        if not torch.cuda.is_available():
+            raise RuntimeError("NativeEngine needs a CUDA device")
+        self.K, self.L = K, L
+        self.lib = L.load()
+        self.graph = graph
+        self.cfg = cfg or Config()
+        self.device = torch.device(device)
+        self.requester_id = requester_id
+        self.max_batch = max_batch or self.cfg.batch
+        self._states: Dict[Tuple[int, int, int, str], _ShapeState] = {}
+        with torch.cuda.device(self.device):
+            self._pack_weights()
+            self.priors, self.variances = K.priorbox(graph.priors_spec, graph.input_hw, self.device)
+
+    # ------------------------------------------------------------------ weights
+    def _pack_weights(self):
+        g, dev = self.graph, self.device
+        pk = packed_weights(g)
+        self.w: Dict[str, torch.Tensor] = {}
+        self.b: Dict[str, torch.Tensor] = {}
+        for c in g.convs:
+            w, b = pk[c.name]
+            if c.name == "conv0" or (c.k == 3 and not c.depthwise and c.cin * 9 < 64):
+                # first layer: fp32 [27][Cout]
+                self.w[c.name] = torch.from_numpy(np.ascontiguousarray(w.T)).to(dev, torch.float32)
+            elif c.depthwise:
+                self.w[c.name] = torch.from_numpy(w).to(dev, torch.float32)
+            else:
+                self.w[c.name] = torch.from_numpy(w).to(dev, torch.float16).contiguous()
+            self.b[c.name] = torch.from_numpy(np.ascontiguousarray(b)).to(dev, torch.float32)
+        for h in g.heads:
+            w, b = pk[f"{h.tap}_mbox"]
+            self.w[f"{h.tap}_mbox"] = torch.from_numpy(w).to(dev, torch.float16).contiguous()
+            self.b[f"{h.tap}_mbox"] = torch.from_numpy(b).to(dev, torch.float32)
+
+    def weight_bytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in list(self.w.values()) + list(self.b.values()))
+
+    # ------------------------------------------------------------------ per-shape state
+    def state(self, B: int, H: int, W: int, requester_id: Optional[str] = None) -> _ShapeState:
+        rid = self.requester_id if requester_id is None else requester_id
+        key = (B, H, W, rid)
+        st = self._states.get(key)
+        if st is None:
+            with torch.cuda.device(self.device):
+                st = self._make_state(B, H, W, rid)
+            self._states[key] = st
+        return st
+
+    def _make_state(self, B: int, H: int, W: int, rid: str) -> _ShapeState:
+        K, L, g, dev, cfg = self.K, self.L, self.graph, self.device, self.cfg
+        st = _ShapeState()
+        st.B, st.H, st.W = B, H, W
+        st.h4, st.w4 = P.out_size_400(H, W, cfg.out_width)
+        assert st.h4 >= 2, "frame too flat"
+        st.raw = torch.zeros((B, H, W, 3), dtype=torch.uint8, device=dev)
+        st.stride400 = K.align16(st.h4 * st.w4 * 3)
+        st.frames400_flat = torch.zeros((B, st.stride400), dtype=torch.uint8, device=dev)
+        st.frames400 = torch.as_strided(st.frames400_flat, (B, st.h4, st.w4, 3), (st.stride400, st.w4 * 3, 3, 1))
+        st.t_area = K.make_area_tables(H, W, st.h4, st.w4, dev)
+        st.t_lin = K.make_linear_tables(st.h4, st.w4, P.NET_SIZE, P.NET_SIZE, dev)
+        st.loc = torch.zeros((B, g.num_priors * 4), dtype=torch.float32, device=dev)
+        st.conf = torch.zeros((B, g.num_priors * g.num_classes), dtype=torch.float32, device=dev)
+        st.det = torch.zeros((B, 100, 7), dtype=torch.float32, device=dev)
+        st.det_count = torch.zeros((B,), dtype=torch.int32, device=dev)
+        st.boxes_i = torch.zeros((B, 100, 4), dtype=torch.int32, device=dev)
+        st.box_count = torch.zeros((B,), dtype=torch.int32, device=dev)
+        st.flags = torch.zeros((B,), dtype=torch.int32, device=dev)
+        st.det_scratch = torch.empty((K.detection_scratch_bytes(B, g.num_priors, g.num_classes),), dtype=torch.uint8, device=dev)
+        st.det_params = K.det_params(g.det, g.num_priors, st.w4, st.h4, cfg.confidence, consider_ids(cfg.consider))
+        idm, ixy, lm, lxy = A.text_masks(rid, st.h4, st.w4, cfg.consider)
+        st.masks = K.TextMasks(torch.from_numpy(idm).to(dev), ixy, torch.from_numpy(lm).to(dev), lxy)
+        st.mean = (C.c_float * 3)(*[float(v) for v in cfg.mean])
+        self._build_plan(st)
+        st.graph = None
+        return st
+
+    # ------------------------------------------------------------------ plan lowering
+    def _build_plan(self, st: _ShapeState):
+        L, g, dev, lib = self.L, self.graph, self.device, self.lib
+        B = st.B
+        sub = self.cfg.sub_batch if self.cfg.sub_batch > 0 else 16
+        sub = min(sub, B)
+        body = g.body
+        # split point: everything up to and including `split_name` runs per sub-batch
+        names = [c.name for c in body]
+        split_name = "conv6" if "conv6" in names else names[min(len(names) - 1, 12)]
+        split_idx = names.index(split_name)
+        per_frame = [c.out_hw[0] * c.out_hw[1] * c.cout for c in body]
+        early_max = max(per_frame[: split_idx + 1])
+        late_max = max(per_frame[split_idx:])
+        st.sA = torch.empty((sub * early_max,), dtype=torch.float16, device=dev)
+        st.sB = torch.empty((sub * early_max,), dtype=torch.float16, device=dev)
+        st.fA = torch.empty((B * late_max,), dtype=torch.float16, device=dev)
+        st.fB = torch.empty((B * late_max,), dtype=torch.float16, device=dev)
+        col_max = max([c.out_hw[0] * c.out_hw[1] * 9 * c.cin for c in body if c.k == 3 and not c.depthwise and c.name != "conv0"] + [8])
+        st.col = torch.empty((B * col_max,), dtype=torch.float16, device=dev)
+        plan = lib.dvc_plan_create()
+        st.plan = plan
+        st._keep = []
+        esz = 2
+        heads = {h.tap: h for h in g.heads}
+
+        def add_conv(c, src_ptr, dst_ptr, nb):
+            if c.depthwise:
+                L.check(lib.dvc_plan_add_dwconv(plan, src_ptr, nb, c.in_hw[0], c.in_hw[1], c.cin, c.stride,
+                                                L.ptr(self.w[c.name]), L.ptr(self.b[c.name]), int(c.relu), dst_ptr), c.name)
+            elif c.k == 1:
+                M = nb * c.out_hw[0] * c.out_hw[1]
+                L.check(lib.dvc_plan_add_gemm(plan, src_ptr, L.ptr(self.w[c.name]), L.ptr(self.b[c.name]), M, c.cout, c.cin,
+                                              c.cin, 0, dst_ptr, c.cout, int(c.relu), None, 0), c.name)
+            else:
+                assert c.k == 3 and c.stride == 2 and c.pad == 1, c
+                L.check(lib.dvc_plan_add_im2col(plan, src_ptr, nb, c.in_hw[0], c.in_hw[1], c.cin, L.ptr(st.col)), c.name + "/im2col")
+                M = nb * c.out_hw[0] * c.out_hw[1]
+                L.check(lib.dvc_plan_add_gemm(plan, L.ptr(st.col), L.ptr(self.w[c.name]), L.ptr(self.b[c.name]), M, c.cout,
+                                              9 * c.cin, 9 * c.cin, 0, dst_ptr, c.cout, int(c.relu), None, 0), c.name)
+
+        def add_head(h, src_ptr, nb, b0):
+            hw = h.grid_hw[0] * h.grid_hw[1]
+            w = self.w[f"{h.tap}_mbox"]
+            head = L.HeadOut(L.ptr(st.loc) + b0 * st.loc.stride(0) * 4, L.ptr(st.conf) + b0 * st.conf.stride(0) * 4,
+                             st.loc.stride(0), st.conf.stride(0), hw, h.loc.cout, h.conf.cout,
+                             h.prior_offset * 4, h.prior_offset * g.num_classes)
+            st._keep.append(head)
+            L.check(lib.dvc_plan_add_gemm(plan, src_ptr, L.ptr(w), L.ptr(self.b[f"{h.tap}_mbox"]), nb * hw, w.shape[0],
+                                          w.shape[1], w.shape[1], 1, None, 0, 0, C.byref(head), 0), h.tap + "_mbox")
+
+        assert body[0].name == "conv0" and body[0].k == 3 and body[0].cout == 32, "first layer must be the 3x3/s2 stem"
+        # ---- early layers, per sub-batch, in the small (L2-resident) ping-pong buffers
+        for b0 in range(0, B, sub):
+            nb = min(sub, B - b0)
+            cur, other = st.sA, st.sB
+            L.check(lib.dvc_plan_add_preproc_conv0(
+                plan, L.ptr(st.frames400_flat) + b0 * st.stride400, st.stride400, None, nb, st.h4, st.w4,
+                L.ptr(st.t_lin.xs), L.ptr(st.t_lin.xq), L.ptr(st.t_lin.ys), L.ptr(st.t_lin.yq), L.ptr(self.w["conv0"]),
+                L.ptr(self.b["conv0"]), C.cast(st.mean, C.c_void_p), float(self.cfg.scale), L.ptr(cur)), "conv0")
+            for li in range(1, split_idx + 1):
+                c = body[li]
+                if li == split_idx:
+                    dst = L.ptr(st.fA) + b0 * per_frame[li] * esz
+                else:
+                    dst = L.ptr(other)
+                add_conv(c, L.ptr(cur), dst, nb)
+                cur, other = other, cur
+                if c.top in heads and li != split_idx:
+                    add_head(heads[c.top], dst, nb, b0)
+        # ---- late layers on the full batch
+        cur, other = st.fA, st.fB
+        if body[split_idx].top in heads:
+            add_head(heads[body[split_idx].top], L.ptr(cur), B, 0)
+        for li in range(split_idx + 1, len(body)):
+            c = body[li]
+            add_conv(c, L.ptr(cur), L.ptr(other), B)
+            cur, other = other, cur
+            if c.top in heads:
+                add_head(heads[c.top], L.ptr(cur), B, 0)
+        L.check(lib.dvc_plan_add_detection(plan, L.ptr(st.loc), L.ptr(st.conf), L.ptr(self.priors), L.ptr(self.variances), B,
+                                           C.byref(st.det_params), None, L.ptr(st.det), L.ptr(st.det_count), L.ptr(st.boxes_i),
+                                           L.ptr(st.box_count), None, 0, L.ptr(st.det_scratch),
+                                           st.det_scratch.numel()), "detection")
+        st.n_ops = lib.dvc_plan_num_ops(plan)
+
+    # ------------------------------------------------------------------ execution
+    def launches_per_batch(self, st: _ShapeState, annotate: bool = True) -> int:
+        return st.n_ops + 1 + (1 if annotate else 0)   # plan ops + K1a resize + K10 annotate
+
+    def _enqueue_resize(self, st: _ShapeState, src: Optional[torch.Tensor] = None):
+        """K1a: raw frames (st.raw, or any other device batch of the same shape) -> 400-wide ring."""
+        self.K.resize_u8(st.raw if src is None else src, st.t_area, st.frames400_flat, st.stride400)
+
+    def _enqueue_body(self, st: _ShapeState, annotate: bool = True):
+        self.L.check(self.lib.dvc_plan_run(st.plan, self.L.stream_ptr()), "plan_run")
+        if annotate:
+            self._annotate_strided(st)
+
+    def _annotate_strided(self, st):
+        L = self.L
+        m = st.masks
+        nl, lh, lw = m.label_masks.shape
+        idh, idw = m.id_mask.shape
+        L.check(self.lib.dvc_annotate(L.ptr(st.frames400_flat), st.stride400, None, st.B, st.h4, st.w4, L.ptr(st.boxes_i),
+                                      L.ptr(st.box_count), None, L.ptr(m.id_mask), m.id_xy[0], m.id_xy[1], idw, idh,
+                                      L.ptr(m.label_masks), nl, m.label_xy[0], m.label_xy[1], lw, lh, L.stream_ptr()), "annotate")
+
+    def run(self, st: _ShapeState, annotate: bool = True, use_graph: Optional[bool] = None,
+            src: Optional[torch.Tensor] = None):
+        """Process the frames in ``st.raw`` (or in ``src``, a device batch of the same shape).
+        Asynchronous on the current stream.  With CUDA graphs the resize launch stays eager
+        (its source pointer may change per call) and everything after it is one graph replay."""
+        use_graph = self.cfg.use_cuda_graph if use_graph is None else use_graph
+        with torch.cuda.device(self.device):
+            self._enqueue_resize(st, src)
+            if not use_graph:
+                self._enqueue_body(st, annotate)
+                return
+            key = "graph_ann" if annotate else "graph_noann"
+            gr = getattr(st, key, None)
+            if gr is None:
+                # warm up outside capture (first-launch attribute setup), then capture
+                self._enqueue_body(st, annotate)
+                torch.cuda.synchronize(self.device)
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr):
+                    self._enqueue_body(st, annotate)
+                setattr(st, key, gr)
+            gr.replay()
+
+    def result(self, st: _ShapeState) -> BatchResult:
+        return BatchResult(st.det, st.det_count, st.boxes_i, st.box_count, st.frames400)
+
+    def process(self, frames, requester_id: Optional[str] = None, annotate: bool = True) -> BatchResult:
+        """frames: uint8 [B,H,W,3] (numpy / CPU tensor / CUDA tensor). Synchronous convenience API."""
+        t = torch.as_tensor(frames) if not isinstance(frames, torch.Tensor) else frames
+        B, H, W, _ = t.shape
+        st = self.state(B, H, W, requester_id)
+        with torch.cuda.device(self.device):
+            st.raw.copy_(t, non_blocking=True)
+            self.run(st, annotate)
+            torch.cuda.current_stream().synchronize()
+        return self.result(st)
+
+    def close(self):
+        for st in self._states.values():
+            if getattr(st, "plan", None):
+                self.lib.dvc_plan_destroy(st.plan)
+                st.plan = None
+        self._states.clear()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def create_engine(graph: SSDGraph, cfg: Optional[Config] = None, device: Optional[str] = None, requester_id: str = "",
+                  max_batch: Optional[int] = None):
+    cfg = cfg or Config()
+    dev = device or cfg.device
+    if dev == "auto":
+        dev = "cuda:0" if torch.cuda.is_available() else "cpu"
+    if str(dev).startswith("cuda"):
+        return NativeEngine(graph, dev, cfg, requester_id, max_batch)
+    return CpuEngine(graph, cfg, requester_id)

@@ -1,0 +1,163 @@
+/* dvc_b200 — C ABI of the B200-native MobileNet-SSD video-inference kernels.
+ *
+ * Every function returns 0 (DVC_OK) or a negative DVC_ERR_* code; dvc_last_error() gives
+ * the message for the calling thread.  All pointers are device pointers unless the name
+ * starts with h_.  `stream` is a cudaStream_t passed as void*.  Nothing in here allocates
+ * device memory unless the comment says so (dvc_plan_create, dvc_p2p_*).
+ *
+ * Reference parity citations are against /root/reference (worker.py, server.py and
+ * MobileNetSSD_deploy.prototxt.txt); the reference itself has no native code.
+ */
+#ifndef DVC_B200_H_
+#define DVC_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DVC_OK 0
+#define DVC_ERR_ARG (-1)
+#define DVC_ERR_CUDA (-2)
+#define DVC_ERR_UNSUPPORTED (-3)
+
+#define DVC_MAX_DET 100      /* keep_top_k, prototxt:1909 */
+#define DVC_DET_ROW 7        /* image_id,label,conf,xmin,ymin,xmax,ymax */
+
+int dvc_version(void);
+const char* dvc_last_error(void);
+/* Number of kernel launches issued by this library in this process (bench "gpu_launches"). */
+long long dvc_launch_count(void);
+
+/* ---- K1a: u8 HWC resize, the imutils.resize(width=400) step (worker.py:243).
+ * mode 0: INTER_AREA decimation by coefficient tables (xs/xc/xa = start index, tap count,
+ *         float weights [dst_w, max_taps]; same for y).
+ * mode 1: INTER_AREA with integer ratios (ix, iy), exact integer sums.
+ * mode 2: bilinear with Q11 fixed-point taps (enlarging INTER_AREA and plain INTER_LINEAR):
+ *         xs = source index, xq = [dst_w,2] int weights; same for y.
+ * src/dst are [B, h, w, 3]; src_frame_stride in bytes lets frames live in a ring. */
+int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int B, int sh, int sw,
+                  uint8_t* dst, long long dst_frame_stride, int dh, int dw, int mode,
+                  const int* xs, const int* xc, const float* xa, int x_taps,
+                  const int* ys, const int* yc, const float* ya, int y_taps,
+                  const int* xq, const int* yq, int ix, int iy, void* stream);
+
+/* ---- K1b: fused frame fetch + cv2.resize(300x300, INTER_LINEAR) + (x-mean_c)*scale +
+ * conv0 3x3/s2 + bias + ReLU (worker.py:245-246, prototxt:9-41).  `src400` may be a peer
+ * (NVLink-mapped) pointer: the loads ARE the frame scatter.  Output NHWC fp16
+ * [B,150,150,32].  w0 is fp32 [27][32] ((kh,kw,cin) major, cout innermost), b0 fp32 [32].
+ * xs/xq/ys/yq are the Q11 bilinear taps from (sh,sw) to 300x300.  h_mean3 is a HOST pointer to
+ * the 3 per-channel means.  frame_index (optional, may be NULL) maps batch slot -> frame slot
+ * inside the source ring.  Frames must be 16-byte aligned (base and stride). */
+int dvc_preproc_conv0(const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B, int sh, int sw,
+                      const int* xs, const int* xq, const int* ys, const int* yq,
+                      const float* w0, const float* b0, const float* h_mean3, float scale,
+                      void* out_f16, void* stream);
+
+/* ---- K3: depthwise 3x3 (+bias, +ReLU), NHWC fp16, pad 1, stride 1|2 (prototxt:42-75 ...).
+ * w is fp32 [9][C] (tap major), b fp32 [C]. */
+int dvc_dwconv3x3(const void* in_f16, int B, int H, int W, int C, int stride, const float* w, const float* b,
+                  int relu, void* out_f16, void* stream);
+
+/* ---- K2/K5: pointwise conv as GEMM on tcgen05 tensor cores with TMA-fed operands and a
+ * TMEM accumulator: out[M,N] = act(A[M,K] * Wt[N,K]^T + bias[N]).  A and Wt are K-major
+ * fp16 (NHWC activations / [Cout,Cin] weights).  N % 16 == 0, K % 8 == 0.
+ * out_mode 0: fp16 [M, ldc] (+ReLU if relu).
+ * out_mode 1: SSD head split store (prototxt:1147-1238 + 1817-1844): row m = b*hw + p;
+ *             columns [0,n_loc) -> loc[b][prior_off*4 + p*n_loc + c] (fp32, row pitch loc_pitch),
+ *             columns [n_loc,n_loc+n_conf) -> conf[b][prior_off*ncls... ] likewise. */
+typedef struct {
+  float* loc;            /* [B, loc_pitch]  */
+  float* conf;           /* [B, conf_pitch] */
+  long long loc_pitch;   /* 1917*4  */
+  long long conf_pitch;  /* 1917*21 */
+  int hw;                /* pixels per frame of this tap */
+  int n_loc;             /* anchors*4  */
+  int n_conf;            /* anchors*classes */
+  long long loc_off;     /* prior_off*4 */
+  long long conf_off;    /* prior_off*classes */
+} dvc_head_out;
+
+int dvc_gemm_f16(const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
+                 int out_mode, void* out_f16, int ldc, int relu, const dvc_head_out* head,
+                 int block_n, void* stream);
+
+/* ---- K4: 3x3 stride-2 pad-1 patch gather (im2col) NHWC fp16 -> [B*Ho*Wo, 9*C] with
+ * (kh,kw,c) column order; the dense extras convs (prototxt:922-954 ...) are then a GEMM. */
+int dvc_im2col3x3s2(const void* in_f16, int B, int H, int W, int C, void* out_f16, void* stream);
+
+/* ---- K6: PriorBox for one tap (prototxt:1239-1256), written at prior_off in [P,4] arrays. */
+int dvc_priorbox(float* boxes, float* variances, int prior_off, int grid_h, int grid_w, int img_h, int img_w,
+                 const float* anchor_wh, int anchors, float offset, const float* h_var4, int clip, void* stream);
+
+/* ---- K7+K8+K9: softmax + CENTER_SIZE decode + per-class top-k + NMS + keep_top_k + app
+ * filter, one CTA per frame (prototxt:1872-1912, worker.py:253-269).  Results are written
+ * through `out` pointers that may live on a peer GPU (the detection gather); when `flags`
+ * is non-NULL, flags[slot] is set to `flag_value` with release.sys semantics after the rows.
+ *   det      [B][100][7] fp32  rows sorted by (conf desc, prior asc, label asc), zero padded
+ *   det_count[B]               number of valid rows
+ *   boxes_i  [B][100][4] int32 app-filtered boxes scaled by (out_w,out_h) and truncated
+ *   box_count[B]               number of app-filtered boxes ("person: N")
+ * slot_index (optional) maps batch entry -> output slot.
+ * `scratch` is caller-provided global memory for the per-class candidate pool (worst case
+ * every prior passes the threshold in every foreground class, which cannot fit in shared
+ * memory): dvc_detection_scratch_bytes(B, priors, classes) bytes, 16-byte aligned.  Its
+ * contents are fully rewritten by every call; concurrent calls must not share it. */
+typedef struct {
+  int num_priors, num_classes, background;
+  float conf_thresh, nms_thresh;
+  int top_k, keep_top_k;
+  float app_conf;            /* 0.2, worker.py:186,257 */
+  uint32_t consider_mask;    /* bit c set => class c is drawn/counted (person = 1<<15) */
+  int out_w, out_h;          /* 400 x h' */
+} dvc_det_params;
+
+size_t dvc_detection_scratch_bytes(int B, int num_priors, int num_classes);
+int dvc_detection_output(const float* loc, const float* conf, const float* priors, const float* variances,
+                         int B, const dvc_det_params* p, const int* slot_index,
+                         float* det, int* det_count, int* boxes_i, int* box_count,
+                         uint32_t* flags, uint32_t flag_value, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- K10: annotation raster on the 400-wide BGR frames (worker.py:268-276): blue
+ * thickness-2 rectangles, then two pre-rendered text masks (id at (10,25) red; "person: N"
+ * at (10,h-20) green).  id_mask is [id_h][id_w] u8 placed at (id_x,id_y); label_masks is
+ * [n_labels][lab_h][lab_w], entry min(count, n_labels-1) is placed at (lab_x,lab_y). */
+int dvc_annotate(uint8_t* frames, long long frame_stride, const int* frame_index, int B, int h, int w,
+                 const int* boxes_i, const int* box_count, const int* slot_index,
+                 const uint8_t* id_mask, int id_x, int id_y, int id_w, int id_h,
+                 const uint8_t* label_masks, int n_labels, int lab_x, int lab_y, int lab_w, int lab_h,
+                 void* stream);
+
+/* ---- plan executor: the whole network as one native launch sequence. --------------------
+ * A plan owns pre-encoded TMA descriptors and launch geometry for a fixed max batch; the
+ * caller owns all memory (weights, activations, workspace).  Ops are appended once and then
+ * dvc_plan_run() replays them on a stream (capturable in a CUDA graph). */
+typedef struct dvc_plan dvc_plan;
+dvc_plan* dvc_plan_create(void);
+void dvc_plan_destroy(dvc_plan*);
+int dvc_plan_num_ops(const dvc_plan*);
+int dvc_plan_add_preproc_conv0(dvc_plan*, const uint8_t* src400, long long src_frame_stride, const int* frame_index,
+                               int B, int sh, int sw, const int* xs, const int* xq, const int* ys, const int* yq,
+                               const float* w0, const float* b0, const float* h_mean3, float scale, void* out_f16);
+int dvc_plan_add_dwconv(dvc_plan*, const void* in_f16, int B, int H, int W, int C, int stride, const float* w,
+                        const float* b, int relu, void* out_f16);
+int dvc_plan_add_gemm(dvc_plan*, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
+                      int out_mode, void* out_f16, int ldc, int relu, const dvc_head_out* head, int block_n);
+int dvc_plan_add_im2col(dvc_plan*, const void* in_f16, int B, int H, int W, int C, void* out_f16);
+int dvc_plan_add_detection(dvc_plan*, const float* loc, const float* conf, const float* priors, const float* variances,
+                           int B, const dvc_det_params* p, const int* slot_index, float* det, int* det_count,
+                           int* boxes_i, int* box_count, uint32_t* flags, uint32_t flag_value,
+                           void* scratch, size_t scratch_bytes);
+/* Re-point the frame source / result sinks of an existing plan (elastic re-dispatch). */
+int dvc_plan_set_source(dvc_plan*, const uint8_t* src400, long long src_frame_stride, const int* frame_index);
+int dvc_plan_set_sinks(dvc_plan*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags,
+                       const int* slot_index);
+int dvc_plan_set_flag_value(dvc_plan*, uint32_t flag_value);
+int dvc_plan_run(dvc_plan*, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DVC_B200_H_ */

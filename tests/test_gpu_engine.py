@@ -1,0 +1,94 @@
+"""GPU end-to-end: NativeEngine (sm_100a plan) vs the CPU restatement, eager vs CUDA graph."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from distributedvolunteercomputing_b200.config import Config
+from distributedvolunteercomputing_b200.engine import CpuEngine, NativeEngine
+from distributedvolunteercomputing_b200.models import detection as D
+
+
+def _frames(B, H, W, seed=0):
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(B):
+        small = rng.integers(0, 256, (H // 16 + 1, W // 16 + 1, 3), dtype=np.uint8)
+        out.append(cv2.resize(small, (W, H), interpolation=cv2.INTER_CUBIC))
+    return np.stack(out)
+
+
+@pytest.fixture(scope="module")
+def engines(graph):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    cfg = Config(sub_batch=4)
+    return NativeEngine(graph, "cuda:0", cfg, requester_id="127.0.0.1:5554"), CpuEngine(graph, cfg, requester_id="127.0.0.1:5554")
+
+
+@pytest.mark.parametrize("B,H,W", [(6, 300, 300), (3, 480, 640), (2, 720, 1280)])
+def test_engine_matches_cpu(engines, B, H, W):
+    nat, cpu = engines
+    frames = _frames(B, H, W, seed=B)
+    r = nat.process(frames).numpy()
+    c = cpu.process(frames)
+    assert r.frames400.shape == c.frames400.shape
+    tot_ref = tot_match = 0
+    for b in range(B):
+        ref = c.det[b, : c.det_count[b]]
+        got = r.det[b, : r.det_count[b]]
+        m, oa, ob = D.match_detections(got, ref, 2e-2, 2e-2)
+        tot_ref += len(ref)
+        tot_match += m
+        assert abs(len(got) - len(ref)) <= max(3, 0.1 * len(ref))
+    assert tot_ref > 10, "random-init model with conf gain should detect something"
+    assert tot_match >= 0.85 * tot_ref, (tot_match, tot_ref)
+    # annotated frames: identical except where a box/label differs because of fp16 detections
+    same = (r.frames400 == c.frames400).mean()
+    assert same > 0.97, same
+
+
+def test_engine_intermediate_layers_close(engines, graph):
+    """loc/conf of the native plan vs fp32 torch on the same preprocessed blob."""
+    nat, cpu = engines
+    frames = _frames(4, 300, 300, seed=9)
+    nat.process(frames)
+    st = nat.state(4, 300, 300)
+    loc = st.loc.cpu().numpy().reshape(4, -1, 4)
+    conf = st.conf.cpu().numpy().reshape(4, -1, graph.num_classes)
+    from distributedvolunteercomputing_b200.models import preprocess as P
+    blobs = np.concatenate([P.preprocess_frame(f, cpu.cfg.mean)[1] for f in frames])
+    rl, rc = cpu.infer_blob(blobs)
+    assert np.abs(loc - rl).max() <= 3e-2 * max(1.0, np.abs(rl).max())
+    assert np.abs(conf - rc).max() <= 3e-2 * max(1.0, np.abs(rc).max())
+
+
+def test_cuda_graph_replay_equals_eager(engines):
+    nat, _ = engines
+    frames = torch.from_numpy(_frames(6, 300, 300, seed=11)).cuda()
+    st = nat.state(6, 300, 300)
+    st.raw.copy_(frames)
+    nat.run(st, use_graph=False)
+    torch.cuda.synchronize()
+    eager = [t.clone() for t in (st.det, st.det_count, st.boxes_i, st.box_count, st.frames400)]
+    for _ in range(2):
+        st.raw.copy_(frames)
+        nat.run(st, use_graph=True)
+        torch.cuda.synchronize()
+        for a, b in zip(eager, (st.det, st.det_count, st.boxes_i, st.box_count, st.frames400)):
+            assert torch.equal(a, b)
+
+
+def test_sub_batch_invariance(graph):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    frames = _frames(8, 300, 300, seed=13)
+    outs = []
+    for sub in (1, 3, 8):
+        e = NativeEngine(graph, "cuda:0", Config(sub_batch=sub, use_cuda_graph=False))
+        outs.append(e.process(frames).numpy())
+        e.close()
+    for o in outs[1:]:
+        assert np.array_equal(o.det, outs[0].det) and np.array_equal(o.frames400, outs[0].frames400)
