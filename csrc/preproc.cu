@@ -91,6 +91,7 @@ constexpr int PC_NET = 300;
 constexpr int PC_OUT = 150;
 constexpr int PC_PCOLS = PC_NET + 1;        // image columns -1 .. 299
 constexpr int PC_THREADS = 256;
+constexpr int PC_BAND_OFF = (((27 * 32 + 32 + PC_PROWS * PC_PCOLS * 3) * 4 + 3 * PC_NET * 4) + 15) & ~15;
 
 struct PreprocArgs {
   const uint8_t* src; long long src_stride; const int* frame_index; int B, sh, sw;
@@ -108,7 +109,7 @@ __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const Prep
   float* s_patch = s_b + 32;                                     // [17][301][3]
   int* s_xs = reinterpret_cast<int*>(s_patch + PC_PROWS * PC_PCOLS * 3);   // [300]
   int* s_xq = s_xs + PC_NET;                                     // [300][2]
-  uint8_t* s_band = reinterpret_cast<uint8_t*>(s_xq + 2 * PC_NET);
+  uint8_t* s_band = smem + PC_BAND_OFF;   // 16-byte aligned: filled with 128-bit stores
 
   const int band = blockIdx.x, b = blockIdx.y;
   const int tid = threadIdx.x;
@@ -250,7 +251,7 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
   if (band_rows_max <= 0) band_rows_max = (PC_PROWS * sh + PC_NET - 1) / PC_NET + 3;
   if (band_rows_max > sh) band_rows_max = sh;
   a.band_bytes = ((band_rows_max * sw * 3 + 31) & ~15) + 16;
-  L->smem = (27 * 32 + 32 + PC_PROWS * PC_PCOLS * 3) * 4 + 3 * PC_NET * 4 + a.band_bytes;
+  L->smem = PC_BAND_OFF + a.band_bytes;
   DVC_REQUIRE(L->smem <= 227 * 1024, "preproc: source band of %d rows x %d px does not fit shared memory", band_rows_max, sw);
   L->grid = dim3((PC_OUT + PC_BAND - 1) / PC_BAND, B);
   return DVC_OK;

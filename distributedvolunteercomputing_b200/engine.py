@@ -309,7 +309,41 @@ class NativeEngine:
                 with torch.cuda.graph(gr):
                     self._enqueue_body(st, annotate)
                 setattr(st, key, gr)
+                # the warm-up pass annotated the 400-wide frames in place: regenerate them before the replay
+                self._enqueue_resize(st, src)
             gr.replay()
+
+    def debug_layerwise(self, frames400: torch.Tensor) -> Dict[str, torch.Tensor]:
+        """Run the network one native kernel at a time (per-op wrappers, separate output tensors).
+        Returns {layer name: NHWC fp16 activation} plus 'loc'/'conf'.  Test/debug aid only."""
+        K, g = self.K, self.graph
+        B = frames400.shape[0]
+        acts: Dict[str, torch.Tensor] = {}
+        with torch.cuda.device(self.device):
+            body = g.body
+            x = K.preproc_conv0(frames400, self.w["conv0"], self.b["conv0"], self.cfg.mean, self.cfg.scale)
+            acts["conv0"] = x
+            tops = {"conv0": x}
+            for c in body[1:]:
+                src = tops[c.bottom]
+                if c.depthwise:
+                    y = K.dwconv3x3(src, self.w[c.name], self.b[c.name], c.stride, c.relu)
+                elif c.k == 1:
+                    y = K.gemm_f16(src.view(-1, c.cin), self.w[c.name], self.b[c.name], c.relu).view(B, c.out_hw[0], c.out_hw[1], c.cout)
+                else:
+                    col = K.im2col3x3s2(src)
+                    y = K.gemm_f16(col, self.w[c.name], self.b[c.name], c.relu).view(B, c.out_hw[0], c.out_hw[1], c.cout)
+                tops[c.top] = y
+                acts[c.name] = y
+            loc = torch.zeros((B, g.num_priors * 4), dtype=torch.float32, device=self.device)
+            conf = torch.zeros((B, g.num_priors * g.num_classes), dtype=torch.float32, device=self.device)
+            for h in g.heads:
+                t = tops[h.tap]
+                K.gemm_head(t.view(-1, t.shape[-1]), self.w[f"{h.tap}_mbox"], self.b[f"{h.tap}_mbox"], loc, conf,
+                            h.grid_hw[0] * h.grid_hw[1], h.loc.cout, h.conf.cout, h.prior_offset, g.num_classes)
+            acts["loc"], acts["conf"] = loc, conf
+            torch.cuda.synchronize(self.device)
+        return acts
 
     def result(self, st: _ShapeState) -> BatchResult:
         return BatchResult(st.det, st.det_count, st.boxes_i, st.box_count, st.frames400)

@@ -7,4 +7,6 @@ timeout 400 $PT tests/test_gpu_kernels.py -k "not gemm" > gpurun_out/t_kernels.l
 timeout 400 $PT tests/test_gpu_kernels.py -k "gemm" > gpurun_out/t_gemm.log 2>&1; echo "gemm rc=$?"
 timeout 500 $PT tests/test_gpu_engine.py > gpurun_out/t_engine.log 2>&1; echo "engine rc=$?"
 timeout 300 python bench.py --steps 20 --warmup 3 > gpurun_out/bench.log 2>gpurun_out/bench.err; echo "bench rc=$?"
-tail -5 gpurun_out/t_kernels.log; tail -5 gpurun_out/t_gemm.log; tail -5 gpurun_out/t_engine.log; tail -2 gpurun_out/bench.log; tail -5 gpurun_out/bench.err
+grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/t_kernels.log gpurun_out/t_gemm.log gpurun_out/t_engine.log | head -40
+grep -E "^E  " gpurun_out/t_engine.log | cut -c1-300 | head -20
+tail -2 gpurun_out/bench.log | cut -c1-600; tail -5 gpurun_out/bench.err

@@ -50,6 +50,30 @@ def test_engine_matches_cpu(engines, B, H, W):
     assert same > 0.97, same
 
 
+def test_layerwise_kernels_vs_torch(engines, graph):
+    """Every layer, one native kernel at a time, against the fp32 torch model on the same blob."""
+    from distributedvolunteercomputing_b200.models import preprocess as P
+    from distributedvolunteercomputing_b200.models.mobilenet_ssd import TorchSSD
+    nat, cpu = engines
+    frames = _frames(5, 300, 300, seed=21)
+    f400 = np.stack([P.resize_width_400(f) for f in frames])
+    acts = nat.debug_layerwise(torch.from_numpy(f400).cuda())
+    blobs = np.concatenate([P.blob_from_image(P.resize_linear_u8(f, 300, 300), cpu.cfg.mean) for f in f400])
+    cap = {}
+    with torch.no_grad():
+        rl, rc = TorchSSD(graph)(torch.from_numpy(blobs), capture=cap)
+    bad = []
+    for c in graph.body:
+        ref = cap[c.name].permute(0, 2, 3, 1).numpy()
+        got = acts[c.name].float().cpu().numpy()
+        err = np.abs(got - ref).max() / max(1.0, np.abs(ref).max())
+        if err > 2e-2:
+            bad.append((c.name, float(err)))
+    assert not bad, bad
+    assert np.abs(acts["loc"].cpu().numpy().reshape(5, -1, 4) - rl.numpy()).max() <= 3e-2 * max(1.0, rl.abs().max().item())
+    assert np.abs(acts["conf"].cpu().numpy().reshape(5, -1, 21) - rc.numpy()).max() <= 3e-2 * max(1.0, rc.abs().max().item())
+
+
 def test_engine_intermediate_layers_close(engines, graph):
     """loc/conf of the native plan vs fp32 torch on the same preprocessed blob."""
     nat, cpu = engines

@@ -31,6 +31,7 @@ def _rand(shape, scale=1.0, seed=0):
     (128, 64, 64, 0), (300, 128, 64, 0), (1000, 64, 32, 0), (5625, 128, 128, 128), (1444, 256, 256, 256),
     (361 * 3, 512, 512, 128), (100, 1024, 1024, 256), (100, 256, 1024, 64), (25, 512, 2304, 0), (9, 128, 256, 0),
     (4, 64, 256, 0), (1, 128, 576, 0), (22500, 64, 32, 64), (700, 80, 512, 80), (300, 160, 1024, 160), (513, 48, 96, 48),
+    (2166, 512, 512, 16), (5776, 256, 256, 32), (2166, 512, 512, 0), (5776, 256, 256, 0), (4 * 22500, 64, 32, 0), (16 * 5625, 128, 128, 0),
 ])
 def test_gemm_matches_fp32(K, M, N, K_, bn):
     a = _rand((M, K_), 1.0, 1).half().to(DEV)
@@ -163,7 +164,10 @@ def test_detection_output_matches_restatement(K, graph, gain, seed):
         assert m == len(ref), (m, len(ref), len(oa), len(ob))
         if len(ref):
             assert np.all(np.diff(got[:, 2]) <= 0)            # sorted by confidence, descending
-            assert np.array_equal(got[:, 1], ref[:, 1])       # same deterministic order as the restatement
+            # same deterministic order as the restatement wherever scores are not within fp noise of a tie
+            gaps = np.abs(np.diff(ref[:, 2])) > 1e-6
+            solid = np.concatenate([[True], gaps]) & np.concatenate([gaps, [True]])
+            assert np.array_equal(got[solid, 1], ref[solid, 1])
         rb, rn = D.app_filter(got, 400, 300)
         assert bcnt[b] == rn and np.array_equal(boxes_i[b, :rn], rb)
 
