@@ -4,6 +4,8 @@
 // Reference ops: cv2.dnn PriorBox / Softmax / DetectionOutput layers
 // (prototxt:1239-1256, 1872-1880, 1890-1912), the Python post-filter loop of
 // worker.py:253-269 and the cv2.rectangle / cv2.putText overlay of worker.py:268-276.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace dvc {
@@ -378,6 +380,52 @@ extern "C" int dvc_detection_output(const float* loc, const float* conf, const f
                             flag_value, scratch, scratch_bytes);
   if (rc) return rc;
   return dvc::det_launch(&L, (cudaStream_t)stream);
+}
+
+// ---- allocation-free variant of dvc_detection_output -------------------------------------
+// The candidate pool lives in this file-scope device array instead of caller memory.  Every
+// GPU that loads the library carries these 4 MiB until the process exits.  In host code the
+// symbol below is only a stand-in: its device address is looked up once per device with
+// cudaGetSymbolAddress (with that device current) and that address is what the kernel gets.
+static __device__ __align__(256) unsigned char g_det_static_scratch[DVC_DET_STATIC_SCRATCH_BYTES];
+
+static int det_static_scratch(void** out) {
+  static std::mutex mu;
+  static void* ptrs[64] = {};
+  static bool ready[64] = {};
+  int dev = 0;
+  DVC_CHECK_CUDA(cudaGetDevice(&dev));
+  DVC_REQUIRE(dev >= 0 && dev < 64, "detection (static scratch): device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ready[dev]) {
+    void* p = nullptr;
+    DVC_CHECK_CUDA(cudaGetSymbolAddress(&p, g_det_static_scratch));
+    DVC_REQUIRE(p != nullptr, "detection (static scratch): cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = p;
+    ready[dev] = true;
+  }
+  *out = ptrs[dev];
+  return DVC_OK;
+}
+
+extern "C" int dvc_detection_output_static(const float* loc, const float* conf, const float* priors, const float* variances,
+                                           int B, const dvc_det_params* p, const int* slot_index, float* det, int* det_count,
+                                           int* boxes_i, int* box_count, uint32_t* flags, uint32_t flag_value, void* stream) {
+  using namespace dvc;
+  DVC_REQUIRE(p && B > 0, "detection (static scratch): bad arguments");
+  const size_t need = det_scratch_bytes(B, p->num_priors, p->num_classes);
+  DVC_REQUIRE(need <= (size_t)DVC_DET_STATIC_SCRATCH_BYTES,
+              "detection (static scratch): B=%d x %d priors x %d classes needs %zu bytes of candidate pool, the built-in "
+              "pool holds %zu; split the batch or use dvc_detection_output with your own scratch",
+              B, p->num_priors, p->num_classes, need, (size_t)DVC_DET_STATIC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  int rc = det_static_scratch(&scratch);
+  if (rc) return rc;
+  DetLaunch L;
+  rc = det_prepare(&L, loc, conf, priors, variances, B, p, slot_index, det, det_count, boxes_i, box_count, flags, flag_value,
+                   scratch, (size_t)DVC_DET_STATIC_SCRATCH_BYTES);
+  if (rc) return rc;
+  return det_launch(&L, (cudaStream_t)stream);
 }
 
 extern "C" int dvc_annotate(uint8_t* frames, long long frame_stride, const int* frame_index, int B, int h, int w,

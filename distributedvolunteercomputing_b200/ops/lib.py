@@ -47,6 +47,7 @@ _SIGS = {
     "dvc_priorbox": ([_P, _P, _I, _I, _I, _I, _I, _P, _I, _F, _P, _I, _P], _I),
     "dvc_detection_scratch_bytes": ([_I, _I, _I], _SZ),
     "dvc_detection_output": ([_P, _P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _U32, _P, _SZ, _P], _I),
+    "dvc_detection_output_static": ([_P, _P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _U32, _P], _I),
     "dvc_annotate": ([_P, _LL, _P, _I, _I, _I, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _P], _I),
     "dvc_plan_create": ([], _P),
     "dvc_plan_destroy": ([_P], None),

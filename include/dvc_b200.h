@@ -120,6 +120,33 @@ int dvc_detection_output(const float* loc, const float* conf, const float* prior
                          float* det, int* det_count, int* boxes_i, int* box_count,
                          uint32_t* flags, uint32_t flag_value, void* scratch, size_t scratch_bytes, void* stream);
 
+/* ---- Allocation-free variant of dvc_detection_output (no counterpart in the reference, which
+ * has no native code at all).
+ *
+ * Who it is for: embedders that cannot hand this library any device memory beyond the inputs
+ * and outputs - a volunteer's host application that reserved the whole GPU in its own pool at
+ * start-up, a capture loop that cannot afford the device-wide stall of cudaMalloc/cudaFree, or
+ * a plugin host written in C with no allocator to lend.  For them the per-class candidate pool
+ * sits in a device array built into the library (DVC_DET_STATIC_SCRATCH_BYTES on every GPU that
+ * loads the library, held until the process exits).  Nothing is allocated or freed here, by
+ * CUDA or by any other library.
+ *
+ * Limit: dvc_detection_scratch_bytes(B, num_priors, num_classes) must not exceed
+ * DVC_DET_STATIC_SCRATCH_BYTES (the 1917-prior, 21-class SSD fits B <= 13); larger requests
+ * are rejected with DVC_ERR_ARG and a message that names both sizes.
+ *
+ * The first call on each device looks the array's address up (that device must be current);
+ * make that first call before any stream capture begins.  All calls on a device share the one
+ * array: two calls whose kernels can overlap on that GPU (different streams, or concurrent
+ * host threads) race on it - serialise them.  The array keeps whatever the previous call left;
+ * the kernel only ever reads pool entries it wrote earlier in the same launch, so nothing has to
+ * be cleared between calls.  Outputs are identical to dvc_detection_output. */
+#define DVC_DET_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int dvc_detection_output_static(const float* loc, const float* conf, const float* priors, const float* variances,
+                                int B, const dvc_det_params* p, const int* slot_index,
+                                float* det, int* det_count, int* boxes_i, int* box_count,
+                                uint32_t* flags, uint32_t flag_value, void* stream);
+
 /* ---- K10: annotation raster on the 400-wide BGR frames (worker.py:268-276): blue
  * thickness-2 rectangles, then two pre-rendered text masks (id at (10,25) red; "person: N"
  * at (10,h-20) green).  id_mask is [id_h][id_w] u8 placed at (id_x,id_y); label_masks is
