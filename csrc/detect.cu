@@ -316,38 +316,74 @@ __device__ __forceinline__ bool on_rect(int x, int y, int x0, int y0, int x1, in
   return true;
 }
 
-__global__ void __launch_bounds__(256) annotate_kernel(const AnnArgs a) {
+constexpr int ANN_THREADS = 512;
+
+// One CTA per frame.  Work is proportional to what is drawn (box perimeters + text masks), not to
+// the frame area: for each box the four 3-pixel bands of its outline are rasterised with the exact
+// rule above; the two text overlays follow after a barrier so they win over box pixels, as in the
+// reference's draw order (worker.py:268-276).
+__global__ void __launch_bounds__(ANN_THREADS) annotate_kernel(const AnnArgs a) {
   __shared__ int s_box[DVC_MAX_DET * 4];
   __shared__ int s_n;
-  const int b = blockIdx.y;
+  const int b = blockIdx.x;
+  const int tid = threadIdx.x;
   const int slot = a.slot_index ? a.slot_index[b] : b;
   const int fslot = a.frame_index ? a.frame_index[b] : b;
-  if (threadIdx.x == 0) s_n = min(max(a.box_count[slot], 0), DVC_MAX_DET);
+  if (tid == 0) s_n = min(max(a.box_count[slot], 0), DVC_MAX_DET);
   __syncthreads();
   const int n = s_n;
-  for (int i = threadIdx.x; i < n * 4; i += 256) s_box[i] = a.boxes_i[(size_t)slot * DVC_MAX_DET * 4 + i];
+  for (int i = tid; i < n * 4; i += ANN_THREADS) s_box[i] = a.boxes_i[(size_t)slot * DVC_MAX_DET * 4 + i];
   __syncthreads();
-  const int label = min(n, a.n_labels - 1);
-  const uint8_t* lab = a.label_masks ? a.label_masks + (size_t)label * a.lab_w * a.lab_h : nullptr;
   uint8_t* frame = a.frames + (size_t)fslot * a.stride;
-  for (int i = blockIdx.x * 256 + threadIdx.x; i < a.h * a.w; i += gridDim.x * 256) {
-    const int y = i / a.w, x = i - y * a.w;
-    int col = -1;   // 0 blue box, 1 red id text, 2 green label text (drawn in that order, later wins)
-    for (int k = 0; k < n; ++k)
-      if (on_rect(x, y, s_box[4 * k], s_box[4 * k + 1], s_box[4 * k + 2], s_box[4 * k + 3])) { col = 0; break; }
-    if (a.id_mask) {
-      const int mx = x - a.id_x, my = y - a.id_y;
-      if (mx >= 0 && mx < a.id_w && my >= 0 && my < a.id_h && a.id_mask[my * a.id_w + mx]) col = 1;
+  for (int k = 0; k < n; ++k) {
+    int x0 = s_box[4 * k], y0 = s_box[4 * k + 1], x1 = s_box[4 * k + 2], y1 = s_box[4 * k + 3];
+    if (x0 > x1) { int t = x0; x0 = x1; x1 = t; }
+    if (y0 > y1) { int t = y0; y0 = y1; y1 = t; }
+    // bands: 0 top, 1 bottom, 2 left, 3 right (each 3 pixels thick, clipped to the frame)
+#pragma unroll
+    for (int band = 0; band < 4; ++band) {
+      long long bx0, bx1, by0, by1;
+      if (band < 2) {
+        bx0 = (long long)x0 - 1; bx1 = (long long)x1 + 1;
+        by0 = band == 0 ? (long long)y0 - 1 : (long long)y1 - 1;
+        by1 = by0 + 2;
+      } else {
+        by0 = (long long)y0 - 1; by1 = (long long)y1 + 1;
+        bx0 = band == 2 ? (long long)x0 - 1 : (long long)x1 - 1;
+        bx1 = bx0 + 2;
+      }
+      const int cx0 = (int)max(bx0, 0LL), cx1 = (int)min(bx1, (long long)a.w - 1);
+      const int cy0 = (int)max(by0, 0LL), cy1 = (int)min(by1, (long long)a.h - 1);
+      if (cx0 > cx1 || cy0 > cy1) continue;
+      const int bw = cx1 - cx0 + 1, cnt = bw * (cy1 - cy0 + 1);
+      for (int i = tid; i < cnt; i += ANN_THREADS) {
+        const int y = cy0 + i / bw, x = cx0 + i % bw;
+        if (on_rect(x, y, x0, y0, x1, y1)) {
+          uint8_t* p = frame + ((size_t)y * a.w + x) * 3;
+          p[0] = 255; p[1] = 0; p[2] = 0;
+        }
+      }
     }
-    if (lab) {
-      const int mx = x - a.lab_x, my = y - a.lab_y;
-      if (mx >= 0 && mx < a.lab_w && my >= 0 && my < a.lab_h && lab[my * a.lab_w + mx]) col = 2;
+  }
+  __syncthreads();
+  if (a.id_mask) {
+    for (int i = tid; i < a.id_w * a.id_h; i += ANN_THREADS) {
+      const int y = a.id_y + i / a.id_w, x = a.id_x + i % a.id_w;
+      if (a.id_mask[i] && x >= 0 && x < a.w && y >= 0 && y < a.h) {
+        uint8_t* p = frame + ((size_t)y * a.w + x) * 3;
+        p[0] = 0; p[1] = 0; p[2] = 255;
+      }
     }
-    if (col >= 0) {
-      uint8_t* p = frame + (size_t)i * 3;
-      p[0] = col == 0 ? 255 : 0;
-      p[1] = col == 2 ? 255 : 0;
-      p[2] = col == 1 ? 255 : 0;
+  }
+  __syncthreads();
+  if (a.label_masks) {
+    const uint8_t* lab = a.label_masks + (size_t)min(n, a.n_labels - 1) * a.lab_w * a.lab_h;
+    for (int i = tid; i < a.lab_w * a.lab_h; i += ANN_THREADS) {
+      const int y = a.lab_y + i / a.lab_w, x = a.lab_x + i % a.lab_w;
+      if (lab[i] && x >= 0 && x < a.w && y >= 0 && y < a.h) {
+        uint8_t* p = frame + ((size_t)y * a.w + x) * 3;
+        p[0] = 0; p[1] = 255; p[2] = 0;
+      }
     }
   }
 }
@@ -437,8 +473,7 @@ extern "C" int dvc_annotate(uint8_t* frames, long long frame_stride, const int* 
   DVC_REQUIRE(!label_masks || n_labels > 0, "annotate: n_labels must be positive");
   AnnArgs a{frames, frame_stride, frame_index, B, h, w, boxes_i, box_count, slot_index, id_mask, id_x, id_y, id_w, id_h,
             label_masks, n_labels, lab_x, lab_y, lab_w, lab_h};
-  dim3 grid(ceil_div(h * w, 256 * 4), B);
-  annotate_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  annotate_kernel<<<B, ANN_THREADS, 0, (cudaStream_t)stream>>>(a);
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;

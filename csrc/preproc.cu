@@ -21,66 +21,94 @@ struct ResizeArgs {
   const int *xq, *yq; int ix, iy;
 };
 
+// Each thread produces RP horizontally adjacent output pixels (RP = 4 when the output width
+// allows it, so the 12 output bytes go out as three aligned 32-bit stores).
+template <int RP>
 __global__ void __launch_bounds__(256) resize_u8_kernel(const ResizeArgs a) {
   const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
-  const long long per = (long long)a.dh * a.dw;
+  const int gw = a.dw / RP;
+  const long long per = (long long)a.dh * gw;
   if (idx >= per * a.B) return;
   const int b = (int)(idx / per);
   const int rem = (int)(idx - (long long)b * per);
-  const int dy = rem / a.dw, dx = rem - dy * a.dw;
+  const int dy = rem / gw, dxg = (rem - dy * gw) * RP;
   const uint8_t* s = a.src + (size_t)b * a.src_stride;
-  uint8_t* d = a.dst + (size_t)b * a.dst_stride + ((size_t)dy * a.dw + dx) * 3;
+  uint8_t* d = a.dst + (size_t)b * a.dst_stride + ((size_t)dy * a.dw + dxg) * 3;
+  uint8_t o[RP * 3];
   if (a.mode == 0) {
-    float o0 = 0.f, o1 = 0.f, o2 = 0.f;
-    const int x0 = a.xs[dx], xn = a.xc[dx], y0 = a.ys[dy], yn = a.yc[dy];
-    for (int ky = 0; ky < yn; ++ky) {
-      const uint8_t* row = s + (size_t)(y0 + ky) * a.sw * 3;
-      float h0 = 0.f, h1 = 0.f, h2 = 0.f;
-      for (int kx = 0; kx < xn; ++kx) {
-        const float al = a.xa[dx * a.x_taps + kx];
-        const uint8_t* p = row + (size_t)(x0 + kx) * 3;
-        // unfused multiply/add on purpose: matches cv2's (and numpy's) float op order bit for bit
-        h0 = __fadd_rn(h0, __fmul_rn((float)p[0], al));
-        h1 = __fadd_rn(h1, __fmul_rn((float)p[1], al));
-        h2 = __fadd_rn(h2, __fmul_rn((float)p[2], al));
+    const int y0 = a.ys[dy], yn = a.yc[dy];
+#pragma unroll
+    for (int r = 0; r < RP; ++r) {
+      const int dx = dxg + r;
+      float o0 = 0.f, o1 = 0.f, o2 = 0.f;
+      const int x0 = a.xs[dx], xn = a.xc[dx];
+      for (int ky = 0; ky < yn; ++ky) {
+        const uint8_t* row = s + (size_t)(y0 + ky) * a.sw * 3;
+        float h0 = 0.f, h1 = 0.f, h2 = 0.f;
+        for (int kx = 0; kx < xn; ++kx) {
+          const float al = a.xa[dx * a.x_taps + kx];
+          const uint8_t* p = row + (size_t)(x0 + kx) * 3;
+          // unfused multiply/add on purpose: matches cv2's (and numpy's) float op order bit for bit
+          h0 = __fadd_rn(h0, __fmul_rn((float)p[0], al));
+          h1 = __fadd_rn(h1, __fmul_rn((float)p[1], al));
+          h2 = __fadd_rn(h2, __fmul_rn((float)p[2], al));
+        }
+        const float be = a.ya[dy * a.y_taps + ky];
+        o0 = __fadd_rn(o0, __fmul_rn(h0, be));
+        o1 = __fadd_rn(o1, __fmul_rn(h1, be));
+        o2 = __fadd_rn(o2, __fmul_rn(h2, be));
       }
-      const float be = a.ya[dy * a.y_taps + ky];
-      o0 = __fadd_rn(o0, __fmul_rn(h0, be));
-      o1 = __fadd_rn(o1, __fmul_rn(h1, be));
-      o2 = __fadd_rn(o2, __fmul_rn(h2, be));
+      o[r * 3 + 0] = (uint8_t)min(max(__float2int_rn(o0), 0), 255);
+      o[r * 3 + 1] = (uint8_t)min(max(__float2int_rn(o1), 0), 255);
+      o[r * 3 + 2] = (uint8_t)min(max(__float2int_rn(o2), 0), 255);
     }
-    d[0] = (uint8_t)min(max(__float2int_rn(o0), 0), 255);
-    d[1] = (uint8_t)min(max(__float2int_rn(o1), 0), 255);
-    d[2] = (uint8_t)min(max(__float2int_rn(o2), 0), 255);
   } else if (a.mode == 1) {
-    int s0 = 0, s1 = 0, s2 = 0;
-    for (int ky = 0; ky < a.iy; ++ky) {
-      const uint8_t* row = s + ((size_t)(dy * a.iy + ky) * a.sw + (size_t)dx * a.ix) * 3;
-      for (int kx = 0; kx < a.ix; ++kx) {
-        s0 += row[kx * 3]; s1 += row[kx * 3 + 1]; s2 += row[kx * 3 + 2];
+#pragma unroll
+    for (int r = 0; r < RP; ++r) {
+      const int dx = dxg + r;
+      int s0 = 0, s1 = 0, s2 = 0;
+      for (int ky = 0; ky < a.iy; ++ky) {
+        const uint8_t* row = s + ((size_t)(dy * a.iy + ky) * a.sw + (size_t)dx * a.ix) * 3;
+        for (int kx = 0; kx < a.ix; ++kx) {
+          s0 += row[kx * 3]; s1 += row[kx * 3 + 1]; s2 += row[kx * 3 + 2];
+        }
       }
-    }
-    if (a.ix == 2 && a.iy == 2) {
-      d[0] = (uint8_t)((s0 + 2) >> 2); d[1] = (uint8_t)((s1 + 2) >> 2); d[2] = (uint8_t)((s2 + 2) >> 2);
-    } else {
-      const float sc = 1.0f / (float)(a.ix * a.iy);
-      d[0] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s0, sc)), 255);
-      d[1] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s1, sc)), 255);
-      d[2] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s2, sc)), 255);
+      if (a.ix == 2 && a.iy == 2) {
+        o[r * 3] = (uint8_t)((s0 + 2) >> 2); o[r * 3 + 1] = (uint8_t)((s1 + 2) >> 2); o[r * 3 + 2] = (uint8_t)((s2 + 2) >> 2);
+      } else {
+        const float sc = 1.0f / (float)(a.ix * a.iy);
+        o[r * 3] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s0, sc)), 255);
+        o[r * 3 + 1] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s1, sc)), 255);
+        o[r * 3 + 2] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s2, sc)), 255);
+      }
     }
   } else {
-    const int sx0 = a.xs[dx], sx1 = min(sx0 + 1, a.sw - 1);
     const int sy0 = a.ys[dy], sy1 = min(sy0 + 1, a.sh - 1);
-    const int a0 = a.xq[dx * 2], a1 = a.xq[dx * 2 + 1], b0 = a.yq[dy * 2], b1 = a.yq[dy * 2 + 1];
+    const int b0 = a.yq[dy * 2], b1 = a.yq[dy * 2 + 1];
     const uint8_t* r0 = s + (size_t)sy0 * a.sw * 3;
     const uint8_t* r1 = s + (size_t)sy1 * a.sw * 3;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
-      const int h1 = r1[sx0 * 3 + c] * a0 + r1[sx1 * 3 + c] * a1;
-      const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-      d[c] = (uint8_t)min(max(v, 0), 255);
+    for (int r = 0; r < RP; ++r) {
+      const int dx = dxg + r;
+      const int sx0 = a.xs[dx], sx1 = min(sx0 + 1, a.sw - 1);
+      const int a0 = a.xq[dx * 2], a1 = a.xq[dx * 2 + 1];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
+        const int h1 = r1[sx0 * 3 + c] * a0 + r1[sx1 * 3 + c] * a1;
+        const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+        o[r * 3 + c] = (uint8_t)min(max(v, 0), 255);
+      }
     }
+  }
+  if (RP == 4) {
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(d);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      d32[k] = (uint32_t)o[4 * k] | ((uint32_t)o[4 * k + 1] << 8) | ((uint32_t)o[4 * k + 2] << 16) | ((uint32_t)o[4 * k + 3] << 24);
+  } else {
+#pragma unroll
+    for (int k = 0; k < RP * 3; ++k) d[k] = o[k];
   }
 }
 
@@ -292,8 +320,10 @@ extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int
   if (mode == 2) DVC_REQUIRE(xs && ys && xq && yq, "resize: bilinear tables missing");
   ResizeArgs a{src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps,
                ys, yc, ya, y_taps, xq, yq, ix, iy};
-  const long long total = (long long)B * dh * dw;
-  resize_u8_kernel<<<(int)ceil_div64(total, 256), 256, 0, (cudaStream_t)stream>>>(a);
+  const bool vec4 = dw % 4 == 0 && dst_frame_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0;
+  const long long total = (long long)B * dh * (vec4 ? dw / 4 : dw);
+  if (vec4) resize_u8_kernel<4><<<(int)ceil_div64(total, 256), 256, 0, (cudaStream_t)stream>>>(a);
+  else resize_u8_kernel<1><<<(int)ceil_div64(total, 256), 256, 0, (cudaStream_t)stream>>>(a);
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;

@@ -1,0 +1,299 @@
+"""`coordinator`: the server process (public surface of the reference's server.py).
+
+Same wire behaviour as the reference class of the same name (server.py:7-163) - UDP membership
+on port 9999, one REP data port per client from the 5555.. pool, chunks relayed as imagezmq
+messages - but the distribution loop is `parallel.scheduler.Scheduler`:
+
+  * chunks wait in per-requester queues until a worker is eligible (the reference drops them,
+    server.py:82,88);
+  * every dispatched chunk stays in the in-flight table until all of its frames have come back;
+    when its owner leaves (`end`) or stops answering, the chunk is re-dispatched, so a job no
+    longer hangs when a volunteer quits mid-stream;
+  * `join` is idempotent, threads block on queues/conditions instead of spinning, every socket
+    call has a timeout so `quit` actually terminates.
+"""
+from __future__ import annotations
+
+import queue
+import socket
+import threading
+import time
+from typing import Dict, List, Optional, Set, Tuple
+
+import numpy as np
+
+from . import protocol as proto
+from .config import Config
+from .parallel.scheduler import Batch, Scheduler
+from .utils.metrics import Logger, Metrics
+
+
+class coordinator:  # noqa: N801  (name kept from the reference's public surface)
+    def __init__(self, ip: str = "localhost", cfg: Optional[Config] = None, start: bool = True):
+        self.cfg = cfg or Config.from_env()
+        self.my_ip = f"{ip}:{self.cfg.control_port}"
+        self.logger = Logger(self.cfg.verbose, "[server] ")
+        self.log = self.logger.log
+        self.metrics = Metrics(self.cfg.metrics_jsonl)
+        self.sched = Scheduler(policy=self.cfg.dispatch_policy, requester_works=False,
+                               worker_timeout_s=self.cfg.worker_timeout_s)
+        self.lock = threading.RLock()
+        self.running = False
+        self.free_ports: List[int] = list(range(self.cfg.data_port_lo, self.cfg.data_port_hi + 1))
+        self.port_of: Dict[str, int] = {}
+        self.senders: Dict[str, proto.ImageSender] = {}
+        self.sender_locks: Dict[str, threading.Lock] = {}
+        self.ingest_stop: Dict[str, threading.Event] = {}
+        self.results: Dict[str, "queue.Queue"] = {}
+        self.reply_stop: Dict[str, threading.Event] = {}
+        # frame bookkeeping: requester -> frame number -> batch id ; batch id -> frames still missing
+        self.frame_owner: Dict[str, Dict[int, int]] = {}
+        self.missing: Dict[int, Set[int]] = {}
+        self.threads: List[threading.Thread] = []
+        if start:
+            self.start()
+
+    # ------------------------------------------------------------------ lifecycle
+    def start(self):
+        self.running = True
+        self.sock = socket.socket(socket.AF_INET, socket.SOCK_DGRAM)
+        self.sock.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+        self.sock.bind(("", self.cfg.control_port))
+        self.sock.settimeout(min(self.cfg.control_poll_s, 0.5))
+        print("\nlistening on %s port %s" % ("", self.cfg.control_port), flush=True)
+        for target in (self.manager, self.send_request, self.watchdog):
+            t = threading.Thread(target=target, daemon=True)
+            t.start()
+            self.threads.append(t)
+
+    def exit_threads(self):
+        """`quit` (server.py:160-163) - and the threads really stop."""
+        self.running = False
+        for ev in list(self.ingest_stop.values()) + list(self.reply_stop.values()):
+            ev.set()
+        with self.sched.cv:
+            self.sched.cv.notify_all()
+        for t in self.threads:
+            t.join(timeout=2.0)
+        try:
+            self.sock.close()
+        except Exception:
+            pass
+        for s in list(self.senders.values()):
+            s.close()
+
+    # ------------------------------------------------------------------ control plane
+    def manager(self):
+        while self.running:
+            try:
+                message, client_address = self.sock.recvfrom(4096)
+            except socket.timeout:
+                continue
+            except OSError:
+                break
+            cmd, address = proto.parse_control(message)
+            try:
+                reply = self.handle_control(cmd, address)
+            except Exception as e:  # never let one bad datagram kill membership
+                self.log(f"control error {cmd} {address}: {e!r}")
+                reply = None
+            if reply is not None:
+                self.sock.sendto(reply.encode("utf-8"), client_address)
+        print("manager terminated.", flush=True)
+
+    def handle_control(self, cmd: Optional[str], address: str) -> Optional[str]:
+        if cmd == "join":
+            with self.lock:
+                _, new = self.sched.join(address, capacity=2)
+                if not new and address in self.port_of:
+                    return "ok||" + str(self.port_of[address])          # idempotent retry
+                port = self._alloc_port()
+                self.port_of[address] = port
+                host, cport = address.split(":")
+                print("sending to : tcp://" + host + ":" + cport, flush=True)
+                self.senders[address] = proto.ImageSender("tcp://" + host + ":" + cport, timeout_s=self.cfg.data_timeout_s)
+                self.sender_locks[address] = threading.Lock()
+                ev = threading.Event()
+                self.ingest_stop[address] = ev
+                t = threading.Thread(target=self.server, args=["", port, address, ev], daemon=True)
+                t.start()
+                self.threads.append(t)
+            self.metrics.inc("joins")
+            return "ok||" + str(port)
+        if cmd == "request":
+            if address not in self.port_of:
+                return None
+            self.sched.become_requester(address)
+            with self.lock:
+                self.frame_owner.setdefault(address, {})
+                if address not in self.results:
+                    self.results[address] = queue.Queue()
+                    ev = threading.Event()
+                    self.reply_stop[address] = ev
+                    t = threading.Thread(target=self.send_reply, args=[address, ev], daemon=True)
+                    t.start()
+                    self.threads.append(t)
+            return "ok"
+        if cmd == "stop":
+            self.sched.stop_requesting(address)
+            return "ok"
+        if cmd == "end":
+            self._remove_client(address)
+            return "ok"
+        return None
+
+    def _alloc_port(self) -> int:
+        if self.free_ports:
+            return self.free_ports.pop(0)
+        return proto.free_tcp_port()          # the reference stops at 45 clients (server.py:18); we keep going
+
+    def _remove_client(self, address: str):
+        requeued = self.sched.leave(address)
+        if requeued:
+            self.metrics.inc("redispatched_chunks", len(requeued))
+            self.log(f"{address} left with {len(requeued)} chunk(s) in flight: re-dispatching")
+        with self.lock:
+            port = self.port_of.pop(address, None)
+            if port is not None and self.cfg.data_port_lo <= port <= self.cfg.data_port_hi:
+                self.free_ports.append(port)
+            ev = self.ingest_stop.pop(address, None)
+            if ev:
+                ev.set()
+            ev = self.reply_stop.pop(address, None)
+            if ev:
+                ev.set()
+            s = self.senders.pop(address, None)
+            if s:
+                s.close()
+            self.sender_locks.pop(address, None)
+            self.results.pop(address, None)
+        if address in self.frame_owner:
+            self.sched.drop_requester(address)
+            self.frame_owner.pop(address, None)
+
+    # ------------------------------------------------------------------ data plane: ingest
+    def server(self, ip: str, port: int, address: str, stop: threading.Event):
+        print("receiving at : tcp://*:" + str(port), flush=True)
+        hub = proto.ImageHub("tcp://*:" + str(port))
+        try:
+            while self.running and not stop.is_set():
+                got = hub.recv_image(timeout_s=0.25)
+                if got is None:
+                    continue
+                info, frame = got
+                self.log(info)
+                try:
+                    self._on_chunk(info, frame, address)
+                finally:
+                    hub.send_reply(b"OK")
+        finally:
+            hub.close()
+            print("server terminated.", flush=True)
+
+    def _on_chunk(self, info: str, frame: np.ndarray, sender_addr: str):
+        hdr = proto.parse_header(info)
+        self.sched.members.touch(sender_addr)
+        if hdr.cmd == "request":
+            while self.running and self.sched.pending() > self.cfg.max_buffer_chunks:
+                time.sleep(0.02)                                        # backpressure (server.py:54)
+            b = self.sched.submit(hdr.requester, hdr.frames, payload=(info, np.array(frame, copy=True)))
+            with self.lock:
+                owner = self.frame_owner.setdefault(hdr.requester, {})
+                for n in hdr.frames:
+                    owner[n] = b.batch_id
+                self.missing[b.batch_id] = set(hdr.frames)
+            self.metrics.inc("frames_in", len(hdr.frames))
+        elif hdr.cmd == "processed":
+            fresh = False
+            finished: List[int] = []
+            with self.lock:
+                owner = self.frame_owner.get(hdr.requester, {})
+                for n in hdr.frames:
+                    bid = owner.get(n)
+                    if bid is None:
+                        continue
+                    miss = self.missing.get(bid)
+                    if miss is not None and n in miss:
+                        miss.discard(n)
+                        fresh = True
+                        if not miss:
+                            finished.append(bid)
+                            del self.missing[bid]
+                q = self.results.get(hdr.requester)
+            for bid in finished:
+                self.sched.complete(bid, sender_addr)
+            if fresh and q is not None:
+                q.put((info, np.array(frame, copy=True)))
+                self.metrics.inc("frames_out", len(hdr.frames))
+            elif not fresh:
+                self.metrics.inc("duplicate_chunks")
+
+    # ------------------------------------------------------------------ data plane: dispatch / return
+    def send_request(self):
+        while self.running:
+            d = self.sched.wait_dispatch(timeout=0.2)
+            if d is None:
+                continue
+            batch, worker, epoch = d
+            info, frame = batch.payload
+            sender = self.senders.get(worker.addr)
+            lock = self.sender_locks.get(worker.addr)
+            if sender is None or lock is None:
+                self.sched.fail(batch.batch_id, "no_sender")
+                continue
+            try:
+                with lock:
+                    sender.send_image(info, frame)
+                self.metrics.inc("chunks_dispatched")
+            except TimeoutError:
+                self.log(f"worker {worker.addr} did not acknowledge a chunk: marking it gone")
+                self.metrics.inc("dispatch_timeouts")
+                self.sched.leave(worker.addr)          # re-queues this batch and anything else it held
+        print("send_request terminated.", flush=True)
+
+    def send_reply(self, address: str, stop: threading.Event):
+        while self.running and not stop.is_set():
+            q = self.results.get(address)
+            if q is None:
+                break
+            try:
+                info, frame = q.get(timeout=0.25)
+            except queue.Empty:
+                continue
+            sender = self.senders.get(address)
+            lock = self.sender_locks.get(address)
+            if sender is None or lock is None:
+                break
+            for attempt in range(3):
+                try:
+                    with lock:
+                        sender.send_image(info, frame)
+                    break
+                except TimeoutError:
+                    self.metrics.inc("reply_timeouts")
+        print("send_reply terminated.", flush=True)
+
+    def watchdog(self):
+        while self.running:
+            time.sleep(0.5)
+            re = self.sched.check_timeouts()
+            if re:
+                self.metrics.inc("redispatched_chunks", len(re))
+                self.log(f"timeout: re-dispatching {len(re)} chunk(s)")
+
+
+def main(argv: Optional[List[str]] = None):
+    """`python server.py [ip]` then `quit` on stdin (server.py:165-175)."""
+    import sys
+    argv = list(sys.argv[1:] if argv is None else argv)
+    cfg = Config.from_argv(argv, positional=("server_ip",))
+    c = coordinator(cfg.server_ip, cfg)
+    while True:
+        try:
+            a = input("\nEnter quit to exit\n")
+        except EOFError:
+            a = "quit"
+        if a == "quit":
+            c.exit_threads()
+            print("done.", flush=True)
+            break

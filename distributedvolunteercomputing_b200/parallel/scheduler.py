@@ -1,0 +1,355 @@
+"""PyTorch-level scheduler: membership table with epochs, in-flight table, dispatch policies,
+re-dispatch on leave / timeout.  Replaces the reference server's distribution and management
+loop (server.py:77-91 `send_request`, server.py:93-158 `manager`).
+
+What it keeps from the reference:
+  * workers join and leave at will; a client that becomes a requester leaves the worker pool
+    and returns on `stop` (server.py:126-139);
+  * round-robin over all *other* clients with one global counter is available as a policy
+    (server.py:84-90);
+  * several requesters share the pool (server.py:56,81).
+What it fixes (SURVEY.md Appendix C #5,7,8,9): work is queued (not dropped) while no worker
+is eligible, join is idempotent, batches owned by a worker that leaves or goes silent are
+re-dispatched, duplicates are harmless (results are de-duplicated by batch id), and dispatch
+defaults to least-loaded with per-requester fair share.
+
+Decisions are per *batch* (>= tens of frames), never per frame, so the Python layer stays off
+the per-frame path.  Thread-safe; no torch dependency so it is unit-testable with fake workers.
+"""
+from __future__ import annotations
+
+import collections
+import itertools
+import threading
+import time
+from dataclasses import dataclass, field
+from typing import Any, Callable, Deque, Dict, Iterable, List, Optional, Tuple
+
+
+@dataclass
+class WorkerInfo:
+    addr: str
+    joined_epoch: int
+    role: str = "worker"          # "worker" | "requester"
+    alive: bool = True
+    inflight: int = 0
+    completed: int = 0
+    capacity: int = 2             # batches it may hold at once (credit-based flow control)
+    last_seen: float = 0.0
+    meta: Dict[str, Any] = field(default_factory=dict)
+
+
+@dataclass
+class Batch:
+    batch_id: int
+    requester: str
+    frame_ids: Tuple[int, ...]
+    payload: Any = None           # opaque to the scheduler (device-ring slots, a packed chunk, ...)
+    attempts: int = 0
+
+
+@dataclass
+class InFlight:
+    batch: Batch
+    worker: str
+    epoch: int
+    t_dispatch: float
+
+
+class Membership:
+    """Membership table. Every change bumps `epoch`; dispatches carry the epoch they were made in."""
+
+    def __init__(self):
+        self.lock = threading.RLock()
+        self.epoch = 0
+        self.workers: Dict[str, WorkerInfo] = {}
+
+    def join(self, addr: str, capacity: int = 2, now: Optional[float] = None, **meta) -> Tuple[WorkerInfo, bool]:
+        """Idempotent: a repeated join (lost reply, worker.py:50-58 retry) returns the existing entry."""
+        with self.lock:
+            w = self.workers.get(addr)
+            if w is not None and w.alive:
+                w.last_seen = time.monotonic() if now is None else now
+                return w, False
+            self.epoch += 1
+            w = WorkerInfo(addr, self.epoch, capacity=capacity, last_seen=time.monotonic() if now is None else now, meta=dict(meta))
+            self.workers[addr] = w
+            return w, True
+
+    def leave(self, addr: str) -> bool:
+        with self.lock:
+            w = self.workers.get(addr)
+            if w is None or not w.alive:
+                return False
+            w.alive = False
+            self.epoch += 1
+            return True
+
+    def set_role(self, addr: str, role: str) -> bool:
+        with self.lock:
+            w = self.workers.get(addr)
+            if w is None or not w.alive:
+                return False
+            if w.role != role:
+                w.role = role
+                self.epoch += 1
+            return True
+
+    def touch(self, addr: str, now: Optional[float] = None):
+        with self.lock:
+            w = self.workers.get(addr)
+            if w is not None:
+                w.last_seen = time.monotonic() if now is None else now
+
+    def alive(self) -> List[WorkerInfo]:
+        with self.lock:
+            return [w for w in self.workers.values() if w.alive]
+
+    def eligible(self, requester: str, requester_works: bool = False) -> List[WorkerInfo]:
+        """Workers that may take a batch of `requester`: alive, in the worker role, and not the
+        requester itself (server.py:84-87) unless `requester_works`."""
+        with self.lock:
+            out = []
+            for w in self.workers.values():
+                if not w.alive:
+                    continue
+                if w.addr == requester:
+                    if requester_works:
+                        out.append(w)
+                    continue
+                if w.role == "worker":
+                    out.append(w)
+            return out
+
+
+class Scheduler:
+    def __init__(self, policy: str = "least_loaded", requester_works: bool = False, worker_timeout_s: float = 10.0,
+                 max_attempts: int = 8, clock: Callable[[], float] = time.monotonic):
+        assert policy in ("least_loaded", "round_robin")
+        self.policy = policy
+        self.requester_works = requester_works
+        self.worker_timeout_s = worker_timeout_s
+        self.max_attempts = max_attempts
+        self.clock = clock
+        self.members = Membership()
+        self.lock = threading.RLock()
+        self.cv = threading.Condition(self.lock)
+        self._ids = itertools.count(1)
+        self.queues: "collections.OrderedDict[str, Deque[Batch]]" = collections.OrderedDict()
+        self.inflight: Dict[int, InFlight] = {}
+        self.done: Dict[str, set] = collections.defaultdict(set)      # requester -> completed batch ids
+        self._rr = 0            # the reference's single global round-robin counter (server.py:78,89-90)
+        self._last_req = None   # requester rotation for fair share
+        self.stats = collections.Counter()
+
+    # ------------------------------------------------------------------ membership facade
+    def join(self, addr: str, **kw):
+        w, new = self.members.join(addr, now=self.clock(), **kw)
+        with self.cv:
+            self.cv.notify_all()
+        return w, new
+
+    def leave(self, addr: str) -> List[Batch]:
+        """A worker leaves (voluntarily or declared dead): its in-flight batches go back to the
+        FRONT of their requesters' queues. Returns the re-queued batches."""
+        self.members.leave(addr)
+        return self._requeue_where(lambda f: f.worker == addr, reason="leave")
+
+    def become_requester(self, addr: str) -> bool:
+        ok = self.members.set_role(addr, "requester")
+        with self.lock:
+            self.queues.setdefault(addr, collections.deque())
+        if ok and not self.requester_works:
+            # it stops being a worker: anything it still owns for other requesters is re-dispatched
+            self._requeue_where(lambda f: f.worker == addr and f.batch.requester != addr, reason="role")
+        return ok
+
+    def stop_requesting(self, addr: str) -> bool:
+        ok = self.members.set_role(addr, "worker")
+        with self.cv:
+            self.cv.notify_all()
+        return ok
+
+    # ------------------------------------------------------------------ work intake
+    def submit(self, requester: str, frame_ids: Iterable[int], payload: Any = None) -> Batch:
+        b = Batch(next(self._ids), requester, tuple(frame_ids), payload)
+        with self.cv:
+            self.queues.setdefault(requester, collections.deque()).append(b)
+            self.stats["submitted"] += 1
+            self.cv.notify_all()
+        return b
+
+    def pending(self, requester: Optional[str] = None) -> int:
+        with self.lock:
+            if requester is not None:
+                return len(self.queues.get(requester, ()))
+            return sum(len(q) for q in self.queues.values())
+
+    def outstanding(self, requester: Optional[str] = None) -> int:
+        with self.lock:
+            n = self.pending(requester)
+            n += sum(1 for f in self.inflight.values() if requester is None or f.batch.requester == requester)
+            return n
+
+    # ------------------------------------------------------------------ dispatch
+    def _pick_worker(self, requester: str) -> Optional[WorkerInfo]:
+        cands = [w for w in self.members.eligible(requester, self.requester_works) if w.inflight < w.capacity]
+        if not cands:
+            return None
+        if self.policy == "round_robin":
+            allw = self.members.eligible(requester, self.requester_works)
+            # reference semantics: clients[iterations % len(clients)], counter advanced per dispatch
+            for k in range(len(allw)):
+                w = allw[(self._rr + k) % len(allw)]
+                if w.inflight < w.capacity:
+                    self._rr += k + 1
+                    return w
+            return None
+        return min(cands, key=lambda w: (w.inflight / max(1, w.capacity), w.completed, w.addr))
+
+    def next_dispatch(self) -> Optional[Tuple[Batch, WorkerInfo, int]]:
+        """Pick (batch, worker, epoch) or None if nothing can be dispatched right now.
+        Requesters are served round-robin (fair share); each requester's queue is FIFO."""
+        with self.lock:
+            order = list(self.queues.keys())
+            if not order:
+                return None
+            # rotate so the requester after the last one served goes first
+            start = (order.index(self._last_req) + 1) % len(order) if self._last_req in self.queues else 0
+            for k in range(len(order)):
+                r = order[(start + k) % len(order)]
+                if not self.queues[r]:
+                    continue
+                w = self._pick_worker(r)
+                if w is None:
+                    continue
+                b = self.queues[r].popleft()
+                b.attempts += 1
+                w.inflight += 1
+                ep = self.members.epoch
+                self.inflight[b.batch_id] = InFlight(b, w.addr, ep, self.clock())
+                self._last_req = r
+                self.stats["dispatched"] += 1
+                return b, w, ep
+            return None
+
+    def wait_dispatch(self, timeout: Optional[float] = None) -> Optional[Tuple[Batch, WorkerInfo, int]]:
+        """Blocking variant: sleeps on a condition variable (the reference busy-spins, server.py:79-80)."""
+        deadline = None if timeout is None else self.clock() + timeout
+        with self.cv:
+            while True:
+                d = self.next_dispatch()
+                if d is not None:
+                    return d
+                remaining = None if deadline is None else deadline - self.clock()
+                if remaining is not None and remaining <= 0:
+                    return None
+                self.cv.wait(0.05 if remaining is None else min(0.05, remaining))
+
+    # ------------------------------------------------------------------ completion / failure
+    def complete(self, batch_id: int, worker: Optional[str] = None) -> Optional[Batch]:
+        """Record a result. Returns the batch the first time, None for duplicates / unknown ids
+        (a re-dispatched batch may legitimately finish twice)."""
+        with self.cv:
+            f = self.inflight.get(batch_id)
+            if f is None:
+                self.stats["duplicate_results"] += 1
+                return None
+            if worker is not None and worker != f.worker:
+                # a stale owner finished a batch that was already handed to someone else: accept the
+                # result (it is the same data) and release the current owner's credit
+                self.stats["stale_owner_results"] += 1
+            del self.inflight[batch_id]
+            w = self.members.workers.get(f.worker)
+            if w is not None:
+                w.inflight = max(0, w.inflight - 1)
+                w.completed += 1
+                w.last_seen = self.clock()
+            self.done[f.batch.requester].add(batch_id)
+            self.stats["completed"] += 1
+            self.cv.notify_all()
+            return f.batch
+
+    def fail(self, batch_id: int, reason: str = "error") -> Optional[Batch]:
+        """Explicit failure report (e.g. a send timed out): re-queue at the front."""
+        out = self._requeue_where(lambda f: f.batch.batch_id == batch_id, reason=reason)
+        return out[0] if out else None
+
+    def check_timeouts(self, now: Optional[float] = None) -> List[Batch]:
+        """Re-dispatch batches whose owner has been silent for `worker_timeout_s`; the owner is
+        marked dead (it can re-join at will)."""
+        now = self.clock() if now is None else now
+        with self.lock:
+            dead = set()
+            for f in self.inflight.values():
+                if now - f.t_dispatch > self.worker_timeout_s:
+                    w = self.members.workers.get(f.worker)
+                    if w is None or now - w.last_seen > self.worker_timeout_s:
+                        dead.add(f.worker)
+        out: List[Batch] = []
+        for addr in dead:
+            self.stats["timeouts"] += 1
+            out.extend(self.leave(addr))
+        return out
+
+    def _requeue_where(self, pred, reason: str) -> List[Batch]:
+        with self.cv:
+            hit = [f for f in self.inflight.values() if pred(f)]
+            hit.sort(key=lambda f: f.batch.batch_id, reverse=True)   # appendleft in reverse keeps FIFO order
+            out = []
+            for f in hit:
+                del self.inflight[f.batch.batch_id]
+                w = self.members.workers.get(f.worker)
+                if w is not None:
+                    w.inflight = max(0, w.inflight - 1)
+                if f.batch.attempts >= self.max_attempts:
+                    self.stats["dropped_after_max_attempts"] += 1
+                    continue
+                self.queues.setdefault(f.batch.requester, collections.deque()).appendleft(f.batch)
+                self.stats["redispatched"] += 1
+                self.stats["redispatched_" + reason] += 1
+                out.append(f.batch)
+            if out:
+                self.cv.notify_all()
+            return list(reversed(out))
+
+    def drop_requester(self, requester: str):
+        with self.lock:
+            self.queues.pop(requester, None)
+            for bid in [bid for bid, f in self.inflight.items() if f.batch.requester == requester]:
+                f = self.inflight.pop(bid)
+                w = self.members.workers.get(f.worker)
+                if w is not None:
+                    w.inflight = max(0, w.inflight - 1)
+            self.done.pop(requester, None)
+
+    def snapshot(self) -> Dict[str, Any]:
+        with self.lock:
+            return {"epoch": self.members.epoch,
+                    "workers": {w.addr: dict(role=w.role, alive=w.alive, inflight=w.inflight, completed=w.completed)
+                                for w in self.members.workers.values()},
+                    "pending": self.pending(), "inflight": len(self.inflight), "stats": dict(self.stats)}
+
+
+class ReorderBuffer:
+    """In-order reassembly by frame number with de-duplication (replaces the O(n^2) list scan of
+    worker.py:214-239).  `push` returns the frames that became contiguous."""
+
+    def __init__(self, first: int = 1):
+        self.next = first
+        self.held: Dict[int, Any] = {}
+        self.duplicates = 0
+
+    def push(self, n: int, item: Any) -> List[Tuple[int, Any]]:
+        if n < self.next or n in self.held:
+            self.duplicates += 1
+            return []
+        self.held[n] = item
+        out = []
+        while self.next in self.held:
+            out.append((self.next, self.held.pop(self.next)))
+            self.next += 1
+        return out
+
+    def __len__(self):
+        return len(self.held)

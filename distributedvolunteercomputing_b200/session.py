@@ -1,0 +1,150 @@
+"""Requester sessions: frame sources, in-order writer, the job timer line.
+
+Reference: `client.requester` (worker.py:82-129) reads frames with cv2.VideoCapture, numbers
+them from 1, and the `processed` branch of `client.worker` (worker.py:210-239) writes them in
+order to video<N>.mp4 (mp4v, 30 fps, 400 x int(h*400/w)) and prints
+``final frame time taken for the job = <s>`` when the last frame lands.
+
+Fixes vs the reference (SURVEY.md Appendix C #3,#4): every frame is processed (frame 0 is not
+thrown away unless `compat_drop_first`), and the tail that does not fill a chunk is flushed
+unless `compat_drop_tail`.
+"""
+from __future__ import annotations
+
+import os
+import time
+from typing import Iterator, List, Optional, Tuple
+
+import numpy as np
+
+from .config import Config
+from .models.preprocess import out_size_400
+from .parallel.scheduler import ReorderBuffer
+
+try:
+    import cv2
+except Exception:  # pragma: no cover
+    cv2 = None
+
+
+class FrameSource:
+    """Iterator of BGR uint8 frames. `path` may be a video file, ``live`` (headless: a synthetic
+    camera, there is no capture device or window system on the box) or ``synthetic:N:HxW``."""
+
+    def __init__(self, path: str, max_frames: Optional[int] = None):
+        self.path = path
+        self.max_frames = max_frames
+        self.cap = None
+        self.synthetic = None
+        if path == "live" or path.startswith("synthetic"):
+            n, h, w = (max_frames or 300), 480, 640
+            if path.startswith("synthetic:"):
+                parts = path.split(":")
+                n = int(parts[1]) if len(parts) > 1 and parts[1] else n
+                if len(parts) > 2 and "x" in parts[2]:
+                    h, w = (int(v) for v in parts[2].split("x"))
+            self.synthetic = (n, h, w)
+        else:
+            if cv2 is None:
+                raise RuntimeError("cv2 is required to read video files")
+            self.cap = cv2.VideoCapture(path)
+            if not self.cap.isOpened():
+                raise FileNotFoundError(path)
+
+    def __iter__(self) -> Iterator[np.ndarray]:
+        count = 0
+        if self.synthetic is not None:
+            n, h, w = self.synthetic
+            rng = np.random.default_rng(1234)
+            base = rng.integers(0, 256, (h // 8 + 1, w // 8 + 1, 3), dtype=np.uint8)
+            base = np.repeat(np.repeat(base, 8, axis=0), 8, axis=1)[:h, :w]
+            for i in range(n):
+                yield np.roll(base, shift=(i * 3) % w, axis=1).copy()
+            return
+        while True:
+            ok, frame = self.cap.read()
+            if not ok:
+                break
+            yield frame
+            count += 1
+            if self.max_frames is not None and count >= self.max_frames:
+                break
+
+    def release(self):
+        if self.cap is not None:
+            self.cap.release()
+
+
+def write_synthetic_video(path: str, n_frames: int, h: int = 480, w: int = 640, fps: int = 30, seed: int = 0) -> str:
+    """A small moving-blocks mp4 for tests and benchmarks (no sample video ships with the reference)."""
+    rng = np.random.default_rng(seed)
+    vw = cv2.VideoWriter(path, cv2.VideoWriter_fourcc(*"mp4v"), fps, (w, h))
+    base = rng.integers(0, 256, (h // 16 + 1, w // 16 + 1, 3), dtype=np.uint8)
+    base = cv2.resize(base, (w, h), interpolation=cv2.INTER_CUBIC)
+    for i in range(n_frames):
+        f = np.roll(base, (i * 5) % w, axis=1).copy()
+        cv2.rectangle(f, (20 + (i * 7) % (w - 120), 40), (100 + (i * 7) % (w - 120), 200), (200, 180, 160), -1)
+        vw.write(f)
+    vw.release()
+    return path
+
+
+class VideoSink:
+    """video<N>.mp4 writer: mp4v, 30 fps, (400, int(h*400/w)) (worker.py:86,90,108-110)."""
+
+    _counter = 0
+
+    def __init__(self, cfg: Config, src_h: int, src_w: int, directory: str = ".", index: Optional[int] = None):
+        if index is None:
+            index = VideoSink._counter
+            VideoSink._counter += 1
+        self.path = os.path.join(directory, f"video{index}.mp4")
+        self.h, self.w = out_size_400(src_h, src_w, cfg.out_width)
+        self.writer = cv2.VideoWriter(self.path, cv2.VideoWriter_fourcc(*"mp4v"), cfg.writer_fps, (self.w, self.h))
+        self.frames_written = 0
+
+    def write(self, frame: np.ndarray):
+        self.writer.write(np.ascontiguousarray(frame))
+        self.frames_written += 1
+
+    def release(self):
+        if self.writer is not None:
+            self.writer.release()
+            self.writer = None
+
+
+class JobTracker:
+    """Reorders processed frames, writes them, and reports the job time exactly like the
+    reference prints it."""
+
+    def __init__(self, sink: Optional[VideoSink], first_frame: int = 1, out=print):
+        self.sink = sink
+        self.reorder = ReorderBuffer(first_frame)
+        self.final_sent_frame: Optional[int] = None
+        self.start_time = time.time()
+        self.finished = False
+        self.job_seconds: Optional[float] = None
+        self.out = out
+        self.counts: List[int] = []
+
+    def set_final(self, n: int):
+        self.final_sent_frame = n
+        self._maybe_finish()
+
+    def push(self, n: int, frame: np.ndarray, count: Optional[int] = None):
+        for k, item in self.reorder.push(n, (frame, count)):
+            if self.sink is not None:
+                self.sink.write(item[0])
+            if item[1] is not None:
+                self.counts.append(item[1])
+        self._maybe_finish()
+
+    def _maybe_finish(self):
+        if self.finished or self.final_sent_frame is None:
+            return
+        if self.reorder.next - 1 >= self.final_sent_frame:
+            self.finished = True
+            self.job_seconds = time.time() - self.start_time
+            self.out("final frame time taken for the job = " + str(self.job_seconds))
+            if self.sink is not None:
+                self.sink.release()
