@@ -38,6 +38,11 @@ static inline long long ceil_div64(long long a, long long b) { return (a + b - 1
 int make_tmap_2d_f16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                      uint32_t box_rows, uint32_t box_cols);
 
+// 4-D NHWC fp16 activation tensor [N, H, W, C] as a TMA descriptor with a {box_c, box_w, box_h, 1}
+// box, no swizzle; out-of-range coordinates (the conv padding halo) read as zeros.
+int make_tmap_nhwc_f16(CUtensorMap* out, const void* base, uint64_t n, uint64_t h, uint64_t w, uint64_t c,
+                       uint32_t box_c, uint32_t box_w, uint32_t box_h);
+
 // ---------------------------------------------------------------------------------- PTX
 #ifdef __CUDACC__
 
@@ -88,6 +93,34 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* t
       ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+// Mixed-precision FMA pair: acc0 += lo(x)*lo(w), acc1 += hi(x)*hi(w) with fp16 inputs and fp32
+// accumulators (single FHFMA each on sm_100a; no separate convert instructions).
+__device__ __forceinline__ void fhfma2(float& acc0, float& acc1, uint32_t x, uint32_t w) {
+  asm("{\n\t.reg .b16 xl, xh, wl, wh;\n\t"
+      "mov.b32 {xl, xh}, %2;\n\t"
+      "mov.b32 {wl, wh}, %3;\n\t"
+      "fma.rn.f32.f16 %0, xl, wl, %0;\n\t"
+      "fma.rn.f32.f16 %1, xh, wh, %1;\n\t}\n"
+      : "+f"(acc0), "+f"(acc1)
+      : "r"(x), "r"(w));
+}
+// TMA 2-D tile store shared -> global (bulk async group); rows/cols outside the tensor are clipped.
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tmap, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(tmap), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }
@@ -153,6 +186,15 @@ __device__ __forceinline__ uint32_t umma_idesc_f16(uint32_t m, uint32_t n) {
          | ((m >> 4) << 24);  // M >> 4
 }
 
+// ---- explicit shared-memory vector access (keeps LDS/STS even when the pointer's address space is opaque)
+__device__ __forceinline__ uint4 lds_v4(uint32_t saddr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(saddr));
+  return r;
+}
+__device__ __forceinline__ void sts_v4(uint32_t saddr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 // ---- vector / cache-hinted global access
 __device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
   uint4 r;

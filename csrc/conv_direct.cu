@@ -94,8 +94,8 @@ dw3x3_kernel(const __half* __restrict__ in, int B, int H, int W, int C, int Ho, 
   }
 }
 
-int dwconv_launch(const void* in, int B, int H, int W, int C, int stride, const float* w, const float* b, int relu,
-                  void* out, cudaStream_t st) {
+int dwconv_launch_direct(const void* in, int B, int H, int W, int C, int stride, const float* w, const float* b, int relu,
+                         void* out, cudaStream_t st) {
   DVC_REQUIRE(C % 8 == 0 && (stride == 1 || stride == 2), "dwconv: C=%d must be a multiple of 8, stride=%d in {1,2}", C, stride);
   DVC_REQUIRE(B > 0 && H > 0 && W > 0, "dwconv: bad shape");
   const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
@@ -108,6 +108,159 @@ int dwconv_launch(const void* in, int B, int H, int W, int C, int stride, const 
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
+}
+
+// ---- TMA-fed depthwise: one CTA per (image, spatial tile, 64-channel chunk).  A single 4-D TMA box
+// load brings the input tile plus its halo into shared memory (out-of-range coordinates read as
+// zeros, so the pad-1 border costs nothing); the loads of several co-resident CTAs overlap each
+// other's math.  Each thread owns 8 channels and walks the tile's pixels: 9 x LDS.128 and 72
+// FHFMA (fp16 x fp16 + fp32) per output vector, no convert instructions.
+struct DwArgs {
+  int B, H, W, C, Ho, Wo;
+  int CT, TX, TY, BW, BH, tiles_x, tiles_y, cchunks;
+  const float* w;
+  const float* bias;
+  int relu;
+  __half* out;
+};
+
+template <int STRIDE>
+__global__ void __launch_bounds__(256) dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tm, const DwArgs a) {
+  extern __shared__ uint8_t dw_smem_raw[];
+  uint8_t* tile = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dw_smem_raw) + 127) & ~uintptr_t(127));
+  __shared__ uint64_t bar;
+  const int tid = threadIdx.x;
+  int bid = blockIdx.x;
+  const int cc = bid % a.cchunks; bid /= a.cchunks;
+  const int tx = bid % a.tiles_x; bid /= a.tiles_x;
+  const int ty = bid % a.tiles_y;
+  const int n = bid / a.tiles_y;
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    mbar_arrive_expect_tx(&bar, (uint32_t)(a.BH * a.BW * a.CT * 2));
+    tma_load_4d(tile, &tm, &bar, cc * a.CT, tx * a.TX * STRIDE - 1, ty * a.TY * STRIDE - 1, n);
+  }
+  const int cgs = a.CT >> 3;
+  const int cg = tid % cgs, pt = tid / cgs, pxt = 256 / cgs;
+  const int c0 = cc * a.CT + cg * 8;
+  // weights of this thread's 8 channels as packed fp16 pairs, bias as fp32 (overlaps the TMA flight)
+  uint32_t wq[9][4];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.w + (size_t)t * a.C + c0));
+    const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.w + (size_t)t * a.C + c0 + 4));
+    wq[t][0] = pack_half2(w0.x, w0.y); wq[t][1] = pack_half2(w0.z, w0.w);
+    wq[t][2] = pack_half2(w1.x, w1.y); wq[t][3] = pack_half2(w1.z, w1.w);
+  }
+  const float4 b0 = __ldg(reinterpret_cast<const float4*>(a.bias + c0));
+  const float4 b1 = __ldg(reinterpret_cast<const float4*>(a.bias + c0 + 4));
+  mbar_wait(&bar, 0);
+  const uint32_t tile_s = smem_u32(tile) + (uint32_t)(cg * 16);
+  const int npix = a.TX * a.TY;
+  for (int p = pt; p < npix; p += pxt) {
+    const int oy = p / a.TX, ox = p - oy * a.TX;
+    const int gx = tx * a.TX + ox, gy = ty * a.TY + oy;
+    if (gx >= a.Wo || gy >= a.Ho) continue;
+    float acc[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const uint4 v = lds_v4(tile_s + (uint32_t)(((oy * STRIDE + ky) * a.BW + ox * STRIDE + kx) * a.CT * 2));
+        const int t = ky * 3 + kx;
+        fhfma2(acc[0], acc[1], v.x, wq[t][0]);
+        fhfma2(acc[2], acc[3], v.y, wq[t][1]);
+        fhfma2(acc[4], acc[5], v.z, wq[t][2]);
+        fhfma2(acc[6], acc[7], v.w, wq[t][3]);
+      }
+    }
+    if (a.relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
+    }
+    *reinterpret_cast<uint4*>(a.out + (((size_t)n * a.Ho + gy) * a.Wo + gx) * a.C + c0) =
+        make_uint4(pack_half2(acc[0], acc[1]), pack_half2(acc[2], acc[3]), pack_half2(acc[4], acc[5]), pack_half2(acc[6], acc[7]));
+  }
+}
+
+struct DwLaunch {
+  CUtensorMap tm;
+  DwArgs args;
+  int grid, smem, stride;
+  bool tma;
+  const void* in;
+};
+
+constexpr int DW_SMEM_LIMIT = 56 * 1024;
+
+int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stride, const float* w, const float* b, int relu,
+               void* out) {
+  DVC_REQUIRE(C % 8 == 0 && (stride == 1 || stride == 2), "dwconv: C=%d must be a multiple of 8, stride=%d in {1,2}", C, stride);
+  DVC_REQUIRE(B > 0 && H > 0 && W > 0, "dwconv: bad shape");
+  DVC_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0, "dwconv: unaligned tensors");
+  DwArgs& a = L->args;
+  a.B = B; a.H = H; a.W = W; a.C = C; a.w = w; a.bias = b; a.relu = relu; a.out = reinterpret_cast<__half*>(out);
+  a.Ho = (H + 2 - 3) / stride + 1; a.Wo = (W + 2 - 3) / stride + 1;
+  L->stride = stride; L->in = in;
+  a.CT = C % 64 == 0 ? 64 : (C % 32 == 0 ? 32 : (C % 16 == 0 ? 16 : 8));
+  a.cchunks = C / a.CT;
+  // tile search: minimise (input pixels fetched incl. halo + output pixels covered incl. edge waste)
+  double best = 1e30;
+  int bx = 0, by = 0;
+  for (int TY = 1; TY <= (a.Ho < 64 ? a.Ho : 64); ++TY) {
+    for (int TX = 1; TX <= (a.Wo < 64 ? a.Wo : 64); ++TX) {
+      const int outs = TX * TY;
+      if (outs > 1024) continue;
+      if (outs < 96 && (TX < a.Wo || TY < a.Ho)) continue;
+      const int BW = (TX - 1) * stride + 3, BH = (TY - 1) * stride + 3;
+      if (BW > 256 || BH > 256 || BW * BH * a.CT * 2 > DW_SMEM_LIMIT) continue;
+      const int ntx = ceil_div(a.Wo, TX), nty = ceil_div(a.Ho, TY);
+      const double cost = (double)ntx * nty * BW * BH / ((double)H * W) + 1.5 * (double)ntx * TX * nty * TY / ((double)a.Wo * a.Ho)
+                          + 0.02 * (256.0 / outs);
+      if (cost < best) { best = cost; bx = TX; by = TY; }
+    }
+  }
+  DVC_REQUIRE(bx > 0, "dwconv: no tile fits shared memory (W=%d H=%d C=%d)", W, H, C);
+  a.TX = bx; a.TY = by;
+  a.BW = (bx - 1) * stride + 3; a.BH = (by - 1) * stride + 3;
+  a.tiles_x = ceil_div(a.Wo, bx); a.tiles_y = ceil_div(a.Ho, by);
+  const long long grid = (long long)B * a.tiles_y * a.tiles_x * a.cchunks;
+  DVC_REQUIRE(grid < (1LL << 31), "dwconv: grid too large");
+  L->grid = (int)grid;
+  L->smem = a.BW * a.BH * a.CT * 2 + 128;
+  L->tma = true;
+  return make_tmap_nhwc_f16(&L->tm, in, (uint64_t)B, (uint64_t)H, (uint64_t)W, (uint64_t)C, (uint32_t)a.CT, (uint32_t)a.BW, (uint32_t)a.BH);
+}
+
+int dw_launch(const DwLaunch* L, cudaStream_t st) {
+  static bool attr_set[64] = {};
+  int dev = 0;
+  DVC_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
+    attr_set[dev & 63] = true;
+  }
+  if (L->stride == 1) dw3x3_tma_kernel<1><<<L->grid, 256, L->smem, st>>>(L->tm, L->args);
+  else dw3x3_tma_kernel<2><<<L->grid, 256, L->smem, st>>>(L->tm, L->args);
+  count_launch();
+  DVC_CHECK_CUDA(cudaGetLastError());
+  return DVC_OK;
+}
+
+DwLaunch* dw_alloc() { return new DwLaunch(); }
+void dw_free(DwLaunch* L) { delete L; }
+
+int dwconv_launch(const void* in, int B, int H, int W, int C, int stride, const float* w, const float* b, int relu, void* out,
+                  cudaStream_t st) {
+  DwLaunch L;
+  int rc = dw_prepare(&L, in, B, H, W, C, stride, w, b, relu, out);
+  if (rc) return rc;
+  return dw_launch(&L, st);
 }
 
 // ---- im2col for the dense 3x3 stride-2 pad-1 extras (conv14_2 .. conv17_2, prototxt:922-1146)
@@ -146,6 +299,11 @@ int im2col_launch(const void* in, int B, int H, int W, int C, void* out, cudaStr
 extern "C" int dvc_dwconv3x3(const void* in_f16, int B, int H, int W, int C, int stride, const float* w, const float* b,
                              int relu, void* out_f16, void* stream) {
   return dvc::dwconv_launch(in_f16, B, H, W, C, stride, w, b, relu, out_f16, (cudaStream_t)stream);
+}
+/* Reference variant without TMA (register sliding window, plain loads); kept for A/B measurements. */
+extern "C" int dvc_dwconv3x3_direct(const void* in_f16, int B, int H, int W, int C, int stride, const float* w, const float* b,
+                                    int relu, void* out_f16, void* stream) {
+  return dvc::dwconv_launch_direct(in_f16, B, H, W, C, stride, w, b, relu, out_f16, (cudaStream_t)stream);
 }
 extern "C" int dvc_im2col3x3s2(const void* in_f16, int B, int H, int W, int C, void* out_f16, void* stream) {
   return dvc::im2col_launch(in_f16, B, H, W, C, out_f16, (cudaStream_t)stream);

@@ -4,13 +4,19 @@
 //
 // A is the NHWC fp16 activation matrix (M = batch * H * W pixels, K = Cin), Wt the
 // [Cout, Cin] weights; both are K-major, so both operands are TMA-loaded as 128-byte
-// swizzled tiles and consumed by tcgen05.mma straight from shared memory.  The fp32
-// accumulator tile (128 x block_n) lives in TMEM and is drained by four epilogue warps
-// with tcgen05.ld -> bias -> ReLU -> fp16 NHWC store (or the SSD loc/conf split store,
-// which makes Permute/Flatten/Concat of prototxt:1172-1192,1817-1844 free).
+// swizzled tiles and consumed by tcgen05.mma straight from shared memory.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer
-// (one elected lane), warps 2..5 = epilogue (TMEM lane quadrant = warp % 4).
+// Persistent, warp-specialised (192 threads, one CTA per SM, tiles strided by gridDim):
+//   warp 0      TMA producer: runs ahead across tiles through a ring of smem stages
+//   warp 1      TMEM allocator + MMA issuer (one elected lane); two accumulator buffers in
+//               TMEM so tile i+1 is multiplied while tile i is drained
+//   warps 2..5  epilogue: tcgen05.ld -> +bias -> ReLU -> fp16 -> swizzled smem staging ->
+//               TMA store (asynchronous, coalesced NHWC rows, M tail clipped by the tensor map);
+//               SSD heads instead split-store fp32 loc/conf rows at their concat offsets, which
+//               makes Permute/Flatten/Concat of prototxt:1172-1192,1817-1844 free.
+// These layers have K = 32..1024: most are bandwidth-bound, so what matters is keeping loads
+// and stores of several tiles in flight per SM, which is what the producer run-ahead and the
+// bulk-async stores are for.
 // Reference op: cv2.dnn Convolution layers, prototxt:76-106 ... 1083-1113, 1147-1775.
 #include "common.cuh"
 
@@ -19,42 +25,50 @@ namespace dvc {
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int GEMM_THREADS = 192;
-constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
+constexpr int A_STAGE_BYTES = BM * BK * 2;       // 16 KiB
 constexpr int GEMM_MAX_SMEM = 227 * 1024;
+constexpr int EPI_CHUNK = 64;                    // columns per staging buffer (128 B of fp16 per row)
+constexpr int EPI_BUF_BYTES = 32 * EPI_CHUNK * 2;   // one warp, 32 rows x 128 B
+constexpr int EPI_SMEM = 4 * 2 * EPI_BUF_BYTES;  // 4 warps x 2 buffers
+constexpr int BIAS_SMEM = 4 * 256 * 4;           // per-epilogue-warp bias slice (block_n <= 256)
 
 struct GemmArgs {
   int M, N, K;
-  int block_n, n_tiles;
+  int block_n, n_tiles, num_tiles;
   int num_kb, stages;
   int tmem_cols;
   const float* bias;
-  int out_mode;
+  int out_mode;        // 0: fp16 [M, ldc]   1: SSD head split store (fp32)
+  int tma_store;       // out_mode 0 only: epilogue goes through smem + TMA store
   __half* out;
   int ldc;
   int relu;
   dvc_head_out head;
 };
 
-__global__ void __launch_bounds__(GEMM_THREADS)
-gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmC, const GemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = __shfl_sync(0xffffffff, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
-  const int n_tile = blockIdx.x % g.n_tiles;
-  const int m_tile = blockIdx.x / g.n_tiles;
   const int b_stage_bytes = g.block_n * BK * 2;
 
-  uint8_t* sA = smem;
-  uint8_t* sB = smem + g.stages * A_STAGE_BYTES;
+  uint8_t* sEpi = smem;                                   // [4 warps][2][32 rows x 128 B], 1024-aligned
+  float* sBias = reinterpret_cast<float*>(smem + EPI_SMEM);
+  uint8_t* sA = smem + EPI_SMEM + BIAS_SMEM;
+  uint8_t* sB = sA + g.stages * A_STAGE_BYTES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + g.stages * b_stage_bytes);
   uint64_t* empty_bar = full_bar + g.stages;
-  uint64_t* tmem_full_bar = empty_bar + g.stages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint64_t* tmem_full_bar = empty_bar + g.stages;         // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;           // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (g.tma_store) tma_prefetch_desc(&tmC);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -62,7 +76,10 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         mbar_init(&full_bar[s], 1);
         mbar_init(&empty_bar[s], 1);
       }
-      mbar_init(tmem_full_bar, 1);
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tmem_full_bar[a], 1);
+        mbar_init(&tmem_empty_bar[a], 4);     // one arrive per epilogue warp
+      }
       fence_mbar_init();
     }
     __syncwarp();
@@ -78,13 +95,17 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ------------------------------------------------------------- TMA producer
     if (elect_one()) {
       const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + b_stage_bytes);
-      for (int kb = 0; kb < g.num_kb; ++kb) {
-        const int s = kb % g.stages;
-        const uint32_t ph = (uint32_t)(kb / g.stages) & 1u;
-        mbar_wait(&empty_bar[s], ph ^ 1u);
-        mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-        tma_load_2d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], kb * BK, m_tile * BM);
-        tma_load_2d(sB + s * b_stage_bytes, &tmB, &full_bar[s], kb * BK, n_tile * g.block_n);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+        const int n_tile = tile % g.n_tiles, m_tile = tile / g.n_tiles;
+        for (int kb = 0; kb < g.num_kb; ++kb, ++it) {
+          const int s = it % g.stages;
+          const uint32_t ph = (uint32_t)(it / g.stages) & 1u;
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+          tma_load_2d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], kb * BK, m_tile * BM);
+          tma_load_2d(sB + s * b_stage_bytes, &tmB, &full_bar[s], kb * BK, n_tile * g.block_n);
+        }
       }
     }
     __syncwarp();
@@ -92,81 +113,129 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ------------------------------------------------------------- MMA issuer
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_f16(BM, (uint32_t)g.block_n);
-      for (int kb = 0; kb < g.num_kb; ++kb) {
-        const int s = kb % g.stages;
-        const uint32_t ph = (uint32_t)(kb / g.stages) & 1u;
-        mbar_wait(&full_bar[s], ph);
+      int it = 0, t = 0;
+      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++t) {
+        const int acc = t & 1;
+        mbar_wait(&tmem_empty_bar[acc], (((uint32_t)t >> 1) & 1u) ^ 1u);   // epilogue has drained this buffer
         tc_fence_after();
-        const uint64_t a_desc = umma_desc_sw128(smem_u32(sA + s * A_STAGE_BYTES));
-        const uint64_t b_desc = umma_desc_sw128(smem_u32(sB + s * b_stage_bytes));
-        int ksteps = (g.K - kb * BK + 15) / 16;
-        ksteps = ksteps > 4 ? 4 : ksteps;
-        for (int k = 0; k < ksteps; ++k) {
-          // advance 16 fp16 = 32 bytes along K inside the 128-byte swizzle atom (+2 in 16-byte units)
-          umma_f16(tmem_base, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * g.block_n);
+        for (int kb = 0; kb < g.num_kb; ++kb, ++it) {
+          const int s = it % g.stages;
+          const uint32_t ph = (uint32_t)(it / g.stages) & 1u;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint64_t a_desc = umma_desc_sw128(smem_u32(sA + s * A_STAGE_BYTES));
+          const uint64_t b_desc = umma_desc_sw128(smem_u32(sB + s * b_stage_bytes));
+          int ksteps = (g.K - kb * BK + 15) / 16;
+          ksteps = ksteps > 4 ? 4 : ksteps;
+          for (int k = 0; k < ksteps; ++k) {
+            // advance 16 fp16 = 32 bytes along K inside the 128-byte swizzle atom (+2 in 16-byte units)
+            umma_f16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+          }
+          umma_commit(&empty_bar[s]);          // frees this smem stage once the MMAs above retire
         }
-        umma_commit(&empty_bar[s]);   // frees this smem stage once the MMAs above retire
+        umma_commit(&tmem_full_bar[acc]);      // accumulator complete -> epilogue
       }
-      umma_commit(tmem_full_bar);     // accumulator complete -> epilogue
     }
     __syncwarp();
   } else {
     // ------------------------------------------------------------- epilogue (4 warps)
-    const int q = warp & 3;
-    const int row = m_tile * BM + q * 32 + lane;
-    const bool row_ok = row < g.M;
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-    const int n0 = n_tile * g.block_n;
-    if (g.out_mode == 0) {
-      __half* orow = g.out + (size_t)row * g.ldc + n0;
-      for (int c0 = 0; c0 < g.block_n; c0 += 16) {
-        float v[16];
-        tmem_ld16(taddr + (uint32_t)c0, v);
-        tmem_ld_wait();
-        const float4* bp = reinterpret_cast<const float4*>(g.bias + n0 + c0);
-        uint32_t pk[8];
+    const int q = warp & 3;                    // TMEM lane quadrant this warp may access
+    float* my_bias = sBias + q * 256;
+    uint8_t* my_epi = sEpi + q * 2 * EPI_BUF_BYTES;
+    int t = 0, chunk_it = 0;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++t) {
+      const int n_tile = tile % g.n_tiles, m_tile = tile / g.n_tiles;
+      const int acc = t & 1;
+      const int n0 = n_tile * g.block_n;
+      const int row0 = m_tile * BM + q * 32;
+      const int row = row0 + lane;
+      const bool row_ok = row < g.M;
+      __syncwarp();
+      for (int i = lane; i < g.block_n; i += 32) my_bias[i] = __ldg(g.bias + n0 + i);
+      __syncwarp();
+      mbar_wait(&tmem_full_bar[acc], ((uint32_t)t >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * g.block_n);
+      if (g.out_mode == 0 && g.tma_store) {
+        for (int c0 = 0; c0 < g.block_n; c0 += EPI_CHUNK, ++chunk_it) {
+          uint8_t* buf = my_epi + (chunk_it & 1) * EPI_BUF_BYTES;
+          // the TMA store issued two chunks ago from this buffer must have finished reading it
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          float v[EPI_CHUNK];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float4 b4 = __ldg(bp + j);
-          float x0 = v[4 * j + 0] + b4.x, x1 = v[4 * j + 1] + b4.y, x2 = v[4 * j + 2] + b4.z, x3 = v[4 * j + 3] + b4.w;
-          if (g.relu) {
-            x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); x2 = fmaxf(x2, 0.f); x3 = fmaxf(x3, 0.f);
+          for (int j = 0; j < EPI_CHUNK / 16; ++j) tmem_ld16(taddr + (uint32_t)(c0 + 16 * j), v + 16 * j);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < EPI_CHUNK / 8; ++j) {          // 8 x 16-byte chunks of this lane's row
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float x0 = v[8 * j + 2 * e] + my_bias[c0 + 8 * j + 2 * e];
+              float x1 = v[8 * j + 2 * e + 1] + my_bias[c0 + 8 * j + 2 * e + 1];
+              if (g.relu) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); }
+              pk[e] = pack_half2(x0, x1);
+            }
+            // 128-byte swizzle: 16-byte chunk j of row r lives at chunk position j ^ (r & 7)
+            sts_v4(smem_u32(buf) + (uint32_t)(lane * 128 + ((j ^ (lane & 7)) << 4)), make_uint4(pk[0], pk[1], pk[2], pk[3]));
           }
-          pk[2 * j] = pack_half2(x0, x1);
-          pk[2 * j + 1] = pack_half2(x2, x3);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && row0 < g.M) {
+            tma_store_2d(&tmC, buf, n0 + c0, row0);
+            tma_store_commit();
+          }
         }
-        if (row_ok) {
-          uint4* dst = reinterpret_cast<uint4*>(orow + c0);
-          dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-          dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-        }
-      }
-    } else {
-      const int b = row_ok ? row / g.head.hw : 0;
-      const int p = row_ok ? row - b * g.head.hw : 0;
-      float* lrow = g.head.loc + (size_t)b * g.head.loc_pitch + g.head.loc_off + (size_t)p * g.head.n_loc;
-      float* crow = g.head.conf + (size_t)b * g.head.conf_pitch + g.head.conf_off + (size_t)p * g.head.n_conf;
-      const int n_valid = g.head.n_loc + g.head.n_conf;
-      for (int c0 = 0; c0 < g.block_n; c0 += 16) {
-        float v[16];
-        tmem_ld16(taddr + (uint32_t)c0, v);
-        tmem_ld_wait();
-        if (row_ok) {
+      } else if (g.out_mode == 0) {
+        __half* orow = g.out + (size_t)row * g.ldc + n0;
+        for (int c0 = 0; c0 < g.block_n; c0 += 16) {
+          float v[16];
+          tmem_ld16(taddr + (uint32_t)c0, v);
+          tmem_ld_wait();
+          uint32_t pk[8];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int c = n0 + c0 + j;
-            if (c < n_valid) {
-              float x = v[j] + __ldg(g.bias + c);
-              if (g.relu) x = fmaxf(x, 0.f);
-              if (c < g.head.n_loc) lrow[c] = x;
-              else crow[c - g.head.n_loc] = x;
+          for (int j = 0; j < 8; ++j) {
+            float x0 = v[2 * j] + my_bias[c0 + 2 * j], x1 = v[2 * j + 1] + my_bias[c0 + 2 * j + 1];
+            if (g.relu) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); }
+            pk[j] = pack_half2(x0, x1);
+          }
+          if (row_ok) {
+            uint4* dst = reinterpret_cast<uint4*>(orow + c0);
+            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          }
+        }
+      } else {
+        const int b = row_ok ? row / g.head.hw : 0;
+        const int p = row_ok ? row - b * g.head.hw : 0;
+        float* lrow = g.head.loc + (size_t)b * g.head.loc_pitch + g.head.loc_off + (size_t)p * g.head.n_loc;
+        float* crow = g.head.conf + (size_t)b * g.head.conf_pitch + g.head.conf_off + (size_t)p * g.head.n_conf;
+        const int n_valid = g.head.n_loc + g.head.n_conf;
+        for (int c0 = 0; c0 < g.block_n; c0 += 16) {
+          float v[16];
+          tmem_ld16(taddr + (uint32_t)c0, v);
+          tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int c = n0 + c0 + j;
+              if (c < n_valid) {
+                float x = v[j] + my_bias[c0 + j];
+                if (g.relu) x = fmaxf(x, 0.f);
+                if (c < g.head.n_loc) lrow[c] = x;
+                else crow[c - g.head.n_loc] = x;
+              }
             }
           }
         }
       }
+      // all tcgen05.ld of this accumulator have completed (wait::ld above): hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
     }
+    if (g.tma_store && lane == 0) tma_store_wait_all<0>();
   }
 
   tc_fence_before();
@@ -176,22 +245,36 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
 // ------------------------------------------------------------------------------------ host
 
+static int num_sms() {
+  static int cached[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (!cached[dev & 63]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev & 63] = n;
+  }
+  return cached[dev & 63];
+}
+
 static int pick_block_n(int M, int N) {
-  // Widest tile dividing N that still yields >= 2 waves of CTAs; otherwise the narrowest
-  // tile >= 64 (more CTAs in flight beats tile width for these bandwidth-bound shapes).
-  const int cand[] = {256, 160, 128, 80, 64, 48, 32, 16};
+  // Persistent kernel: the widest tile that still gives every SM a tile (fewer re-reads of A,
+  // wider TMA stores); otherwise the narrowest tile that is still >= 64 columns.
+  const int cand[] = {256, 160, 128, 80, 64};
   const int m_tiles = ceil_div(M, BM);
-  int fallback = 0;
+  const int sms = num_sms();
+  int last = 0;
   for (int c : cand) {
     if (N % c) continue;
-    if (m_tiles * (N / c) >= 2 * 148) return c;
-    if (c >= 64 || !fallback) fallback = c;
+    last = c;
+    if (m_tiles * (N / c) >= sms) return c;
   }
-  return fallback ? fallback : 16;
+  if (last) return last;
+  return N <= 256 ? N : 16;     // N in {16, 32, 48}
 }
 
 struct GemmLaunch {
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmC;
   GemmArgs args;
   int grid;
   int smem;
@@ -216,24 +299,38 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
   g.M = M; g.N = N; g.K = K;
   g.block_n = block_n;
   g.n_tiles = N / block_n;
+  g.num_tiles = ceil_div(M, BM) * g.n_tiles;
   g.num_kb = ceil_div(K, BK);
-  g.stages = g.num_kb < 4 ? g.num_kb : 4;
+  const int stage_bytes = A_STAGE_BYTES + block_n * BK * 2;
+  const int fixed = EPI_SMEM + BIAS_SMEM + 1024 + 256;
+  int stages = (GEMM_MAX_SMEM - fixed) / stage_bytes;
+  if (stages > 8) stages = 8;
+  DVC_REQUIRE(stages >= 2, "gemm: tile does not fit shared memory");
+  g.stages = stages;
   int cols = 32;
-  while (cols < block_n) cols <<= 1;
+  while (cols < 2 * block_n) cols <<= 1;
   g.tmem_cols = cols;
   g.bias = bias;
   g.out_mode = out_mode;
+  g.tma_store = (out_mode == 0 && block_n % EPI_CHUNK == 0) ? 1 : 0;
   g.out = reinterpret_cast<__half*>(out);
   g.ldc = ldc;
   g.relu = relu;
   if (head) g.head = *head; else g.head = dvc_head_out{};
-  L->grid = ceil_div(M, BM) * g.n_tiles;
-  L->smem = g.stages * (A_STAGE_BYTES + block_n * BK * 2) + 1024 + 256;
-  DVC_REQUIRE(L->smem <= GEMM_MAX_SMEM, "gemm: smem %d too large", L->smem);
+  const int sms = num_sms();
+  L->grid = g.num_tiles < sms ? g.num_tiles : sms;
+  L->smem = g.stages * stage_bytes + fixed;
   int rc = make_tmap_2d_f16(&L->tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
   if (rc) return rc;
   rc = make_tmap_2d_f16(&L->tmB, Wt, (uint64_t)N, (uint64_t)K, (uint64_t)K, (uint32_t)block_n, BK);
-  return rc;
+  if (rc) return rc;
+  if (g.tma_store) {
+    rc = make_tmap_2d_f16(&L->tmC, out, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 32, EPI_CHUNK);
+    if (rc) return rc;
+  } else {
+    L->tmC = L->tmA;
+  }
+  return DVC_OK;
 }
 
 int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
@@ -244,7 +341,7 @@ int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(gemm_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_MAX_SMEM));
     attr_set[dev & 63] = true;
   }
-  gemm_f16_kernel<<<L->grid, GEMM_THREADS, L->smem, st>>>(L->tmA, L->tmB, L->args);
+  gemm_f16_kernel<<<L->grid, GEMM_THREADS, L->smem, st>>>(L->tmA, L->tmB, L->tmC, L->args);
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;

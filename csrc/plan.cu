@@ -36,8 +36,12 @@ void det_free(DetLaunch*);
 void det_set_flag_value(DetLaunch*, uint32_t);
 void det_set_sinks(DetLaunch*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index);
 
-int dwconv_launch(const void* in, int B, int H, int W, int C, int stride, const float* w, const float* b, int relu, void* out,
-                  cudaStream_t st);
+struct DwLaunch;
+int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stride, const float* w, const float* b, int relu,
+               void* out);
+int dw_launch(const DwLaunch* L, cudaStream_t st);
+DwLaunch* dw_alloc();
+void dw_free(DwLaunch*);
 int im2col_launch(const void* in, int B, int H, int W, int C, void* out, cudaStream_t st);
 
 enum OpKind { OP_PREPROC, OP_DW, OP_GEMM, OP_IM2COL, OP_DET };
@@ -47,7 +51,8 @@ struct Op {
   GemmLaunch* gemm = nullptr;
   PreprocLaunch* pre = nullptr;
   DetLaunch* det = nullptr;
-  // dw / im2col
+  DwLaunch* dw = nullptr;
+  // im2col
   const void* in = nullptr; void* out = nullptr; const float* w = nullptr; const float* b = nullptr;
   int B = 0, H = 0, W = 0, C = 0, stride = 1, relu = 0;
 };
@@ -68,6 +73,7 @@ extern "C" void dvc_plan_destroy(dvc_plan* p) {
     if (op.gemm) gemm_free(op.gemm);
     if (op.pre) preproc_free(op.pre);
     if (op.det) det_free(op.det);
+    if (op.dw) dw_free(op.dw);
   }
   delete p;
 }
@@ -89,8 +95,9 @@ extern "C" int dvc_plan_add_dwconv(dvc_plan* p, const void* in_f16, int B, int H
                                    const float* b, int relu, void* out_f16) {
   DVC_REQUIRE(p, "plan is null");
   DVC_REQUIRE(C % 8 == 0 && (stride == 1 || stride == 2), "dwconv: C=%d stride=%d unsupported", C, stride);
-  Op op; op.kind = OP_DW; op.in = in_f16; op.out = out_f16; op.w = w; op.b = b;
-  op.B = B; op.H = H; op.W = W; op.C = C; op.stride = stride; op.relu = relu;
+  Op op; op.kind = OP_DW; op.dw = dw_alloc();
+  int rc = dw_prepare(op.dw, in_f16, B, H, W, C, stride, w, b, relu, out_f16);
+  if (rc) { dw_free(op.dw); return rc; }
   p->ops.push_back(op);
   return DVC_OK;
 }
@@ -156,7 +163,7 @@ extern "C" int dvc_plan_run(dvc_plan* p, void* stream) {
     int rc = DVC_OK;
     switch (op.kind) {
       case OP_PREPROC: rc = preproc_launch(op.pre, st); break;
-      case OP_DW: rc = dwconv_launch(op.in, op.B, op.H, op.W, op.C, op.stride, op.w, op.b, op.relu, op.out, st); break;
+      case OP_DW: rc = dw_launch(op.dw, st); break;
       case OP_GEMM: rc = gemm_launch(op.gemm, st); break;
       case OP_IM2COL: rc = im2col_launch(op.in, op.B, op.H, op.W, op.C, op.out, st); break;
       case OP_DET: rc = det_launch(op.det, st); break;

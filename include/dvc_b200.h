@@ -57,9 +57,14 @@ int dvc_preproc_conv0(const uint8_t* src400, long long src_frame_stride, const i
                       void* out_f16, void* stream);
 
 /* ---- K3: depthwise 3x3 (+bias, +ReLU), NHWC fp16, pad 1, stride 1|2 (prototxt:42-75 ...).
- * w is fp32 [9][C] (tap major), b fp32 [C]. */
+ * w is fp32 [9][C] (tap major), b fp32 [C].  The input tile + halo arrives by one 4-D TMA box load
+ * (zero-filled outside the image = the padding); products are fp16 x fp16 accumulated in fp32
+ * (FHFMA), so the weights are rounded to fp16 inside the kernel. */
 int dvc_dwconv3x3(const void* in_f16, int B, int H, int W, int C, int stride, const float* w, const float* b,
                   int relu, void* out_f16, void* stream);
+
+int dvc_dwconv3x3_direct(const void* in_f16, int B, int H, int W, int C, int stride, const float* w, const float* b,
+                         int relu, void* out_f16, void* stream);   /* non-TMA variant, for A/B measurements */
 
 /* ---- K2/K5: pointwise conv as GEMM on tcgen05 tensor cores with TMA-fed operands and a
  * TMEM accumulator: out[M,N] = act(A[M,K] * Wt[N,K]^T + bias[N]).  A and Wt are K-major
