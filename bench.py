@@ -84,47 +84,96 @@ def run_native(args):
     eng = NativeEngine(graph, dev, cfg, requester_id="127.0.0.1:5554")
     st = eng.state(B, H, W)
 
-    # ---- inputs: POOL distinct batches per rank, on the device (kernel timing) and pinned on the host (e2e)
-    host_pool = torch.from_numpy(synth_frames(POOL * B, H, W, seed=100 + rank)).view(POOL, B, H, W, 3).pin_memory()
-    dev_pool = host_pool.to(dev)
-    host_det = torch.empty((B, 100, 7), dtype=torch.float32).pin_memory()
-    host_cnt = torch.empty((B,), dtype=torch.int32).pin_memory()
-
     def barrier():
         if multi:
             dist.barrier()
         torch.cuda.synchronize()
 
+    if not multi:
+        # ---- inputs: POOL distinct batches, on the device (kernel timing) and pinned on the host (e2e)
+        host_pool = torch.from_numpy(synth_frames(POOL * B, H, W, seed=100)).view(POOL, B, H, W, 3).pin_memory()
+        dev_pool = host_pool.to(dev)
+        step = lambda i: eng.run(st, src=dev_pool[i % POOL])
+        per_step_launches = eng.launches_per_batch(st)
+    else:
+        # ---- one requester: the client GPU (rank 0) owns the frames of the whole global batch; every rank
+        # pulls its 64 frames over NVLink inside K1b and pushes its detection rows back inside the NMS kernel.
+        from distributedvolunteercomputing_b200.parallel.cluster import BoxCluster
+        cluster = BoxCluster(eng, B, H, W, client_rank=0)
+        if rank == 0:
+            host_pool = torch.from_numpy(synth_frames(POOL * world * B, H, W, seed=100)).view(POOL, world * B, H, W, 3).pin_memory()
+            dev_pool = host_pool.to(dev)
+            step = lambda i: cluster.step(dev_pool[i % POOL])
+        else:
+            step = lambda i: cluster.step()
+        per_step_launches = cluster.launches_per_step()
+
     # ---- device-timed region
     for i in range(args.warmup):
-        eng.run(st, src=dev_pool[i % POOL])
+        step(i)
     barrier()
     sampler = ClockSampler(local).start() if rank == 0 else None
     l0 = lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for i in range(args.steps):
-        eng.run(st, src=dev_pool[i % POOL])
+        step(i)
     ev1.record()
     barrier()
     dev_ms = ev0.elapsed_time(ev1)
     launches_eager = lib.launch_count() - l0
-    det_sum = int(st.det_count.sum().item())
+    det_sum = int((cluster.det_count if multi and rank == 0 else st.det_count).sum().item()) if (not multi or rank == 0) else 0
 
-    # ---- end-to-end region through the public API: pinned host frames in, detections out, every step
-    for i in range(min(3, args.warmup)):
-        eng.process(host_pool[i % POOL])
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        r = eng.process(host_pool[i % POOL])
-        host_det.copy_(r.det, non_blocking=True)
-        host_cnt.copy_(r.det_count, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-    e1.record()
-    barrier()
-    e2e_ms = e0.elapsed_time(e1)
+    # ---- end-to-end region through the public API: every step copies that step's frames from pinned host
+    # memory to the device and reads the step's detections back to the host.
+    if not multi:
+        def host_batches(n):
+            for i in range(n):
+                yield host_pool[i % POOL]
+
+        for r in eng.process_stream(host_batches(max(3, min(args.warmup, 6)))):
+            pass
+        barrier()
+        t_e2e0 = time.perf_counter()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        got = 0
+        for r in eng.process_stream(host_batches(args.steps)):
+            got += int(r.det_count[0] >= 0)          # touch the host copy of every step's result
+        e1.record()
+        barrier()
+        assert got == args.steps
+        e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - t_e2e0) * 1e3)
+        e2e_api = "NativeEngine.process_stream (3 streams, depth 2)"
+        h2d, d2h = B * H * W * 3, B * 100 * 7 * 4 + B * 100 * 4 * 4 + 2 * B * 4
+    else:
+        n_all = world * B
+        if rank == 0:
+            h_det = torch.empty((n_all, 100, 7), dtype=torch.float32).pin_memory()
+            h_cnt = torch.empty((n_all,), dtype=torch.int32).pin_memory()
+
+        def e2e_step(i):
+            if rank == 0:
+                cluster.raw_all.copy_(host_pool[i % POOL], non_blocking=True)
+                cluster.step()
+                h_det.copy_(cluster.det, non_blocking=True)
+                h_cnt.copy_(cluster.det_count, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+            else:
+                cluster.step()
+
+        for i in range(3):
+            e2e_step(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            e2e_step(i)
+        e1.record()
+        barrier()
+        e2e_ms = e0.elapsed_time(e1)
+        e2e_api = "BoxCluster.step (client GPU uploads the global batch, NVLink pull/push inside the kernels)"
+        h2d, d2h = n_all * H * W * 3, n_all * 100 * 7 * 4 + n_all * 4
     clocks = sampler.stop() if sampler else None
 
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
@@ -134,18 +183,17 @@ def run_native(args):
     frames_total = world * B * args.steps
     value = frames_total / (dev_ms / 1e3)
     e2e = frames_total / (e2e_ms / 1e3)
-    per_step_launches = eng.launches_per_batch(st)
     out = {
         "metric": METRIC, "value": round(value, 1), "unit": "frames/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "fp16", "data": "synthetic", "impl": "native",
         "config": {"model": "MobileNet-SSD 300x300 (random-init caffemodel architecture, 5.78M params)",
-                   "global_batch": world * B, "seq_len": None, "frame_hw": [H, W], "parallelism": f"dp{world}",
+                   "global_batch": world * B, "seq_len": None, "frame_hw": [H, W], "parallelism": f"dp{world}" + (" (frame scatter / detection gather fused into kernels over NVLink)" if multi else ""),
                    "l2_policy": f"inputs rotate over {POOL} distinct batches ({POOL * B * H * W * 3 / 1e6:.0f} MB > 126 MB L2)",
                    "cuda_graph": not args.no_graph, "sub_batch": cfg.sub_batch or 16,
                    "p50_frame_latency_ms": round(dev_ms / args.steps, 4)},
-        "e2e": {"value": round(e2e, 1), "unit": "frames/s", "h2d_bytes_per_step": int(B * H * W * 3),
-                "d2h_bytes_per_step": int(B * 100 * 7 * 4 + B * 4), "ms_per_step": round(e2e_ms / args.steps, 4)},
+        "e2e": {"value": round(e2e, 1), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": round(e2e_ms / args.steps, 4), "api": e2e_api},
         "gpu_launches": int(per_step_launches * args.steps),
         "gpu_launches_counted_by_library": int(launches_eager),
         "clocks": clocks, "detections_last_batch": det_sum,

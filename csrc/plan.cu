@@ -21,7 +21,7 @@ void gemm_free(GemmLaunch*);
 
 int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B, int sh,
                     int sw, const int* xs, const int* xq, const int* ys, const int* yq, const float* w0, const float* b0,
-                    const float* h_mean3, float scale, void* out, int band_rows_max);
+                    const float* h_mean3, float scale, void* out, int band_rows_max, int slot0);
 int preproc_launch(const PreprocLaunch* L, cudaStream_t st);
 PreprocLaunch* preproc_alloc();
 void preproc_free(PreprocLaunch*);
@@ -82,10 +82,11 @@ extern "C" int dvc_plan_num_ops(const dvc_plan* p) { return p ? (int)p->ops.size
 
 extern "C" int dvc_plan_add_preproc_conv0(dvc_plan* p, const uint8_t* src400, long long src_frame_stride, const int* frame_index,
                                           int B, int sh, int sw, const int* xs, const int* xq, const int* ys, const int* yq,
-                                          const float* w0, const float* b0, const float* h_mean3, float scale, void* out_f16) {
+                                          const float* w0, const float* b0, const float* h_mean3, float scale, void* out_f16,
+                                          int slot0) {
   DVC_REQUIRE(p, "plan is null");
   Op op; op.kind = OP_PREPROC; op.pre = preproc_alloc();
-  int rc = preproc_prepare(op.pre, src400, src_frame_stride, frame_index, B, sh, sw, xs, xq, ys, yq, w0, b0, h_mean3, scale, out_f16, 0);
+  int rc = preproc_prepare(op.pre, src400, src_frame_stride, frame_index, B, sh, sw, xs, xq, ys, yq, w0, b0, h_mean3, scale, out_f16, 0, slot0);
   if (rc) { preproc_free(op.pre); return rc; }
   p->ops.push_back(op);
   return DVC_OK;

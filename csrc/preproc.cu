@@ -128,6 +128,7 @@ struct PreprocArgs {
   float mean0, mean1, mean2, scale;
   __half* out;
   int band_bytes;     // smem bytes reserved for the staged source rows
+  int slot0;          // first source slot of this launch (sub-batch offset inside the ring)
 };
 
 __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const PreprocArgs a) {
@@ -144,7 +145,7 @@ __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const Prep
   const int oy0 = band * PC_BAND;
   const int iy_first = max(2 * oy0 - 1, 0);
   const int iy_last = min(2 * oy0 + 2 * PC_BAND - 1, PC_NET - 1);
-  const int slot = a.frame_index ? a.frame_index[b] : b;
+  const int slot = a.frame_index ? a.frame_index[a.slot0 + b] : a.slot0 + b;
   const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
   const int row_bytes = a.sw * 3;
 
@@ -265,7 +266,7 @@ struct PreprocLaunch {
 
 int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B,
                     int sh, int sw, const int* xs, const int* xq, const int* ys, const int* yq, const float* w0,
-                    const float* b0, const float* h_mean3, float scale, void* out, int band_rows_max) {
+                    const float* b0, const float* h_mean3, float scale, void* out, int band_rows_max, int slot0) {
   DVC_REQUIRE(B > 0 && sh > 1 && sw > 1, "preproc: bad shape B=%d %dx%d", B, sh, sw);
   DVC_REQUIRE(src_frame_stride % 16 == 0 && (reinterpret_cast<uintptr_t>(src400) & 15) == 0,
               "preproc: frames must be 16-byte aligned (stride %lld)", src_frame_stride);
@@ -275,6 +276,7 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
   a.xs = xs; a.xq = xq; a.ys = ys; a.yq = yq; a.w0 = w0; a.b0 = b0;
   a.mean0 = h_mean3[0]; a.mean1 = h_mean3[1]; a.mean2 = h_mean3[2]; a.scale = scale;
   a.out = reinterpret_cast<__half*>(out);
+  a.slot0 = slot0;
   // worst-case staged rows for one band: 17 net rows span at most ceil(17*sh/300)+2 source rows
   if (band_rows_max <= 0) band_rows_max = (PC_PROWS * sh + PC_NET - 1) / PC_NET + 3;
   if (band_rows_max > sh) band_rows_max = sh;
@@ -334,7 +336,7 @@ extern "C" int dvc_preproc_conv0(const uint8_t* src400, long long src_frame_stri
                                  const float* b0, const float* mean3, float scale, void* out_f16, void* stream) {
   dvc::PreprocLaunch L;
   int rc = dvc::preproc_prepare(&L, src400, src_frame_stride, frame_index, B, sh, sw, xs, xq, ys, yq, w0, b0, mean3, scale,
-                                out_f16, 0);
+                                out_f16, 0, 0);
   if (rc) return rc;
   return dvc::preproc_launch(&L, (cudaStream_t)stream);
 }

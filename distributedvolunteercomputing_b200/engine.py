@@ -142,9 +142,9 @@ class NativeEngine:
         return sum(t.numel() * t.element_size() for t in list(self.w.values()) + list(self.b.values()))
 
     # ------------------------------------------------------------------ per-shape state
-    def state(self, B: int, H: int, W: int, requester_id: Optional[str] = None) -> _ShapeState:
+    def state(self, B: int, H: int, W: int, requester_id: Optional[str] = None, slot: int = 0) -> _ShapeState:
         rid = self.requester_id if requester_id is None else requester_id
-        key = (B, H, W, rid)
+        key = (B, H, W, rid, slot)
         st = self._states.get(key)
         if st is None:
             with torch.cuda.device(self.device):
@@ -237,9 +237,9 @@ class NativeEngine:
             nb = min(sub, B - b0)
             cur, other = st.sA, st.sB
             L.check(lib.dvc_plan_add_preproc_conv0(
-                plan, L.ptr(st.frames400_flat) + b0 * st.stride400, st.stride400, None, nb, st.h4, st.w4,
+                plan, L.ptr(st.frames400_flat), st.stride400, None, nb, st.h4, st.w4,
                 L.ptr(st.t_lin.xs), L.ptr(st.t_lin.xq), L.ptr(st.t_lin.ys), L.ptr(st.t_lin.yq), L.ptr(self.w["conv0"]),
-                L.ptr(self.b["conv0"]), C.cast(st.mean, C.c_void_p), float(self.cfg.scale), L.ptr(cur)), "conv0")
+                L.ptr(self.b["conv0"]), C.cast(st.mean, C.c_void_p), float(self.cfg.scale), L.ptr(cur), b0), "conv0")
             for li in range(1, split_idx + 1):
                 c = body[li]
                 if li == split_idx:
@@ -288,14 +288,30 @@ class NativeEngine:
                                       L.ptr(st.box_count), None, L.ptr(m.id_mask), m.id_xy[0], m.id_xy[1], idw, idh,
                                       L.ptr(m.label_masks), nl, m.label_xy[0], m.label_xy[1], lw, lh, L.stream_ptr()), "annotate")
 
+    def bind_remote(self, st: _ShapeState, frames_ptr: int, frame_stride: int, det_ptr: int, det_count_ptr: int,
+                    boxes_ptr: int, box_count_ptr: int, flags_ptr: int = 0, flag_value: int = 0):
+        """Point this state's plan at frames that live elsewhere (e.g. the ingest GPU's ring, mapped over
+        NVLink) and at result rings that live elsewhere (the client GPU).  K1b then pulls its frames with
+        peer loads and the detection kernel pushes its rows with peer stores.  Must precede graph capture."""
+        L = self.L
+        L.check(self.lib.dvc_plan_set_source(st.plan, frames_ptr, frame_stride, None), "plan_set_source")
+        L.check(self.lib.dvc_plan_set_sinks(st.plan, det_ptr, det_count_ptr, boxes_ptr, box_count_ptr, flags_ptr or None, None),
+                "plan_set_sinks")
+        L.check(self.lib.dvc_plan_set_flag_value(st.plan, flag_value), "plan_set_flag_value")
+        for key in ("graph_ann", "graph_noann"):
+            if hasattr(st, key):
+                delattr(st, key)
+        st.remote = True
+
     def run(self, st: _ShapeState, annotate: bool = True, use_graph: Optional[bool] = None,
-            src: Optional[torch.Tensor] = None):
+            src: Optional[torch.Tensor] = None, resize: bool = True):
         """Process the frames in ``st.raw`` (or in ``src``, a device batch of the same shape).
         Asynchronous on the current stream.  With CUDA graphs the resize launch stays eager
         (its source pointer may change per call) and everything after it is one graph replay."""
         use_graph = self.cfg.use_cuda_graph if use_graph is None else use_graph
         with torch.cuda.device(self.device):
-            self._enqueue_resize(st, src)
+            if resize:
+                self._enqueue_resize(st, src)
             if not use_graph:
                 self._enqueue_body(st, annotate)
                 return
@@ -310,7 +326,8 @@ class NativeEngine:
                     self._enqueue_body(st, annotate)
                 setattr(st, key, gr)
                 # the warm-up pass annotated the 400-wide frames in place: regenerate them before the replay
-                self._enqueue_resize(st, src)
+                if resize:
+                    self._enqueue_resize(st, src)
             gr.replay()
 
     def debug_layerwise(self, frames400: torch.Tensor) -> Dict[str, torch.Tensor]:
@@ -358,6 +375,68 @@ class NativeEngine:
             self.run(st, annotate)
             torch.cuda.current_stream().synchronize()
         return self.result(st)
+
+    def process_stream(self, batches, depth: int = 2, annotate: bool = True, fetch_frames: bool = False,
+                       requester_id: Optional[str] = None):
+        """Pipelined public API: iterate over host batches (uint8 [B,H,W,3], ideally pinned) and yield one
+        host-side ``BatchResult`` per batch, in order.  Three streams and ``depth`` independent slots overlap
+        the host->device copy of batch i+1, the kernels of batch i and the device->host read of batch i-1.
+        ``fetch_frames`` also brings the annotated 400-wide frames back (large); detections always come back."""
+        dev = self.device
+        with torch.cuda.device(dev):
+            s_in, s_run, s_out = (torch.cuda.Stream(device=dev) for _ in range(3))
+            slots = {}
+            pending = []      # (slot record, ready event)
+
+            def finish(rec, ev):
+                ev.synchronize()
+                return BatchResult(rec["h_det"], rec["h_cnt"], rec["h_boxes"], rec["h_bcnt"],
+                                   rec["h_frames"] if fetch_frames else None)
+
+            for i, batch in enumerate(batches):
+                t = batch if isinstance(batch, torch.Tensor) else torch.as_tensor(batch)
+                B, H, W, _ = t.shape
+                k = i % depth
+                key = (k, B, H, W)
+                rec = slots.get(key)
+                if rec is None:
+                    st = self.state(B, H, W, requester_id, slot=1 + k)
+                    rec = {"st": st, "free": None,
+                           "h_det": torch.empty((B, 100, 7), dtype=torch.float32).pin_memory(),
+                           "h_cnt": torch.empty((B,), dtype=torch.int32).pin_memory(),
+                           "h_boxes": torch.empty((B, 100, 4), dtype=torch.int32).pin_memory(),
+                           "h_bcnt": torch.empty((B,), dtype=torch.int32).pin_memory(),
+                           "h_frames": torch.empty((B, st.h4, st.w4, 3), dtype=torch.uint8).pin_memory() if fetch_frames else None}
+                    slots[key] = rec
+                # a slot is reused only after its previous result has been handed out
+                while pending and len(pending) >= depth:
+                    yield finish(*pending.pop(0))
+                st = rec["st"]
+                with torch.cuda.stream(s_in):
+                    if rec["free"] is not None:
+                        s_in.wait_event(rec["free"])
+                    st.raw.copy_(t, non_blocking=True)
+                    ev_in = torch.cuda.Event()
+                    ev_in.record(s_in)
+                with torch.cuda.stream(s_run):
+                    s_run.wait_event(ev_in)
+                    self.run(st, annotate)
+                    ev_run = torch.cuda.Event()
+                    ev_run.record(s_run)
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(ev_run)
+                    rec["h_det"].copy_(st.det, non_blocking=True)
+                    rec["h_cnt"].copy_(st.det_count, non_blocking=True)
+                    rec["h_boxes"].copy_(st.boxes_i, non_blocking=True)
+                    rec["h_bcnt"].copy_(st.box_count, non_blocking=True)
+                    if fetch_frames:
+                        rec["h_frames"].copy_(st.frames400, non_blocking=True)
+                    ev_out = torch.cuda.Event()
+                    ev_out.record(s_out)
+                rec["free"] = ev_out
+                pending.append((rec, ev_out))
+            while pending:
+                yield finish(*pending.pop(0))
 
     def close(self):
         for st in self._states.values():

@@ -52,7 +52,7 @@ _SIGS = {
     "dvc_plan_create": ([], _P),
     "dvc_plan_destroy": ([_P], None),
     "dvc_plan_num_ops": ([_P], _I),
-    "dvc_plan_add_preproc_conv0": ([_P, _P, _LL, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _F, _P], _I),
+    "dvc_plan_add_preproc_conv0": ([_P, _P, _LL, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _F, _P, _I], _I),
     "dvc_plan_add_dwconv": ([_P, _P, _I, _I, _I, _I, _I, _P, _P, _I, _P], _I),
     "dvc_plan_add_gemm": ([_P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _I, _I, _P, _I], _I),
     "dvc_plan_add_im2col": ([_P, _P, _I, _I, _I, _I, _P], _I),
@@ -61,6 +61,16 @@ _SIGS = {
     "dvc_plan_set_sinks": ([_P, _P, _P, _P, _P, _P, _P], _I),
     "dvc_plan_set_flag_value": ([_P, _U32], _I),
     "dvc_plan_run": ([_P, _P], _I),
+    "dvc_dwconv3x3_direct": ([_P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P], _I),
+    "dvc_p2p_alloc": ([_SZ, C.POINTER(C.c_void_p)], _I),
+    "dvc_p2p_free": ([_P], _I),
+    "dvc_p2p_get_handle": ([_P, _P], _I),
+    "dvc_p2p_open": ([_P, C.POINTER(C.c_void_p)], _I),
+    "dvc_p2p_close": ([_P], _I),
+    "dvc_p2p_enable_peer": ([_I], _I),
+    "dvc_epoch_broadcast": ([_P, _I, _U32, _P], _I),
+    "dvc_push_multicast": ([_P, _P, _I, _SZ, _P], _I),
+    "dvc_peer_read": ([_P, _SZ, _P, _P], _I),
 }
 
 

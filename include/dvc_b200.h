@@ -172,7 +172,8 @@ void dvc_plan_destroy(dvc_plan*);
 int dvc_plan_num_ops(const dvc_plan*);
 int dvc_plan_add_preproc_conv0(dvc_plan*, const uint8_t* src400, long long src_frame_stride, const int* frame_index,
                                int B, int sh, int sw, const int* xs, const int* xq, const int* ys, const int* yq,
-                               const float* w0, const float* b0, const float* h_mean3, float scale, void* out_f16);
+                               const float* w0, const float* b0, const float* h_mean3, float scale, void* out_f16,
+                               int slot0 /* first ring slot read by this op; src400 is the ring base */);
 int dvc_plan_add_dwconv(dvc_plan*, const void* in_f16, int B, int H, int W, int C, int stride, const float* w,
                         const float* b, int relu, void* out_f16);
 int dvc_plan_add_gemm(dvc_plan*, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
@@ -188,6 +189,23 @@ int dvc_plan_set_sinks(dvc_plan*, float* det, int* det_count, int* boxes_i, int*
                        const int* slot_index);
 int dvc_plan_set_flag_value(dvc_plan*, uint32_t flag_value);
 int dvc_plan_run(dvc_plan*, void* stream);
+
+/* ---- P2P substrate (csrc/p2p.cu).  These DO allocate / map device memory (set-up time only).
+ * A buffer is owned by one GPU process, exported as a 64-byte CUDA IPC handle and mapped by the
+ * other per-GPU processes of the box; kernels then load/store it directly over NVLink.  This
+ * replaces the reference's 4-hop TCP relay through the server (server.py:56,89,60,73). */
+int dvc_p2p_alloc(size_t bytes, void** out);                 /* cudaMalloc + zero */
+int dvc_p2p_free(void* p);
+int dvc_p2p_get_handle(void* p, void* h_handle64);           /* export (owner) */
+int dvc_p2p_open(const void* h_handle64, void** out);        /* map (peer), enables peer access lazily */
+int dvc_p2p_close(void* p);
+int dvc_p2p_enable_peer(int peer_device);                    /* same-process multi-GPU */
+/* K14 membership epoch: write `value` (release.sys) to each of n peer addresses (server.py:104-154). */
+int dvc_epoch_broadcast(void** d_dst_ptrs, int n, uint32_t value, void* stream);
+/* K13 weight distribution: push `bytes` from src into n peer buffers (worker.py:194 loads per client). */
+int dvc_push_multicast(const void* src, void** d_dst_ptrs, int n, size_t bytes, void* stream);
+/* NVLink read-bandwidth probe (16-byte loads of a possibly remote buffer). */
+int dvc_peer_read(const void* src, size_t bytes, void* d_sink, void* stream);
 
 #ifdef __cplusplus
 }

