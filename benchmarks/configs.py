@@ -1,0 +1,147 @@
+#!/usr/bin/env python
+"""The other BASELINE.json configs, on the in-process elastic cluster (one NativeEngine per GPU):
+
+  --config live          single synthetic 1080p stream at --fps 30|60: p50/p99 per-frame latency
+  --config elastic       8 -> 4 -> 8 workers (or N -> N/2 -> N) mid-stream, no dropped frames
+  --config multi_client  32 concurrent synthetic 720p streams, whole-box frames/s
+
+Prints one JSON line per run.  Latencies are host wall-clock from "frame handed to the cluster" to
+"result delivered in order" (they include H2D, all kernels, D2H and scheduling).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def synth(n, h, w, seed=0):
+    rng = np.random.default_rng(seed)
+    small = rng.integers(0, 256, (n, h // 16 + 1, w // 16 + 1, 3), dtype=np.uint8)
+    return np.ascontiguousarray(np.repeat(np.repeat(small, 16, axis=1), 16, axis=2)[:, :h, :w])
+
+
+def main():
+    import torch
+    from distributedvolunteercomputing_b200.config import Config
+    from distributedvolunteercomputing_b200.engine import NativeEngine
+    from distributedvolunteercomputing_b200.models.mobilenet_ssd import SSDGraph
+    from distributedvolunteercomputing_b200.parallel.local_cluster import LocalCluster
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", required=True, choices=["live", "elastic", "multi_client"])
+    ap.add_argument("--gpus", type=int, default=torch.cuda.device_count())
+    ap.add_argument("--fps", type=int, default=30)
+    ap.add_argument("--frames", type=int, default=0)
+    ap.add_argument("--batch", type=int, default=0)
+    args = ap.parse_args()
+    n_gpu = min(args.gpus, torch.cuda.device_count())
+    graph = SSDGraph.random(seed=1, conf_gain=2.5)
+
+    def engine(i, batch, sub):
+        return NativeEngine(graph, f"cuda:{i}", Config(batch=batch, sub_batch=sub, use_cuda_graph=True), requester_id="client")
+
+    if args.config == "live":
+        B = args.batch or 1
+        H, W = 1080, 1920
+        n = args.frames or 300
+        cfg = Config(batch=B, worker_timeout_s=5.0)
+        lat = []
+        cl = LocalCluster(cfg, annotate=True, on_frame=lambda r, fr: lat.append(fr.latency_s * 1e3))
+        for i in range(n_gpu):
+            cl.join(f"gpu{i}", engine(i, B, 1), capacity=2)
+        frames = [torch.from_numpy(f).pin_memory() for f in synth(8, H, W)]
+        for i in range(2 * n_gpu * 3):                                        # warm-up (plans, graphs)
+            cl.submit("warm", frames[i % 8][None], i + 1)
+        cl.wait("warm", 2 * n_gpu * 3, 120)
+        lat.clear()
+        period = 1.0 / args.fps
+        t0 = time.monotonic()
+        for i in range(n):
+            target = t0 + i * period
+            while time.monotonic() < target:
+                time.sleep(0.0002)
+            cl.submit("cam", frames[i % 8][None], i + 1)
+        ok = cl.wait("cam", n, 120)
+        lat_s = sorted(lat)
+        out = {"config": "live 1080p", "fps": args.fps, "n_gpus": n_gpu, "frames": n, "complete": ok,
+               "p50_ms": round(lat_s[len(lat_s) // 2], 3), "p99_ms": round(lat_s[int(len(lat_s) * 0.99) - 1], 3),
+               "max_ms": round(lat_s[-1], 3), "batch": B}
+        print(json.dumps(out), flush=True)
+        cl.close()
+    elif args.config == "elastic":
+        B = args.batch or 64
+        H, W = 300, 300
+        n_batches = 60 * n_gpu
+        cfg = Config(batch=B, worker_timeout_s=10.0)
+        seen = []
+        cl = LocalCluster(cfg, annotate=True, on_frame=lambda r, fr: seen.append(fr.frame_id))
+        engines = [engine(i, B, 0) for i in range(n_gpu)]
+        for i, e in enumerate(engines):
+            cl.join(f"gpu{i}", e)
+        pool = torch.from_numpy(synth(B * 4, H, W)).pin_memory()
+        for i in range(n_gpu * 2):
+            cl.submit("warm", pool[:B], i * B + 1)
+        cl.wait("warm", n_gpu * 2 * B, 180)
+        N = n_batches * B
+        t0 = time.monotonic()
+        for b in range(n_batches):
+            cl.submit("client", pool[(b % 4) * B:(b % 4 + 1) * B], b * B + 1)
+        time.sleep(0.05)
+        half = list(range(n_gpu // 2, n_gpu)) if n_gpu > 1 else []
+        t_leave = time.monotonic() - t0
+        lost = sum(cl.leave(f"gpu{i}") for i in half)                         # N -> N/2 with batches in flight
+        time.sleep(0.15)
+        for i in half:
+            cl.join(f"gpu{i}", engines[i])                                    # N/2 -> N
+        t_join = time.monotonic() - t0
+        ok = cl.wait("client", N, 300)
+        dt = time.monotonic() - t0
+        in_order = seen[-N:] == list(range(1, N + 1))
+        out = {"config": f"elastic {n_gpu}->{n_gpu - len(half)}->{n_gpu}", "n_gpus": n_gpu, "frames": N, "complete": ok,
+               "in_order_no_drop_no_dup": bool(in_order), "redispatched_batches": int(cl.sched.stats["redispatched"]),
+               "batches_in_flight_at_leave": int(lost), "t_leave_s": round(t_leave, 3), "t_rejoin_s": round(t_join, 3),
+               "frames_per_s": round(N / dt, 1), "seconds": round(dt, 3)}
+        print(json.dumps(out), flush=True)
+        cl.close()
+    else:
+        B = args.batch or 16
+        H, W = 720, 1280
+        streams, per = 32, (args.frames or 128)
+        cfg = Config(batch=B, worker_timeout_s=10.0)
+        counts = {}
+        lk = threading.Lock()
+
+        def on_frame(r, fr):
+            with lk:
+                counts[r] = counts.get(r, 0) + 1
+
+        cl = LocalCluster(cfg, annotate=True, on_frame=on_frame)
+        for i in range(n_gpu):
+            cl.join(f"gpu{i}", engine(i, B, 4))
+        pool = torch.from_numpy(synth(B * 2, H, W)).pin_memory()
+        for i in range(n_gpu * 2):
+            cl.submit("warm", pool[:B], i * B + 1)
+        cl.wait("warm", n_gpu * 2 * B, 180)
+        t0 = time.monotonic()
+        for s in range(streams):
+            for k in range(0, per, B):
+                cl.submit(f"cam{s}", pool[(k // B % 2) * B:(k // B % 2 + 1) * B], k + 1)
+        ok = all(cl.wait(f"cam{s}", per, 300) for s in range(streams))
+        dt = time.monotonic() - t0
+        out = {"config": "32 concurrent 720p streams", "n_gpus": n_gpu, "streams": streams, "frames": streams * per, "complete": ok,
+               "frames_per_s": round(streams * per / dt, 1), "seconds": round(dt, 3), "batch": B,
+               "batch_latency_p50_ms": cl.metrics.percentile("batch_latency_ms", 50), "batch_latency_p99_ms": cl.metrics.percentile("batch_latency_ms", 99)}
+        print(json.dumps(out), flush=True)
+        cl.close()
+
+
+if __name__ == "__main__":
+    main()

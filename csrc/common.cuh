@@ -192,6 +192,16 @@ __device__ __forceinline__ uint4 lds_v4(uint32_t saddr) {
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(saddr));
   return r;
 }
+__device__ __forceinline__ float2 lds_f2(uint32_t saddr) {
+  float2 r;
+  asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(r.x), "=f"(r.y) : "r"(saddr));
+  return r;
+}
+__device__ __forceinline__ float lds_f1(uint32_t saddr) {
+  float r;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(saddr));
+  return r;
+}
 __device__ __forceinline__ void sts_v4(uint32_t saddr, const uint4& v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }

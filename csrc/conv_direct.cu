@@ -215,7 +215,7 @@ int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stri
     for (int TX = 1; TX <= (a.Wo < 64 ? a.Wo : 64); ++TX) {
       const int outs = TX * TY;
       if (outs > 1024) continue;
-      if (outs < 96 && (TX < a.Wo || TY < a.Ho)) continue;
+      if (outs < 64 && (TX < a.Wo || TY < a.Ho)) continue;
       const int BW = (TX - 1) * stride + 3, BH = (TY - 1) * stride + 3;
       if (BW > 256 || BH > 256 || BW * BH * a.CT * 2 > DW_SMEM_LIMIT) continue;
       const int ntx = ceil_div(a.Wo, TX), nty = ceil_div(a.Ho, TY);

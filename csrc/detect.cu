@@ -35,7 +35,7 @@ __global__ void priorbox_kernel(float* boxes, float* variances, int prior_off, i
 }
 
 // ------------------------------------------------------------------------------ K7/K8/K9
-constexpr int DET_THREADS = 512;
+constexpr int DET_THREADS = 672;    // 21 warps: one per class for the NMS phase
 constexpr int DET_MAXC = 32;      // classes
 constexpr int DET_MAXK = 128;     // per-class top_k capacity
 
@@ -183,24 +183,60 @@ __global__ void __launch_bounds__(DET_THREADS) detection_kernel(const DetArgs a)
     }
   }
   __syncthreads();
-  // ---- phase 6: gather survivors, global keep_top_k by rank counting
-  for (int e = tid; e < C * K; e += DET_THREADS) {
-    const int c = e / K, r = e - c * K;
-    if (r < s_nsel[c] && sel_keep[c * DET_MAXK + r]) kept[atomicAdd(&s_misc[0], 1)] = (c << 16) | r;
+  // ---- phase 6: global keep_top_k.  Survivors of one class are already in rank order, so the global
+  // rank of an entry is the sum over classes of "survivors of that class that sort before it": a
+  // binary search per class over its sorted list plus an exclusive prefix count of the keep flags.
+  int* kprefix = kept;                                   // [C][DET_MAXK] survivors among r' < r
+  for (int c = warp; c < C; c += DET_THREADS / 32) {
+    const int n = s_nsel[c];
+    int cnt = 0;
+    int flags4[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int r = lane * 4 + k;
+      flags4[k] = (r < n && sel_keep[c * DET_MAXK + r]) ? 1 : 0;
+      cnt += flags4[k];
+    }
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int up = __shfl_up_sync(0xffffffff, incl, d);
+      if (lane >= d) incl += up;
+    }
+    int run = incl - cnt;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      kprefix[c * DET_MAXK + lane * 4 + k] = run;
+      run += flags4[k];
+    }
+    if (lane == 31) s_fill[c] = incl;                    // survivors of class c (s_fill is free by now)
   }
+  __syncthreads();
+  if (tid == 0) {
+    int tot = 0;
+    for (int c = 0; c < C; ++c) tot += s_fill[c];
+    s_misc[0] = tot;
+  }
+  for (int e = tid; e < DVC_MAX_DET * DVC_DET_ROW; e += DET_THREADS) s_rows[e] = 0.f;
   __syncthreads();
   const int n_kept = s_misc[0];
   const int n_out = min(n_kept, min(a.p.keep_top_k, DVC_MAX_DET));
-  for (int e = tid; e < DVC_MAX_DET * DVC_DET_ROW; e += DET_THREADS) s_rows[e] = 0.f;
-  __syncthreads();
-  for (int e = tid; e < n_kept; e += DET_THREADS) {
-    const int c = kept[e] >> 16, r = kept[e] & 0xffff;
+  for (int e = tid; e < C * K; e += DET_THREADS) {
+    const int c = e / K, r = e - c * K;
+    if (r >= s_nsel[c] || !sel_keep[c * DET_MAXK + r]) continue;
     const float s = sel_score[c * DET_MAXK + r];
     const int id = sel_idx[c * DET_MAXK + r];
     int rank = 0;
-    for (int j = 0; j < n_kept; ++j) {
-      const int cj = kept[j] >> 16, rj = kept[j] & 0xffff;
-      rank += before(sel_score[cj * DET_MAXK + rj], sel_idx[cj * DET_MAXK + rj], cj, s, id, c) ? 1 : 0;
+    for (int c2 = 0; c2 < C; ++c2) {
+      const int n2 = s_nsel[c2];
+      if (n2 == 0) continue;
+      int lo = 0, hi = n2;                               // first index whose entry does NOT sort before (s,id,c)
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (before(sel_score[c2 * DET_MAXK + mid], sel_idx[c2 * DET_MAXK + mid], c2, s, id, c)) lo = mid + 1;
+        else hi = mid;
+      }
+      rank += lo == n2 ? s_fill[c2] : kprefix[c2 * DET_MAXK + lo];
     }
     if (rank < n_out) {
       float* row = s_rows + rank * DVC_DET_ROW;

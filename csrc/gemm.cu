@@ -24,13 +24,14 @@ namespace dvc {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;               // 2 control warps + 2 groups of 4 epilogue warps
 constexpr int A_STAGE_BYTES = BM * BK * 2;       // 16 KiB
 constexpr int GEMM_MAX_SMEM = 227 * 1024;
 constexpr int EPI_CHUNK = 64;                    // columns per staging buffer (128 B of fp16 per row)
 constexpr int EPI_BUF_BYTES = 32 * EPI_CHUNK * 2;   // one warp, 32 rows x 128 B
-constexpr int EPI_SMEM = 4 * 2 * EPI_BUF_BYTES;  // 4 warps x 2 buffers
-constexpr int BIAS_SMEM = 4 * 256 * 4;           // per-epilogue-warp bias slice (block_n <= 256)
+constexpr int EPI_SMEM = 2 * 4 * 2 * EPI_BUF_BYTES;   // 2 groups x 4 warps x 2 buffers
+constexpr int BIAS_MAX_N = 2048;
+constexpr int BIAS_SMEM = BIAS_MAX_N * 4;        // the whole bias vector, loaded once per CTA
 
 struct GemmArgs {
   int M, N, K;
@@ -65,6 +66,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;           // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
+  for (int i = threadIdx.x; i < g.N; i += GEMM_THREADS) sBias[i] = __ldg(g.bias + i);
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -139,21 +141,23 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------- epilogue (4 warps)
+    // ------------------------------------------------------------- epilogue (2 groups x 4 warps)
+    // Group e drains accumulator buffer e, i.e. every second tile of this CTA, so two tiles are in
+    // the epilogue at once while the MMA warp fills the buffer the other group has just released.
     const int q = warp & 3;                    // TMEM lane quadrant this warp may access
-    float* my_bias = sBias + q * 256;
-    uint8_t* my_epi = sEpi + q * 2 * EPI_BUF_BYTES;
-    int t = 0, chunk_it = 0;
-    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++t) {
+    const int grp = (warp - 2) >> 2;
+    const uint32_t bias_s = smem_u32(sBias);
+    uint8_t* my_epi = sEpi + (grp * 4 + q) * 2 * EPI_BUF_BYTES;
+    int chunk_it = 0;
+    for (int t = grp; ; t += 2) {
+      const int tile = blockIdx.x + t * gridDim.x;
+      if (tile >= g.num_tiles) break;
       const int n_tile = tile % g.n_tiles, m_tile = tile / g.n_tiles;
-      const int acc = t & 1;
+      const int acc = grp;
       const int n0 = n_tile * g.block_n;
       const int row0 = m_tile * BM + q * 32;
       const int row = row0 + lane;
       const bool row_ok = row < g.M;
-      __syncwarp();
-      for (int i = lane; i < g.block_n; i += 32) my_bias[i] = __ldg(g.bias + n0 + i);
-      __syncwarp();
       mbar_wait(&tmem_full_bar[acc], ((uint32_t)t >> 1) & 1u);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * g.block_n);
@@ -172,8 +176,9 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             uint32_t pk[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              float x0 = v[8 * j + 2 * e] + my_bias[c0 + 8 * j + 2 * e];
-              float x1 = v[8 * j + 2 * e + 1] + my_bias[c0 + 8 * j + 2 * e + 1];
+              const float2 bb = lds_f2(bias_s + (uint32_t)((n0 + c0 + 8 * j + 2 * e) * 4));
+              float x0 = v[8 * j + 2 * e] + bb.x;
+              float x1 = v[8 * j + 2 * e + 1] + bb.y;
               if (g.relu) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); }
               pk[e] = pack_half2(x0, x1);
             }
@@ -196,7 +201,8 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           uint32_t pk[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            float x0 = v[2 * j] + my_bias[c0 + 2 * j], x1 = v[2 * j + 1] + my_bias[c0 + 2 * j + 1];
+            const float2 bb = lds_f2(bias_s + (uint32_t)((n0 + c0 + 2 * j) * 4));
+            float x0 = v[2 * j] + bb.x, x1 = v[2 * j + 1] + bb.y;
             if (g.relu) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); }
             pk[j] = pack_half2(x0, x1);
           }
@@ -221,7 +227,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             for (int j = 0; j < 16; ++j) {
               const int c = n0 + c0 + j;
               if (c < n_valid) {
-                float x = v[j] + my_bias[c0 + j];
+                float x = v[j] + lds_f1(bias_s + (uint32_t)(c * 4));
                 if (g.relu) x = fmaxf(x, 0.f);
                 if (c < g.head.n_loc) lrow[c] = x;
                 else crow[c - g.head.n_loc] = x;
@@ -283,7 +289,7 @@ struct GemmLaunch {
 int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
                  int out_mode, void* out, int ldc, int relu, const dvc_head_out* head, int block_n) {
   DVC_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
-  DVC_REQUIRE(N % 16 == 0, "gemm: N=%d must be a multiple of 16 (pad the weights)", N);
+  DVC_REQUIRE(N % 16 == 0 && N <= BIAS_MAX_N, "gemm: N=%d must be a multiple of 16 (pad the weights) and <= %d", N, BIAS_MAX_N);
   DVC_REQUIRE(K % 16 == 0 && lda % 8 == 0, "gemm: K=%d must be a multiple of 16 and lda=%d of 8", K, lda);
   DVC_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(Wt) & 15) == 0,
               "gemm: operands must be 16-byte aligned");

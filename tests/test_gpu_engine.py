@@ -128,5 +128,6 @@ def test_process_stream_matches_sync(engines):
         outs.append((r.det.numpy().copy(), r.det_count.numpy().copy(), r.boxes_i.numpy().copy(), r.box_count.numpy().copy()))
     assert len(outs) == 5
     for a, b in zip(sync, outs):
-        for x, y in zip(a, b):
-            assert np.array_equal(x, y)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[3], b[3])
+        for k in range(len(a[3])):                       # integer boxes: only the first box_count rows are defined
+            assert np.array_equal(a[2][k, : a[3][k]], b[2][k, : b[3][k]])
