@@ -63,7 +63,7 @@ def run(args, metric: str):
     n_workers = max(1, args.gpus)
     chunk = args.batch
     steps = args.steps
-    cap_frames = int(os.environ.get("DVC_REF_MAX_FRAMES", "512"))
+    cap_frames = int(os.environ.get("DVC_REF_MAX_FRAMES", "256"))
     while steps > 1 and steps * chunk * n_workers > cap_frames:
         steps -= 1
     total = steps * chunk * n_workers
@@ -98,15 +98,15 @@ def run(args, metric: str):
         def ready(log):
             txt = open(log).read()
             return "READY" in txt and "[INFO] detecting" in txt
-        while time.time() - t0 < 120 and not all(ready(l) for l in logs):
+        while time.time() - t0 < 90 and not all(ready(l) for l in logs):
             time.sleep(0.25)
         if not all(ready(l) for l in logs):
-            return _unavailable("reference clients did not come up within 120 s: " + open(logs[0]).read()[-200:].replace("\n", " "))
+            return _unavailable("reference clients did not come up within 90 s: " + open(logs[0]).read()[-200:].replace("\n", " "))
         time.sleep(0.5)
         req = clients[-1]
         req.stdin.write(f"request {video}\n")
         req.stdin.flush()
-        limit = float(os.environ.get("DVC_REF_TIMEOUT", "600"))
+        limit = float(os.environ.get("DVC_REF_TIMEOUT", "240"))
         job = None
         t0 = time.time()
         while time.time() - t0 < limit:

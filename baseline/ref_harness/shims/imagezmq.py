@@ -42,10 +42,13 @@ class ImageHub:
             self.zmq_socket.connect(open_port)
         self.REQ_REP = REQ_REP
 
-    def recv_image(self, copy=False):
+    def recv_image(self, copy=True):
+        # copy=True: the reference keeps crops of this array alive across later recv calls and hands
+        # them to cv2.VideoWriter from another thread; with zero-copy zmq frames that segfaults here
+        # (cv2 4.13 / pyzmq 27), so the shim owns its bytes.  The wire format is unchanged.
         md = self.zmq_socket.recv_json()
         msg = self.zmq_socket.recv(copy=copy, track=False)
-        A = np.frombuffer(msg, dtype=md["dtype"])
+        A = np.frombuffer(bytearray(msg) if copy else msg, dtype=md["dtype"])
         return md["msg"], A.reshape(md["shape"])
 
     def send_reply(self, reply_message=b"OK"):

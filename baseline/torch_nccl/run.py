@@ -63,23 +63,27 @@ def run(args, metric: str):
         cx, cy = var[:, 0] * l[..., 0] * pw + pcx, var[:, 1] * l[..., 1] * ph + pcy
         w, h = torch.exp(var[:, 2] * l[..., 2]) * pw, torch.exp(var[:, 3] * l[..., 3]) * ph
         boxes = torch.stack([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2], -1)          # [B,P,4]
-        sc = prob[..., 1:]                                                                # [B,P,20]
+        sc = prob[..., 1:].transpose(1, 2)                                                # [B,20,P]
+        top, idx = torch.where(sc > 0.25, sc, torch.zeros_like(sc)).topk(100, dim=2)      # per-class top_k (prototxt:1905)
+        bx = torch.gather(boxes[:, None].expand(-1, 20, -1, -1), 2, idx[..., None].expand(-1, -1, -1, 4))   # [B,20,100,4]
+        G = B * 20
+        bx, top = bx.reshape(G, 100, 4), top.reshape(G, 100)
+        x0 = torch.maximum(bx[:, :, None, 0], bx[:, None, :, 0]); y0 = torch.maximum(bx[:, :, None, 1], bx[:, None, :, 1])
+        x1 = torch.minimum(bx[:, :, None, 2], bx[:, None, :, 2]); y1 = torch.minimum(bx[:, :, None, 3], bx[:, None, :, 3])
+        inter = (x1 - x0).clamp(min=0) * (y1 - y0).clamp(min=0)
+        area = (bx[..., 2] - bx[..., 0]) * (bx[..., 3] - bx[..., 1])
+        iou = inter / (area[:, :, None] + area[:, None, :] - inter).clamp(min=1e-12)
+        over = (iou > 0.45).triu(1)                                                       # i suppresses later j
+        keep = top > 0
+        for i in range(100):                                                              # greedy, vectorised over groups
+            keep = keep & ~(over[:, i, :] & keep[:, i:i + 1])
+        score = torch.where(keep, top, torch.zeros_like(top)).view(B, 2000)
+        best, flat = score.topk(100, dim=1)                                               # keep_top_k
+        cls = (flat // 100 + 1).float()
         out = torch.zeros((B, 100, 7), device=dev)
-        if batched_nms is None:
-            return out
-        m = sc > 0.25
-        bi, pi, ci = m.nonzero(as_tuple=True)
-        keep = batched_nms(boxes[bi, pi], sc[bi, pi, ci], bi * 32 + ci, 0.45)
-        kb = bi[keep]
-        # top-100 per image (keep is score-sorted)
-        order = torch.argsort(kb, stable=True)
-        keep, kb = keep[order], kb[order]
-        pos = torch.arange(len(kb), device=dev) - torch.searchsorted(kb, kb)
-        sel = pos < 100
-        keep, kb, pos = keep[sel], kb[sel], pos[sel]
-        out[kb, pos, 1] = (ci[keep] + 1).float()
-        out[kb, pos, 2] = sc[bi[keep], pi[keep], ci[keep]]
-        out[kb, pos, 3:7] = boxes[bi[keep], pi[keep]]
+        out[..., 1] = torch.where(best > 0, cls, torch.zeros_like(cls))
+        out[..., 2] = best
+        out[..., 3:7] = torch.gather(bx.view(B, 2000, 4), 1, flat[..., None].expand(-1, -1, 4)) * (best > 0)[..., None]
         return out
 
     rng = np.random.default_rng(100 + rank)
@@ -156,7 +160,7 @@ def run(args, metric: str):
             "impl": "torch",
             "config": {"model": "MobileNet-SSD 300x300 (torch cuDNN channels_last fp16 + CUDA graph)", "global_batch": total_B,
                        "seq_len": None, "frame_hw": [H, W], "parallelism": f"dp{world} nccl scatter/gather",
-                       "nms": "torchvision.batched_nms" if batched_nms is not None else "none (torchvision missing)"},
+                       "nms": "per-class top-100 + vectorised greedy NMS in torch ops"},
             "e2e": {"value": round(frames / (float(t[1]) / 1e3), 1), "unit": "frames/s",
                     "h2d_bytes_per_step": int(total_B * H * W * 3), "d2h_bytes_per_step": int(total_B * 100 * 7 * 4)},
             "gpu_launches": 0, "clocks": clocks}), flush=True)

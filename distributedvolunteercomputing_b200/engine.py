@@ -93,6 +93,13 @@ class CpuEngine:
 
 
 # ==================================================================================== native
+import threading
+
+# CUDA-graph capture is process-global state: engines on different GPUs driven from different threads
+# must not capture at the same time, and other threads' CUDA calls must not invalidate a capture.
+_CAPTURE_LOCK = threading.Lock()
+
+
 class _ShapeState:
     """Everything that depends on (batch, source frame size): buffers, tables, plan, graph."""
     pass
@@ -319,12 +326,13 @@ class NativeEngine:
             gr = getattr(st, key, None)
             if gr is None:
                 # warm up outside capture (first-launch attribute setup), then capture
-                self._enqueue_body(st, annotate)
-                torch.cuda.synchronize(self.device)
-                gr = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(gr):
+                with _CAPTURE_LOCK:
                     self._enqueue_body(st, annotate)
-                setattr(st, key, gr)
+                    torch.cuda.synchronize(self.device)
+                    gr = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gr, capture_error_mode="thread_local"):
+                        self._enqueue_body(st, annotate)
+                    setattr(st, key, gr)
                 # the warm-up pass annotated the 400-wide frames in place: regenerate them before the replay
                 if resize:
                     self._enqueue_resize(st, src)

@@ -59,11 +59,13 @@ class _Worker:
             frames, t_submit, fetch = b.payload
             try:
                 res = self.engine.process(frames, requester_id=b.requester, annotate=cl.annotate).numpy()
-            except Exception as e:    # a failing worker must not lose work
+            except BaseException as e:    # a failing worker must not lose work: it is retired, its batches move on
                 cl.metrics.inc("worker_errors")
-                cl.sched.fail(b.batch_id, reason="error")
                 cl.log(f"worker {self.name} failed on batch {b.batch_id}: {e!r}")
-                continue
+                cl.last_error = repr(e)
+                self.alive = False
+                cl.sched.leave(self.name)
+                return
             if not self.alive and cl.drop_results_of_departed:
                 continue              # it left before finishing: the re-dispatched copy will deliver
             first = cl.sched.complete(b.batch_id, self.name)
@@ -89,6 +91,7 @@ class LocalCluster:
         self.lock = threading.RLock()
         self.done_cv = threading.Condition(self.lock)
         self.drop_results_of_departed = False
+        self.last_error: Optional[str] = None
         self.running = True
         self.dispatcher = threading.Thread(target=self._dispatch_loop, daemon=True, name="dispatcher")
         self.dispatcher.start()
