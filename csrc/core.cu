@@ -87,5 +87,12 @@ int make_tmap_nhwc_f16(CUtensorMap* out, const void* base, uint64_t n, uint64_t 
 }  // namespace dvc
 
 extern "C" int dvc_version(void) { return 100; }
+/* This library links its own (static) CUDA runtime, whose per-thread current device is separate from the
+ * one PyTorch's runtime tracks.  Callers that drive several GPUs from one process select the device here
+ * before preparing or launching anything on it. */
+extern "C" int dvc_set_device(int device) {
+  DVC_CHECK_CUDA(cudaSetDevice(device));
+  return DVC_OK;
+}
 extern "C" const char* dvc_last_error(void) { return dvc::g_err; }
 extern "C" long long dvc_launch_count(void) { return dvc::g_launches.load(); }

@@ -121,6 +121,7 @@ class NativeEngine:
         self.max_batch = max_batch or self.cfg.batch
         self._states: Dict[Tuple[int, int, int, str], _ShapeState] = {}
         with torch.cuda.device(self.device):
+            L.set_device(self.device)
             self._pack_weights()
             self.priors, self.variances = K.priorbox(graph.priors_spec, graph.input_hw, self.device)
 
@@ -155,6 +156,7 @@ class NativeEngine:
         st = self._states.get(key)
         if st is None:
             with torch.cuda.device(self.device):
+                self.L.set_device(self.device)
                 st = self._make_state(B, H, W, rid)
             self._states[key] = st
         return st
@@ -317,6 +319,7 @@ class NativeEngine:
         (its source pointer may change per call) and everything after it is one graph replay."""
         use_graph = self.cfg.use_cuda_graph if use_graph is None else use_graph
         with torch.cuda.device(self.device):
+            self.L.set_device(self.device)
             if resize:
                 self._enqueue_resize(st, src)
             if not use_graph:
@@ -330,7 +333,10 @@ class NativeEngine:
                     self._enqueue_body(st, annotate)
                     torch.cuda.synchronize(self.device)
                     gr = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(gr, capture_error_mode="thread_local"):
+                    # an explicit capture stream on THIS device: torch's default capture stream is created
+                    # once per process on whichever device was current first
+                    cap_stream = torch.cuda.Stream(device=self.device)
+                    with torch.cuda.graph(gr, stream=cap_stream, capture_error_mode="thread_local"):
                         self._enqueue_body(st, annotate)
                     setattr(st, key, gr)
                 # the warm-up pass annotated the 400-wide frames in place: regenerate them before the replay

@@ -39,6 +39,7 @@ _SIGS = {
     "dvc_version": ([], _I),
     "dvc_last_error": ([], C.c_char_p),
     "dvc_launch_count": ([], _LL),
+    "dvc_set_device": ([_I], _I),
     "dvc_resize_u8": ([_P, _LL, _I, _I, _I, _P, _LL, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _P], _I),
     "dvc_preproc_conv0": ([_P, _LL, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _F, _P, _P], _I),
     "dvc_dwconv3x3": ([_P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P], _I),
@@ -118,6 +119,12 @@ def ptr(t) -> Optional[int]:
     if isinstance(t, int):
         return t
     return t.data_ptr()
+
+
+def set_device(device) -> None:
+    """Make `device` current in the library's own CUDA runtime (see dvc_set_device)."""
+    idx = torch.device(device).index
+    check(load().dvc_set_device(0 if idx is None else idx), "set_device")
 
 
 def stream_ptr(stream=None) -> int:

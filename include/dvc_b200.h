@@ -30,6 +30,9 @@ int dvc_version(void);
 const char* dvc_last_error(void);
 /* Number of kernel launches issued by this library in this process (bench "gpu_launches"). */
 long long dvc_launch_count(void);
+/* Select the device for this thread inside the library's own (statically linked) CUDA runtime.  Needed only
+ * when one process drives several GPUs; call it whenever you switch devices. */
+int dvc_set_device(int device);
 
 /* ---- K1a: u8 HWC resize, the imutils.resize(width=400) step (worker.py:243).
  * mode 0: INTER_AREA decimation by coefficient tables (xs/xc/xa = start index, tap count,
