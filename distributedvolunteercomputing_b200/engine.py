@@ -393,12 +393,14 @@ class NativeEngine:
     def process_stream(self, batches, depth: int = 2, annotate: bool = True, fetch_frames: bool = False,
                        requester_id: Optional[str] = None):
         """Pipelined public API: iterate over host batches (uint8 [B,H,W,3], ideally pinned) and yield one
-        host-side ``BatchResult`` per batch, in order.  Three streams and ``depth`` independent slots overlap
-        the host->device copy of batch i+1, the kernels of batch i and the device->host read of batch i-1.
+        host-side ``BatchResult`` per batch, in order.  ``depth`` independent slots (own buffers, plan, CUDA
+        graph and compute stream each) plus a copy-in and a copy-out stream overlap the host->device copy of
+        batch i+1, the kernels of batches i and i-1 (which share the SMs) and the device->host read of batch i-2.
         ``fetch_frames`` also brings the annotated 400-wide frames back (large); detections always come back."""
         dev = self.device
         with torch.cuda.device(dev):
-            s_in, s_run, s_out = (torch.cuda.Stream(device=dev) for _ in range(3))
+            s_in, s_out = (torch.cuda.Stream(device=dev) for _ in range(2))
+            run_lanes = [torch.cuda.Stream(device=dev) for _ in range(depth)]    # batches in flight overlap on the SMs
             slots = {}
             pending = []      # (slot record, ready event)
 
@@ -432,6 +434,7 @@ class NativeEngine:
                     st.raw.copy_(t, non_blocking=True)
                     ev_in = torch.cuda.Event()
                     ev_in.record(s_in)
+                s_run = run_lanes[k]
                 with torch.cuda.stream(s_run):
                     s_run.wait_event(ev_in)
                     self.run(st, annotate)

@@ -13,10 +13,14 @@ torch.distributed (NCCL) is used for set-up (IPC handle exchange) and for two st
 one-element all-reduces per step that order "ring filled" -> "pull" and "rows pushed" -> "annotate";
 no frame or detection bytes go through NCCL.  This replaces the reference's star relay, where every
 frame crosses TCP four times through the server (server.py:56,89,60,73).
+
+`lanes` global batches are in flight at once: each lane has its own rings, plan, CUDA graph, stream
+and NCCL communicator, so the small latency-bound kernels of one global batch overlap the large
+kernels of the other on every GPU.
 """
 from __future__ import annotations
 
-from typing import Optional
+from typing import List, Optional
 
 import torch
 
@@ -25,23 +29,39 @@ from ..ops import lib as L
 from . import p2p
 
 
+class _Lane:
+    pass
+
+
 class BoxCluster:
-    def __init__(self, engine, B: int, H: int, W: int, client_rank: int = 0, group=None):
+    def __init__(self, engine, B: int, H: int, W: int, client_rank: int = 0, lanes: int = 2):
         import torch.distributed as dist
         self.dist = dist
-        self.group = group
         self.engine = engine
-        self.rank = dist.get_rank(group)
-        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank()
+        self.world = dist.get_world_size()
         self.client_rank = client_rank
         self.is_client = self.rank == client_rank
         self.B, self.H, self.W = B, H, W
         self.dev = engine.device
-        st = engine.state(B, H, W)
-        self.st = st
-        n = self.world * B
-        self.n = n
-        bufs = {k: None for k in ("frames", "det", "det_count", "boxes", "box_count", "flags")}
+        self.n = self.world * B
+        self.step_id = 0
+        self.lanes: List[_Lane] = [self._make_lane(k) for k in range(max(1, lanes))]
+        # convenience aliases to lane 0 (single-lane users and tests)
+        l0 = self.lanes[0]
+        self.st = l0.st
+        if self.is_client:
+            self.raw_all, self.frames400, self.det, self.det_count = l0.raw_all, l0.frames400, l0.det, l0.det_count
+            self.boxes_i, self.box_count, self.flags = l0.boxes_i, l0.box_count, l0.flags
+
+    def _make_lane(self, k: int) -> _Lane:
+        dist, eng, B, n = self.dist, self.engine, self.B, self.n
+        ln = _Lane()
+        ln.group = dist.new_group(list(range(self.world))) if k > 0 else None      # own communicator per lane
+        ln.stream = torch.cuda.Stream(device=self.dev)
+        st = eng.state(B, self.H, self.W, slot=200 + k)
+        ln.st = st
+        bufs = {name: None for name in ("frames", "det", "det_count", "boxes", "box_count", "flags")}
         if self.is_client:
             bufs["frames"] = p2p.DevBuffer(n * st.stride400, self.dev)
             bufs["det"] = p2p.DevBuffer(n * 700 * 4, self.dev)
@@ -49,50 +69,65 @@ class BoxCluster:
             bufs["boxes"] = p2p.DevBuffer(n * 400 * 4, self.dev)
             bufs["box_count"] = p2p.DevBuffer(n * 4, self.dev)
             bufs["flags"] = p2p.DevBuffer(n * 4, self.dev)
-        self.bufs = bufs
-        self.ptrs = p2p.exchange(bufs, self.dev, group)
-        c = client_rank
-        r = self.rank
-        base = {k: self.ptrs[k][c] for k in bufs}
-        engine.bind_remote(st,
-                           frames_ptr=base["frames"] + r * B * st.stride400, frame_stride=st.stride400,
-                           det_ptr=base["det"] + r * B * 700 * 4, det_count_ptr=base["det_count"] + r * B * 4,
-                           boxes_ptr=base["boxes"] + r * B * 400 * 4, box_count_ptr=base["box_count"] + r * B * 4,
-                           flags_ptr=base["flags"] + r * B * 4, flag_value=1)
-        self.step_id = 0
-        self._tok = torch.zeros(1, device=self.dev)
+        ln.bufs = bufs
+        ptrs = p2p.exchange(bufs, self.dev, None)
+        c, r = self.client_rank, self.rank
+        base = {name: ptrs[name][c] for name in bufs}
+        eng.bind_remote(st,
+                        frames_ptr=base["frames"] + r * B * st.stride400, frame_stride=st.stride400,
+                        det_ptr=base["det"] + r * B * 700 * 4, det_count_ptr=base["det_count"] + r * B * 4,
+                        boxes_ptr=base["boxes"] + r * B * 400 * 4, box_count_ptr=base["box_count"] + r * B * 4,
+                        flags_ptr=base["flags"] + r * B * 4, flag_value=1)
+        ln.tok = torch.zeros(1, device=self.dev)
         if self.is_client:
-            self.raw_all = torch.zeros((n, H, W, 3), dtype=torch.uint8, device=self.dev)
-            self.frames_flat = bufs["frames"].tensor(torch.uint8, (n, st.stride400))
-            self.frames400 = torch.as_strided(self.frames_flat, (n, st.h4, st.w4, 3), (st.stride400, st.w4 * 3, 3, 1))
-            self.det = bufs["det"].tensor(torch.float32, (n, 100, 7))
-            self.det_count = bufs["det_count"].tensor(torch.int32, (n,))
-            self.boxes_i = bufs["boxes"].tensor(torch.int32, (n, 100, 4))
-            self.box_count = bufs["box_count"].tensor(torch.int32, (n,))
-            self.flags = bufs["flags"].tensor(torch.int32, (n,))
+            ln.raw_all = torch.zeros((n, self.H, self.W, 3), dtype=torch.uint8, device=self.dev)
+            ln.frames_flat = bufs["frames"].tensor(torch.uint8, (n, st.stride400))
+            ln.frames400 = torch.as_strided(ln.frames_flat, (n, st.h4, st.w4, 3), (st.stride400, st.w4 * 3, 3, 1))
+            ln.det = bufs["det"].tensor(torch.float32, (n, 100, 7))
+            ln.det_count = bufs["det_count"].tensor(torch.int32, (n,))
+            ln.boxes_i = bufs["boxes"].tensor(torch.int32, (n, 100, 4))
+            ln.box_count = bufs["box_count"].tensor(torch.int32, (n,))
+            ln.flags = bufs["flags"].tensor(torch.int32, (n,))
+        return ln
 
-    def _order(self):
-        """Stream-ordered rendezvous of all ranks (no host synchronisation)."""
-        self.dist.all_reduce(self._tok, group=self.group)
+    def lane_of(self, step_index: int) -> _Lane:
+        return self.lanes[step_index % len(self.lanes)]
 
-    def step(self, raw_all: Optional[torch.Tensor] = None, annotate: bool = True):
-        """One global batch: world*B frames (on the client GPU) -> detections + annotated frames on the
-        client GPU.  Asynchronous on the current stream of every rank."""
-        st = self.st
-        self.step_id += 1
+    def _run_lane(self, ln: _Lane, raw_all: Optional[torch.Tensor], annotate: bool):
+        st = ln.st
         if self.is_client:
-            K.resize_u8(self.raw_all if raw_all is None else raw_all, st.t_area, self.frames_flat, st.stride400)
-        self._order()                                   # ring filled -> everyone may pull
+            K.resize_u8(ln.raw_all if raw_all is None else raw_all, st.t_area, ln.frames_flat, st.stride400)
+        self.dist.all_reduce(ln.tok, group=ln.group)          # ring filled -> everyone may pull (stream-ordered)
         self.engine.run(st, annotate=False, resize=False)
-        self._order()                                   # rows pushed -> the client may draw
+        self.dist.all_reduce(ln.tok, group=ln.group)          # rows pushed -> the client may draw
         if self.is_client and annotate:
             m = st.masks
             nl, lh, lw = m.label_masks.shape
             idh, idw = m.id_mask.shape
-            L.check(self.engine.lib.dvc_annotate(L.ptr(self.frames_flat), st.stride400, None, self.n, st.h4, st.w4,
-                                                 L.ptr(self.boxes_i), L.ptr(self.box_count), None, L.ptr(m.id_mask), m.id_xy[0],
+            L.check(self.engine.lib.dvc_annotate(L.ptr(ln.frames_flat), st.stride400, None, self.n, st.h4, st.w4,
+                                                 L.ptr(ln.boxes_i), L.ptr(ln.box_count), None, L.ptr(m.id_mask), m.id_xy[0],
                                                  m.id_xy[1], idw, idh, L.ptr(m.label_masks), nl, m.label_xy[0], m.label_xy[1],
                                                  lw, lh, L.stream_ptr()), "annotate")
+
+    def step(self, raw_all: Optional[torch.Tensor] = None, annotate: bool = True, overlap: bool = False) -> _Lane:
+        """One global batch: world*B frames (on the client GPU) -> detections + annotated frames on the
+        client GPU.  Asynchronous.  With ``overlap`` the batch runs on its lane's stream so consecutive
+        batches share the GPUs; call ``join()`` (or wait on the lane's stream) before reading results.
+        Every rank must call step() the same number of times in the same order."""
+        ln = self.lane_of(self.step_id if overlap else 0)
+        self.step_id += 1
+        with torch.cuda.device(self.dev):
+            if not overlap:
+                self._run_lane(ln, raw_all, annotate)
+                return ln
+            ln.stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(ln.stream):
+                self._run_lane(ln, raw_all, annotate)
+        return ln
+
+    def join(self):
+        for ln in self.lanes:
+            torch.cuda.current_stream().wait_stream(ln.stream)
 
     def launches_per_step(self) -> int:
         n = self.st.n_ops
