@@ -254,7 +254,7 @@ def run_native(args):
         "config": {"model": "MobileNet-SSD 300x300 (random-init caffemodel architecture, 5.78M params)",
                    "global_batch": world * B, "seq_len": None, "frame_hw": [H, W], "parallelism": f"dp{world}" + (" (frame scatter / detection gather fused into kernels over NVLink)" if multi else ""),
                    "l2_policy": f"inputs rotate over {POOL} distinct batches ({POOL * B * H * W * 3 / 1e6:.0f} MB > 126 MB L2)",
-                   "cuda_graph": not args.no_graph, "sub_batch": cfg.sub_batch or 16,
+                   "cuda_graph": not args.no_graph, "sub_batch": cfg.sub_batch or B,
                    "batches_in_flight": conc, "p50_batch_latency_ms": round(p50_batch_ms, 4)},
         "e2e": {"value": round(e2e, 1), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": round(e2e_ms / args.steps, 4), "api": e2e_api},

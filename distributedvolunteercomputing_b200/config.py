@@ -49,7 +49,7 @@ class Config:
     # ---- B200 engine
     device: str = "auto"                # "auto" | "cpu" | "cuda:N"
     batch: int = 64                     # frames per GPU batch (BASELINE.json config 2)
-    sub_batch: int = 0                  # 0 = auto; early layers run in L2-sized sub-batches
+    sub_batch: int = 0                  # 0 = whole batch per launch; >0 runs conv0..conv6 in sub-batches of this size
     use_cuda_graph: bool = True
     metrics_jsonl: Optional[str] = None
 

@@ -193,7 +193,9 @@ class NativeEngine:
     def _build_plan(self, st: _ShapeState):
         L, g, dev, lib = self.L, self.graph, self.device, self.lib
         B = st.B
-        sub = self.cfg.sub_batch if self.cfg.sub_batch > 0 else 16
+        # sub_batch = 0 (default): no split.  Measured on B200 (batch 64, two batches in flight): 57.5k / 65.5k /
+        # 70.1k / 71.7k frames/s for sub-batches of 8 / 16 / 32 / 64 - fewer, larger launches beat L2 residency.
+        sub = self.cfg.sub_batch if self.cfg.sub_batch > 0 else B
         sub = min(sub, B)
         body = g.body
         # split point: everything up to and including `split_name` runs per sub-batch
