@@ -19,96 +19,123 @@ struct ResizeArgs {
   const int *xs, *xc; const float* xa; int x_taps;
   const int *ys, *yc; const float* ya; int y_taps;
   const int *xq, *yq; int ix, iy;
+  int band;       // output rows per CTA
+  int aligned;    // frames 16-byte aligned (base and stride): vectorised staging
 };
 
-// Each thread produces RP horizontally adjacent output pixels (RP = 4 when the output width
-// allows it, so the 12 output bytes go out as three aligned 32-bit stores).
+// One CTA per (band of output rows, frame).  The source rows the band needs are staged in shared memory
+// with coalesced 16-byte loads (every source byte is fetched once per band), then each thread produces RP
+// horizontally adjacent output pixels (RP = 4 when the output width allows it, so the 12 output bytes go
+// out as three aligned 32-bit stores).
 template <int RP>
 __global__ void __launch_bounds__(256) resize_u8_kernel(const ResizeArgs a) {
-  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
-  const int gw = a.dw / RP;
-  const long long per = (long long)a.dh * gw;
-  if (idx >= per * a.B) return;
-  const int b = (int)(idx / per);
-  const int rem = (int)(idx - (long long)b * per);
-  const int dy = rem / gw, dxg = (rem - dy * gw) * RP;
-  const uint8_t* s = a.src + (size_t)b * a.src_stride;
-  uint8_t* d = a.dst + (size_t)b * a.dst_stride + ((size_t)dy * a.dw + dxg) * 3;
-  uint8_t o[RP * 3];
-  if (a.mode == 0) {
-    const int y0 = a.ys[dy], yn = a.yc[dy];
-#pragma unroll
-    for (int r = 0; r < RP; ++r) {
-      const int dx = dxg + r;
-      float o0 = 0.f, o1 = 0.f, o2 = 0.f;
-      const int x0 = a.xs[dx], xn = a.xc[dx];
-      for (int ky = 0; ky < yn; ++ky) {
-        const uint8_t* row = s + (size_t)(y0 + ky) * a.sw * 3;
-        float h0 = 0.f, h1 = 0.f, h2 = 0.f;
-        for (int kx = 0; kx < xn; ++kx) {
-          const float al = a.xa[dx * a.x_taps + kx];
-          const uint8_t* p = row + (size_t)(x0 + kx) * 3;
-          // unfused multiply/add on purpose: matches cv2's (and numpy's) float op order bit for bit
-          h0 = __fadd_rn(h0, __fmul_rn((float)p[0], al));
-          h1 = __fadd_rn(h1, __fmul_rn((float)p[1], al));
-          h2 = __fadd_rn(h2, __fmul_rn((float)p[2], al));
-        }
-        const float be = a.ya[dy * a.y_taps + ky];
-        o0 = __fadd_rn(o0, __fmul_rn(h0, be));
-        o1 = __fadd_rn(o1, __fmul_rn(h1, be));
-        o2 = __fadd_rn(o2, __fmul_rn(h2, be));
-      }
-      o[r * 3 + 0] = (uint8_t)min(max(__float2int_rn(o0), 0), 255);
-      o[r * 3 + 1] = (uint8_t)min(max(__float2int_rn(o1), 0), 255);
-      o[r * 3 + 2] = (uint8_t)min(max(__float2int_rn(o2), 0), 255);
-    }
-  } else if (a.mode == 1) {
-#pragma unroll
-    for (int r = 0; r < RP; ++r) {
-      const int dx = dxg + r;
-      int s0 = 0, s1 = 0, s2 = 0;
-      for (int ky = 0; ky < a.iy; ++ky) {
-        const uint8_t* row = s + ((size_t)(dy * a.iy + ky) * a.sw + (size_t)dx * a.ix) * 3;
-        for (int kx = 0; kx < a.ix; ++kx) {
-          s0 += row[kx * 3]; s1 += row[kx * 3 + 1]; s2 += row[kx * 3 + 2];
-        }
-      }
-      if (a.ix == 2 && a.iy == 2) {
-        o[r * 3] = (uint8_t)((s0 + 2) >> 2); o[r * 3 + 1] = (uint8_t)((s1 + 2) >> 2); o[r * 3 + 2] = (uint8_t)((s2 + 2) >> 2);
-      } else {
-        const float sc = 1.0f / (float)(a.ix * a.iy);
-        o[r * 3] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s0, sc)), 255);
-        o[r * 3 + 1] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s1, sc)), 255);
-        o[r * 3 + 2] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s2, sc)), 255);
-      }
-    }
+  extern __shared__ __align__(16) uint8_t rs_band[];
+  const int tid = threadIdx.x;
+  const int b = blockIdx.y;
+  const int dy0 = blockIdx.x * a.band;
+  const int dy1 = min(dy0 + a.band, a.dh) - 1;
+  const int row_bytes = a.sw * 3;
+  int r_lo, r_hi;
+  if (a.mode == 0) { r_lo = a.ys[dy0]; r_hi = a.ys[dy1] + a.yc[dy1] - 1; }
+  else if (a.mode == 1) { r_lo = dy0 * a.iy; r_hi = dy1 * a.iy + a.iy - 1; }
+  else { r_lo = a.ys[dy0]; r_hi = min(a.ys[dy1] + 1, a.sh - 1); }
+  r_hi = min(r_hi, a.sh - 1);
+  const uint8_t* frame = a.src + (size_t)b * a.src_stride;
+  const long long start = (long long)r_lo * row_bytes, end = (long long)(r_hi + 1) * row_bytes;
+  int skew = 0;
+  if (a.aligned) {
+    const long long start_al = start & ~15LL;
+    skew = (int)(start - start_al);
+    const int nvec = (int)((end - start_al + 15) >> 4);
+    const uint4* gsrc = reinterpret_cast<const uint4*>(frame + start_al);
+    uint4* sdst = reinterpret_cast<uint4*>(rs_band);
+    for (int i = tid; i < nvec; i += 256) sdst[i] = ldg_nc_v4(gsrc + i);
   } else {
-    const int sy0 = a.ys[dy], sy1 = min(sy0 + 1, a.sh - 1);
-    const int b0 = a.yq[dy * 2], b1 = a.yq[dy * 2 + 1];
-    const uint8_t* r0 = s + (size_t)sy0 * a.sw * 3;
-    const uint8_t* r1 = s + (size_t)sy1 * a.sw * 3;
-#pragma unroll
-    for (int r = 0; r < RP; ++r) {
-      const int dx = dxg + r;
-      const int sx0 = a.xs[dx], sx1 = min(sx0 + 1, a.sw - 1);
-      const int a0 = a.xq[dx * 2], a1 = a.xq[dx * 2 + 1];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
-        const int h1 = r1[sx0 * 3 + c] * a0 + r1[sx1 * 3 + c] * a1;
-        const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-        o[r * 3 + c] = (uint8_t)min(max(v, 0), 255);
-      }
-    }
+    for (int i = tid; i < (int)(end - start); i += 256) rs_band[i] = frame[start + i];
   }
-  if (RP == 4) {
-    uint32_t* d32 = reinterpret_cast<uint32_t*>(d);
+  __syncthreads();
+  const uint8_t* s = rs_band + skew;          // row y of the frame lives at s + (y - r_lo) * row_bytes
+  const int gw = a.dw / RP;
+  const int groups = (dy1 - dy0 + 1) * gw;
+  for (int g = tid; g < groups; g += 256) {
+    const int dy = dy0 + g / gw, dxg = (g % gw) * RP;
+    uint8_t* d = a.dst + (size_t)b * a.dst_stride + ((size_t)dy * a.dw + dxg) * 3;
+    uint8_t o[RP * 3];
+    if (a.mode == 0) {
+      const int y0 = a.ys[dy], yn = a.yc[dy];
 #pragma unroll
-    for (int k = 0; k < 3; ++k)
-      d32[k] = (uint32_t)o[4 * k] | ((uint32_t)o[4 * k + 1] << 8) | ((uint32_t)o[4 * k + 2] << 16) | ((uint32_t)o[4 * k + 3] << 24);
-  } else {
+      for (int r = 0; r < RP; ++r) {
+        const int dx = dxg + r;
+        float o0 = 0.f, o1 = 0.f, o2 = 0.f;
+        const int x0 = a.xs[dx], xn = a.xc[dx];
+        for (int ky = 0; ky < yn; ++ky) {
+          const uint8_t* row = s + (size_t)(y0 + ky - r_lo) * row_bytes;
+          float h0 = 0.f, h1 = 0.f, h2 = 0.f;
+          for (int kx = 0; kx < xn; ++kx) {
+            const float al = a.xa[dx * a.x_taps + kx];
+            const uint8_t* p = row + (size_t)(x0 + kx) * 3;
+            // unfused multiply/add on purpose: matches cv2's (and numpy's) float op order bit for bit
+            h0 = __fadd_rn(h0, __fmul_rn((float)p[0], al));
+            h1 = __fadd_rn(h1, __fmul_rn((float)p[1], al));
+            h2 = __fadd_rn(h2, __fmul_rn((float)p[2], al));
+          }
+          const float be = a.ya[dy * a.y_taps + ky];
+          o0 = __fadd_rn(o0, __fmul_rn(h0, be));
+          o1 = __fadd_rn(o1, __fmul_rn(h1, be));
+          o2 = __fadd_rn(o2, __fmul_rn(h2, be));
+        }
+        o[r * 3 + 0] = (uint8_t)min(max(__float2int_rn(o0), 0), 255);
+        o[r * 3 + 1] = (uint8_t)min(max(__float2int_rn(o1), 0), 255);
+        o[r * 3 + 2] = (uint8_t)min(max(__float2int_rn(o2), 0), 255);
+      }
+    } else if (a.mode == 1) {
 #pragma unroll
-    for (int k = 0; k < RP * 3; ++k) d[k] = o[k];
+      for (int r = 0; r < RP; ++r) {
+        const int dx = dxg + r;
+        int s0 = 0, s1 = 0, s2 = 0;
+        for (int ky = 0; ky < a.iy; ++ky) {
+          const uint8_t* row = s + (size_t)(dy * a.iy + ky - r_lo) * row_bytes + (size_t)dx * a.ix * 3;
+          for (int kx = 0; kx < a.ix; ++kx) {
+            s0 += row[kx * 3]; s1 += row[kx * 3 + 1]; s2 += row[kx * 3 + 2];
+          }
+        }
+        if (a.ix == 2 && a.iy == 2) {
+          o[r * 3] = (uint8_t)((s0 + 2) >> 2); o[r * 3 + 1] = (uint8_t)((s1 + 2) >> 2); o[r * 3 + 2] = (uint8_t)((s2 + 2) >> 2);
+        } else {
+          const float sc = 1.0f / (float)(a.ix * a.iy);
+          o[r * 3] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s0, sc)), 255);
+          o[r * 3 + 1] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s1, sc)), 255);
+          o[r * 3 + 2] = (uint8_t)min(__float2int_rn(__fmul_rn((float)s2, sc)), 255);
+        }
+      }
+    } else {
+      const int sy0 = a.ys[dy], sy1 = min(sy0 + 1, a.sh - 1);
+      const int b0 = a.yq[dy * 2], b1 = a.yq[dy * 2 + 1];
+      const uint8_t* r0 = s + (size_t)(sy0 - r_lo) * row_bytes;
+      const uint8_t* r1 = s + (size_t)(sy1 - r_lo) * row_bytes;
+#pragma unroll
+      for (int r = 0; r < RP; ++r) {
+        const int dx = dxg + r;
+        const int sx0 = a.xs[dx], sx1 = min(sx0 + 1, a.sw - 1);
+        const int a0 = a.xq[dx * 2], a1 = a.xq[dx * 2 + 1];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
+          const int h1 = r1[sx0 * 3 + c] * a0 + r1[sx1 * 3 + c] * a1;
+          const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+          o[r * 3 + c] = (uint8_t)min(max(v, 0), 255);
+        }
+      }
+    }
+    if (RP == 4) {
+      uint32_t* d32 = reinterpret_cast<uint32_t*>(d);
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        d32[k] = (uint32_t)o[4 * k] | ((uint32_t)o[4 * k + 1] << 8) | ((uint32_t)o[4 * k + 2] << 16) | ((uint32_t)o[4 * k + 3] << 24);
+    } else {
+#pragma unroll
+      for (int k = 0; k < RP * 3; ++k) d[k] = o[k];
+    }
   }
 }
 
@@ -321,11 +348,29 @@ extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int
   if (mode == 1) DVC_REQUIRE(ix > 0 && iy > 0 && dw * ix <= sw && dh * iy <= sh, "resize: bad integer ratio");
   if (mode == 2) DVC_REQUIRE(xs && ys && xq && yq, "resize: bilinear tables missing");
   ResizeArgs a{src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps,
-               ys, yc, ya, y_taps, xq, yq, ix, iy};
+               ys, yc, ya, y_taps, xq, yq, ix, iy, 1, 0};
+  a.aligned = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && src_frame_stride % 16 == 0) ? 1 : 0;
+  // band height: as many output rows as keep the staged source rows within ~64 KB of shared memory
+  const long long row_bytes = (long long)sw * 3;
+  const double sy = mode == 1 ? (double)iy : (double)sh / (double)dh;
+  int band = 16;
+  auto rows_for = [&](int bnd) { return (int)(bnd * sy + 0.999) + (mode == 0 ? y_taps : 2) + 1; };
+  while (band > 1 && (long long)rows_for(band) * row_bytes > 64 * 1024) band >>= 1;
+  a.band = band;
+  const long long smem = (long long)rows_for(band) * row_bytes + 64;
+  DVC_REQUIRE(smem <= 200 * 1024, "resize: one band of source rows (%lld bytes) does not fit shared memory", smem);
+  static bool attr_set[64] = {};
+  int dev = 0;
+  DVC_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(resize_u8_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(resize_u8_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set[dev & 63] = true;
+  }
   const bool vec4 = dw % 4 == 0 && dst_frame_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0;
-  const long long total = (long long)B * dh * (vec4 ? dw / 4 : dw);
-  if (vec4) resize_u8_kernel<4><<<(int)ceil_div64(total, 256), 256, 0, (cudaStream_t)stream>>>(a);
-  else resize_u8_kernel<1><<<(int)ceil_div64(total, 256), 256, 0, (cudaStream_t)stream>>>(a);
+  dim3 grid(ceil_div(dh, band), B);
+  if (vec4) resize_u8_kernel<4><<<grid, 256, (size_t)smem, (cudaStream_t)stream>>>(a);
+  else resize_u8_kernel<1><<<grid, 256, (size_t)smem, (cudaStream_t)stream>>>(a);
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;

@@ -131,3 +131,8 @@ def test_process_stream_matches_sync(engines):
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[3], b[3])
         for k in range(len(a[3])):                       # integer boxes: only the first box_count rows are defined
             assert np.array_equal(a[2][k, : a[3][k]], b[2][k, : b[3][k]])
+
+
+def test_graft_entry_smoke():
+    import __graft_entry__ as g
+    g.smoke()

@@ -192,3 +192,29 @@ def test_annotate_matches_cv2(K):
     for b in range(B):
         ref = A.annotate_cpu(frames[b].copy(), boxes[b, : counts[b]], rid, A.label_text({"person": int(counts[b])}))
         assert np.array_equal(out[b], ref), (b, int((out[b] != ref).sum()))
+
+
+def test_p2p_buffers_epoch_broadcast_and_weight_push(K):
+    """P2P substrate on one GPU: cudaMalloc'ed exportable buffers, K14 epoch word, K13 multicast push."""
+    import ctypes as C
+    from distributedvolunteercomputing_b200.ops import lib as L
+    from distributedvolunteercomputing_b200.parallel import p2p
+    lib = L.load()
+    bufs = [p2p.DevBuffer(4096, DEV) for _ in range(3)]
+    assert len(bufs[0].handle()) == 64
+    views = [b.tensor(torch.int32, (1024,)) for b in bufs]
+    assert all(int(v.abs().sum()) == 0 for v in views)                     # zero-initialised
+    ptrs = p2p.device_ptr_array([b.ptr + 16 for b in bufs], DEV)
+    L.check(lib.dvc_epoch_broadcast(ptrs.data_ptr(), 3, 7, L.stream_ptr()), "epoch")
+    src = torch.arange(1024, dtype=torch.int32, device=DEV)
+    wptrs = p2p.device_ptr_array([b.ptr + 1024 for b in bufs], DEV)
+    L.check(lib.dvc_push_multicast(src.data_ptr(), wptrs.data_ptr(), 3, 2048, L.stream_ptr()), "push")
+    sink = torch.zeros(1, dtype=torch.int32, device=DEV)
+    L.check(lib.dvc_peer_read(bufs[0].ptr, 4096, sink.data_ptr(), L.stream_ptr()), "peer_read")
+    torch.cuda.synchronize()
+    for v in views:
+        assert int(v[4]) == 7                                              # epoch word landed
+        assert torch.equal(v[256:768], src[:512])                          # 2048 bytes of weights landed
+        assert int(v[:4].abs().sum()) == 0 and int(v[768:].abs().sum()) == 0
+    for b in bufs:
+        b.free()
