@@ -8,6 +8,8 @@
 // (the only bytes that cross the link: ~1.06x the frame), resamples them in shared memory
 // with cv2's Q11 fixed-point bilinear arithmetic, applies (x - mean_c) * scale, and runs the
 // 3x3/s2 convolution + bias + ReLU from shared memory, writing NHWC fp16.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace dvc {
@@ -285,10 +287,212 @@ __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const Prep
   }
 }
 
+
+// ------------------------------------------------------------------------------- K1b on tensor cores
+// Same band decomposition and the same staging / resample / normalise phases as above, but the 3x3/s2
+// convolution is an implicit GEMM on tcgen05: per 128-pixel tile the threads gather the im2col rows
+// (K = 27 -> 32) as fp16 into a 128-byte-swizzled shared-memory A tile, one thread issues two
+// tcgen05.mma (M=128, N=32, K=16 each) against the [32 x 32] weight tile, and the fp32 accumulator
+// (32 TMEM columns, double buffered) is drained with tcgen05.ld -> bias -> ReLU -> fp16 NHWC stores
+// while the next tile is being gathered.
+constexpr int TC_A_BYTES = 128 * 128;     // 128 rows x 64 fp16 (only k < 32 is read)
+constexpr int TC_B_BYTES = 32 * 128;
+constexpr int TC_OFF_B = 0;                                   // 1024-aligned region first
+constexpr int TC_OFF_A = TC_OFF_B + TC_B_BYTES;               // 4096
+constexpr int TC_OFF_PATCH = TC_OFF_A + 2 * TC_A_BYTES;       // fp16 patch [17][301][3]
+constexpr int TC_PATCH_BYTES = ((PC_PROWS * PC_PCOLS * 3 * 2) + 15) & ~15;
+constexpr int TC_OFF_TAB = TC_OFF_PATCH + TC_PATCH_BYTES;     // xs[300], xq[600] ints
+constexpr int TC_OFF_BIAS = TC_OFF_TAB + 3 * PC_NET * 4;
+constexpr int TC_OFF_BAR = TC_OFF_BIAS + 32 * 4;              // 2 mbarriers + tmem slot
+constexpr int TC_OFF_BAND = (TC_OFF_BAR + 32 + 15) & ~15;
+
+__global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_tc_kernel(const PreprocArgs a) {
+  extern __shared__ uint8_t tc_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sB = smem + TC_OFF_B;
+  uint8_t* sA = smem + TC_OFF_A;
+  __half* s_patch = reinterpret_cast<__half*>(smem + TC_OFF_PATCH);
+  int* s_xs = reinterpret_cast<int*>(smem + TC_OFF_TAB);
+  int* s_xq = s_xs + PC_NET;
+  float* s_b = reinterpret_cast<float*>(smem + TC_OFF_BIAS);
+  uint64_t* mma_done = reinterpret_cast<uint64_t*>(smem + TC_OFF_BAR);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_done + 2);
+  uint8_t* s_band = smem + TC_OFF_BAND;
+
+  const int band = blockIdx.x, b = blockIdx.y;
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int oy0 = band * PC_BAND;
+  const int iy_first = max(2 * oy0 - 1, 0);
+  const int iy_last = min(2 * oy0 + 2 * PC_BAND - 1, PC_NET - 1);
+  const int slot = a.frame_index ? a.frame_index[a.slot0 + b] : a.slot0 + b;
+  const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
+  const int row_bytes = a.sw * 3;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_init(&mma_done[0], 1);
+      mbar_init(&mma_done[1], 1);
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 64);
+    tmem_relinquish();
+  }
+  // ---- stage the source rows this band needs (the NVLink pull when src is a peer pointer)
+  const int r_lo = a.ys[iy_first];
+  const int r_hi = min(a.ys[iy_last] + 1, a.sh - 1);
+  const long long start = (long long)r_lo * row_bytes;
+  const long long end = (long long)(r_hi + 1) * row_bytes;
+  const long long start_al = start & ~15LL;
+  const int skew = (int)(start - start_al);
+  const int nvec = (int)((end - start_al + 15) >> 4);
+  {
+    const uint4* gsrc = reinterpret_cast<const uint4*>(frame + start_al);
+    uint4* sdst = reinterpret_cast<uint4*>(s_band);
+    for (int i = tid; i < nvec; i += PC_THREADS) sdst[i] = ldg_nc_v4(gsrc + i);
+  }
+  if (tid < 32) s_b[tid] = a.b0[tid];
+  for (int i = tid; i < PC_NET; i += PC_THREADS) {
+    s_xs[i] = a.xs[i];
+    s_xq[2 * i] = a.xq[2 * i];
+    s_xq[2 * i + 1] = a.xq[2 * i + 1];
+  }
+  // weight tile: row n (output channel), 16-byte chunk j holds k = 8j..8j+7 (k >= 27 is zero), swizzled
+  if (tid < 32 * 4) {
+    const int n = tid >> 2, j = tid & 3;
+    uint32_t pk[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k0 = 8 * j + 2 * e, k1 = k0 + 1;
+      const float w0v = k0 < 27 ? a.w0[k0 * 32 + n] : 0.f;
+      const float w1v = k1 < 27 ? a.w0[k1 * 32 + n] : 0.f;
+      pk[e] = pack_half2(w0v, w1v);
+    }
+    sts_v4(smem_u32(sB) + (uint32_t)(n * 128 + ((j ^ (n & 7)) << 4)), make_uint4(pk[0], pk[1], pk[2], pk[3]));
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // ---- bilinear resample (cv2 Q11 fixed point) + normalise into the fp16 conv patch
+  const uint8_t* bandp = s_band + skew;
+  for (int i = tid; i < PC_PROWS * PC_PCOLS; i += PC_THREADS) {
+    const int pr = i / PC_PCOLS, pc = i - pr * PC_PCOLS;
+    const int iy = 2 * oy0 - 1 + pr, ix = pc - 1;
+    float v0 = 0.f, v1 = 0.f, v2 = 0.f;   // zero padding of the normalised blob (pad: 1)
+    if (iy >= 0 && iy < PC_NET && ix >= 0) {
+      const int sy0 = a.ys[iy], sy1 = min(sy0 + 1, a.sh - 1);
+      const int q0 = a.yq[2 * iy], q1 = a.yq[2 * iy + 1];
+      const int sx0 = s_xs[ix], sx1 = min(sx0 + 1, a.sw - 1);
+      const int a0 = s_xq[2 * ix], a1 = s_xq[2 * ix + 1];
+      const uint8_t* r0 = bandp + (size_t)(sy0 - r_lo) * row_bytes;
+      const uint8_t* r1 = bandp + (size_t)(sy1 - r_lo) * row_bytes;
+      int px[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
+        const int h1 = r1[sx0 * 3 + c] * a0 + r1[sx1 * 3 + c] * a1;
+        px[c] = min(max((((q0 * (h0 >> 4)) >> 16) + ((q1 * (h1 >> 4)) >> 16) + 2) >> 2, 0), 255);
+      }
+      v0 = __fmul_rn(__fsub_rn((float)px[0], a.mean0), a.scale);
+      v1 = __fmul_rn(__fsub_rn((float)px[1], a.mean1), a.scale);
+      v2 = __fmul_rn(__fsub_rn((float)px[2], a.mean2), a.scale);
+    }
+    s_patch[i * 3 + 0] = __float2half_rn(v0);
+    s_patch[i * 3 + 1] = __float2half_rn(v1);
+    s_patch[i * 3 + 2] = __float2half_rn(v2);
+  }
+  __syncthreads();
+
+  const int rows_here = min(PC_BAND, PC_OUT - oy0);
+  const int npix = rows_here * PC_OUT;
+  const int ntiles = (npix + 127) >> 7;
+  const uint32_t idesc = umma_idesc_f16(128, 32);
+  const int frow = tid & 127, fhalf = tid >> 7;      // gather: row of the A tile, which 16 k-values (warp-uniform)
+  const int q = warp & 3, chalf = warp >> 2;         // drain: TMEM lane quadrant, which 16 output channels
+
+  auto drain = [&](int t) {
+    mbar_wait(&mma_done[t & 1], (uint32_t)(t >> 1) & 1u);
+    tc_fence_after();
+    float v[16];
+    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((t & 1) * 32 + chalf * 16), v);
+    tmem_ld_wait();
+    const int pix = t * 128 + q * 32 + lane;
+    if (pix < npix) {
+      const int oy = pix / PC_OUT, ox = pix - oy * PC_OUT;
+      uint32_t pk[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        pk[j] = pack_half2(fmaxf(v[2 * j] + s_b[chalf * 16 + 2 * j], 0.f), fmaxf(v[2 * j + 1] + s_b[chalf * 16 + 2 * j + 1], 0.f));
+      uint4* dst = reinterpret_cast<uint4*>(a.out + (((size_t)b * PC_OUT + (oy0 + oy)) * PC_OUT + ox) * 32 + chalf * 16);
+      dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    }
+    tc_fence_before();
+  };
+
+  for (int t = 0; t < ntiles; ++t) {
+    // gather im2col rows of tile t (buffer t&1 was last read by the MMA of tile t-2, whose completion every
+    // thread observed when it drained tile t-2 in the previous iteration)
+    {
+      const int pix = t * 128 + frow;
+      uint32_t pk[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) pk[e] = 0u;
+      if (pix < npix) {
+        const int oy = pix / PC_OUT, ox = pix - oy * PC_OUT;
+        const __half* p0 = s_patch + ((2 * oy) * PC_PCOLS + 2 * ox) * 3;
+        if (fhalf == 0) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int k0 = 2 * e, k1 = 2 * e + 1;       // k = ky*9 + (kx*3+c)
+            const __half h0 = p0[(k0 / 9) * PC_PCOLS * 3 + (k0 % 9)];
+            const __half h1 = p0[(k1 / 9) * PC_PCOLS * 3 + (k1 % 9)];
+            pk[e] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int k0 = 16 + 2 * e, k1 = 17 + 2 * e;
+            const __half h0 = k0 < 27 ? p0[(k0 / 9) * PC_PCOLS * 3 + (k0 % 9)] : __ushort_as_half((unsigned short)0);
+            const __half h1 = k1 < 27 ? p0[(k1 / 9) * PC_PCOLS * 3 + (k1 % 9)] : __ushort_as_half((unsigned short)0);
+            pk[e] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+          }
+        }
+      }
+      const uint32_t abase = smem_u32(sA + (t & 1) * TC_A_BYTES) + (uint32_t)(frow * 128);
+      const int j0 = 2 * fhalf;
+      sts_v4(abase + (uint32_t)(((j0) ^ (frow & 7)) << 4), make_uint4(pk[0], pk[1], pk[2], pk[3]));
+      sts_v4(abase + (uint32_t)(((j0 + 1) ^ (frow & 7)) << 4), make_uint4(pk[4], pk[5], pk[6], pk[7]));
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint64_t a_desc = umma_desc_sw128(smem_u32(sA + (t & 1) * TC_A_BYTES));
+      const uint64_t b_desc = umma_desc_sw128(smem_u32(sB));
+      const uint32_t d_tmem = tmem_base + (uint32_t)((t & 1) * 32);
+      umma_f16(d_tmem, a_desc, b_desc, idesc, 0u);
+      umma_f16(d_tmem, a_desc + 2, b_desc + 2, idesc, 1u);
+      umma_commit(&mma_done[t & 1]);
+    }
+    if (t > 0) drain(t - 1);
+  }
+  if (ntiles > 0) drain(ntiles - 1);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 64);
+}
+
 struct PreprocLaunch {
   PreprocArgs args;
   dim3 grid;
   int smem;
+  int smem_tc;
+  bool use_tc;
 };
 
 int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B,
@@ -309,6 +513,9 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
   if (band_rows_max > sh) band_rows_max = sh;
   a.band_bytes = ((band_rows_max * sw * 3 + 31) & ~15) + 16;
   L->smem = PC_BAND_OFF + a.band_bytes;
+  L->smem_tc = TC_OFF_BAND + a.band_bytes + 1024;
+  const char* env = getenv("DVC_CONV0_CUDA_CORES");            // A/B switch: the fp32 CUDA-core variant
+  L->use_tc = !(env && env[0] == '1') && L->smem_tc <= 110 * 1024;
   DVC_REQUIRE(L->smem <= 227 * 1024, "preproc: source band of %d rows x %d px does not fit shared memory", band_rows_max, sw);
   L->grid = dim3((PC_OUT + PC_BAND - 1) / PC_BAND, B);
   return DVC_OK;
@@ -320,9 +527,11 @@ int preproc_launch(const PreprocLaunch* L, cudaStream_t st) {
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     attr_set[dev & 63] = true;
   }
-  preproc_conv0_kernel<<<L->grid, PC_THREADS, L->smem, st>>>(L->args);
+  if (L->use_tc) preproc_conv0_tc_kernel<<<L->grid, PC_THREADS, L->smem_tc, st>>>(L->args);
+  else preproc_conv0_kernel<<<L->grid, PC_THREADS, L->smem, st>>>(L->args);
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;

@@ -122,7 +122,7 @@ def test_preproc_conv0_matches_restatement(K, h4, mean):
     blobs = np.concatenate([P.blob_from_image(P.resize_linear_u8(f, 300, 300), mean) for f in frames])
     ref = F.relu(F.conv2d(torch.from_numpy(blobs), w, b, stride=2, padding=1)).permute(0, 2, 3, 1)
     err = (out.float().cpu() - ref).abs().max().item()
-    assert err <= 2e-3 * max(1.0, ref.abs().max().item()), err
+    assert err <= 4e-3 * max(1.0, ref.abs().max().item()), err   # fp16 im2col operands on the tensor-core path
 
 
 def test_preproc_frame_index_gathers_ring_slots(K):
