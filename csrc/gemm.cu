@@ -41,6 +41,7 @@ struct GemmArgs {
   const float* bias;
   int out_mode;        // 0: fp16 [M, ldc]   1: SSD head split store (fp32)
   int tma_store;       // out_mode 0 only: epilogue goes through smem + TMA store
+  int b_resident;      // whole weight matrix stays in smem (one N tile, few K blocks): loaded once per CTA
   __half* out;
   int ldc;
   int relu;
@@ -60,11 +61,13 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   float* sBias = reinterpret_cast<float*>(smem + EPI_SMEM);
   uint8_t* sA = smem + EPI_SMEM + BIAS_SMEM;
   uint8_t* sB = sA + g.stages * A_STAGE_BYTES;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + g.stages * b_stage_bytes);
+  const int b_tiles = g.b_resident ? g.num_kb : g.stages;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + b_tiles * b_stage_bytes);
   uint64_t* empty_bar = full_bar + g.stages;
   uint64_t* tmem_full_bar = empty_bar + g.stages;         // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;           // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  uint64_t* bres_bar = tmem_empty_bar + 2;                // weights resident
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_bar + 1);
 
   for (int i = threadIdx.x; i < g.N; i += GEMM_THREADS) sBias[i] = __ldg(g.bias + i);
   if (warp == 0 && lane == 0) {
@@ -82,6 +85,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         mbar_init(&tmem_full_bar[a], 1);
         mbar_init(&tmem_empty_bar[a], 4);     // one arrive per epilogue warp
       }
+      mbar_init(bres_bar, 1);
       fence_mbar_init();
     }
     __syncwarp();
@@ -96,7 +100,14 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (warp == 0) {
     // ------------------------------------------------------------- TMA producer
     if (elect_one()) {
-      const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + b_stage_bytes);
+      const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + (g.b_resident ? 0 : b_stage_bytes));
+      if (g.b_resident) {
+        // small weight matrices are fetched once: re-reading the same few KB from every SM for every tile
+        // hot-spots one L2 slice and starves the pipeline (measured on conv1: 38% of samples in the
+        // epilogue's wait for the accumulator)
+        mbar_arrive_expect_tx(bres_bar, (uint32_t)(g.num_kb * b_stage_bytes));
+        for (int kb = 0; kb < g.num_kb; ++kb) tma_load_2d(sB + kb * b_stage_bytes, &tmB, bres_bar, kb * BK, 0);
+      }
       int it = 0;
       for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
         const int n_tile = tile % g.n_tiles, m_tile = tile / g.n_tiles;
@@ -106,7 +117,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           mbar_wait(&empty_bar[s], ph ^ 1u);
           mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
           tma_load_2d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], kb * BK, m_tile * BM);
-          tma_load_2d(sB + s * b_stage_bytes, &tmB, &full_bar[s], kb * BK, n_tile * g.block_n);
+          if (!g.b_resident) tma_load_2d(sB + s * b_stage_bytes, &tmB, &full_bar[s], kb * BK, n_tile * g.block_n);
         }
       }
     }
@@ -115,6 +126,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ------------------------------------------------------------- MMA issuer
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_f16(BM, (uint32_t)g.block_n);
+      if (g.b_resident) mbar_wait(bres_bar, 0);
       int it = 0, t = 0;
       for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++t) {
         const int acc = t & 1;
@@ -127,7 +139,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           mbar_wait(&full_bar[s], ph);
           tc_fence_after();
           const uint64_t a_desc = umma_desc_sw128(smem_u32(sA + s * A_STAGE_BYTES));
-          const uint64_t b_desc = umma_desc_sw128(smem_u32(sB + s * b_stage_bytes));
+          const uint64_t b_desc = umma_desc_sw128(smem_u32(sB + (g.b_resident ? kb : s) * b_stage_bytes));
           int ksteps = (g.K - kb * BK + 15) / 16;
           ksteps = ksteps > 4 ? 4 : ksteps;
           for (int k = 0; k < ksteps; ++k) {
@@ -307,8 +319,10 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
   g.n_tiles = N / block_n;
   g.num_tiles = ceil_div(M, BM) * g.n_tiles;
   g.num_kb = ceil_div(K, BK);
-  const int stage_bytes = A_STAGE_BYTES + block_n * BK * 2;
-  const int fixed = EPI_SMEM + BIAS_SMEM + 1024 + 256;
+  const int b_tile_bytes = block_n * BK * 2;
+  g.b_resident = (g.n_tiles == 1 && g.num_kb * b_tile_bytes <= 64 * 1024 && g.num_tiles > 1) ? 1 : 0;
+  const int stage_bytes = A_STAGE_BYTES + (g.b_resident ? 0 : b_tile_bytes);
+  const int fixed = EPI_SMEM + BIAS_SMEM + 1024 + 256 + (g.b_resident ? g.num_kb * b_tile_bytes : 0);
   int stages = (GEMM_MAX_SMEM - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
   DVC_REQUIRE(stages >= 2, "gemm: tile does not fit shared memory");
