@@ -78,9 +78,10 @@ def make_linear_tables(sh: int, sw: int, dh: int, dw: int, device, area_mode: bo
 
 def resize_u8(src: torch.Tensor, t: ResizeTables, dst: Optional[torch.Tensor] = None, dst_frame_stride: int = 0,
               stream=None) -> torch.Tensor:
-    assert src.dtype == torch.uint8 and src.is_cuda and src.dim() == 4 and src.shape[3] == 3 and src.is_contiguous()
+    assert src.dtype == torch.uint8 and src.is_cuda and src.dim() == 4 and src.shape[3] == 3
     B = src.shape[0]
     assert (src.shape[1], src.shape[2]) == (t.sh, t.sw)
+    assert src.stride()[1:] == (t.sw * 3, 3, 1), "frames must be dense HWC (a frame pitch is allowed)"
     if dst is None:
         dst = torch.empty((B, t.dh, t.dw, 3), dtype=torch.uint8, device=src.device)
         dst_frame_stride = t.dh * t.dw * 3

@@ -14,6 +14,15 @@ one-element all-reduces per step that order "ring filled" -> "pull" and "rows pu
 no frame or detection bytes go through NCCL.  This replaces the reference's star relay, where every
 frame crosses TCP four times through the server (server.py:56,89,60,73).
 
+Two scatter modes:
+  * ``pull_raw`` (default): the client keeps only the RAW frame ring.  Every GPU's K1a resize pulls its
+    raw frames with coalesced peer loads (the scatter is fused into the resize; 270 KB per 300x300 frame
+    on the wire), runs the network locally, pushes its detection rows to the client (fused gather) and
+    overlays its own 400-wide frames, reading the integer boxes back from the client ring.  The client does
+    no per-frame work for the other GPUs, so throughput scales with the number of GPUs.
+  * ``pull_400``: the client resizes every frame to 400 wide; K1b on every GPU pulls from that ring
+    (scatter fused into resize-to-300 + normalise + conv0) and the client overlays all frames.
+
 `lanes` global batches are in flight at once: each lane has its own rings, plan, CUDA graph, stream
 and NCCL communicator, so the small latency-bound kernels of one global batch overlap the large
 kernels of the other on every GPU.
@@ -33,8 +42,14 @@ class _Lane:
     pass
 
 
+def p2p_align(n: int) -> int:
+    return (n + 15) & ~15
+
+
 class BoxCluster:
-    def __init__(self, engine, B: int, H: int, W: int, client_rank: int = 0, lanes: int = 2):
+    def __init__(self, engine, B: int, H: int, W: int, client_rank: int = 0, lanes: int = 2, mode: str = "pull_raw"):
+        assert mode in ("pull_raw", "pull_400")
+        self.mode = mode
         import torch.distributed as dist
         self.dist = dist
         self.engine = engine
@@ -50,6 +65,7 @@ class BoxCluster:
         # convenience aliases to lane 0 (single-lane users and tests)
         l0 = self.lanes[0]
         self.st = l0.st
+        self.frames400_local = l0.st.frames400          # pull_raw: this rank's annotated frames
         if self.is_client:
             self.raw_all, self.frames400, self.det, self.det_count = l0.raw_all, l0.frames400, l0.det, l0.det_count
             self.boxes_i, self.box_count, self.flags = l0.boxes_i, l0.box_count, l0.flags
@@ -61,9 +77,14 @@ class BoxCluster:
         ln.stream = torch.cuda.Stream(device=self.dev)
         st = eng.state(B, self.H, self.W, slot=200 + k)
         ln.st = st
-        bufs = {name: None for name in ("frames", "det", "det_count", "boxes", "box_count", "flags")}
+        raw_bytes = p2p_align(self.H * self.W * 3)
+        ln.raw_stride = raw_bytes
+        bufs = {name: None for name in ("frames", "raw", "det", "det_count", "boxes", "box_count", "flags")}
         if self.is_client:
-            bufs["frames"] = p2p.DevBuffer(n * st.stride400, self.dev)
+            if self.mode == "pull_400":
+                bufs["frames"] = p2p.DevBuffer(n * st.stride400, self.dev)
+            else:
+                bufs["raw"] = p2p.DevBuffer(n * raw_bytes, self.dev)
             bufs["det"] = p2p.DevBuffer(n * 700 * 4, self.dev)
             bufs["det_count"] = p2p.DevBuffer(n * 4, self.dev)
             bufs["boxes"] = p2p.DevBuffer(n * 400 * 4, self.dev)
@@ -73,16 +94,29 @@ class BoxCluster:
         ptrs = p2p.exchange(bufs, self.dev, None)
         c, r = self.client_rank, self.rank
         base = {name: ptrs[name][c] for name in bufs}
-        eng.bind_remote(st,
-                        frames_ptr=base["frames"] + r * B * st.stride400, frame_stride=st.stride400,
-                        det_ptr=base["det"] + r * B * 700 * 4, det_count_ptr=base["det_count"] + r * B * 4,
-                        boxes_ptr=base["boxes"] + r * B * 400 * 4, box_count_ptr=base["box_count"] + r * B * 4,
-                        flags_ptr=base["flags"] + r * B * 4, flag_value=1)
+        ln.base = base
+        sinks = dict(det_ptr=base["det"] + r * B * 700 * 4, det_count_ptr=base["det_count"] + r * B * 4,
+                     boxes_ptr=base["boxes"] + r * B * 400 * 4, box_count_ptr=base["box_count"] + r * B * 4,
+                     flags_ptr=base["flags"] + r * B * 4, flag_value=1)
+        if self.mode == "pull_400":
+            eng.bind_remote(st, frames_ptr=base["frames"] + r * B * st.stride400, frame_stride=st.stride400, **sinks)
+        else:
+            eng.bind_remote(st, frames_ptr=L.ptr(st.frames400_flat), frame_stride=st.stride400, **sinks)
+            # this rank's slice of the client's raw ring, as a tensor the resize kernel reads over NVLink
+            ln.raw_mine = p2p.tensor_from_ptr(base["raw"] + r * B * raw_bytes, (B, raw_bytes), torch.uint8, self.dev)
+            ln.raw_mine = torch.as_strided(ln.raw_mine, (B, self.H, self.W, 3), (raw_bytes, self.W * 3, 3, 1))
+            ln.my_boxes = p2p.tensor_from_ptr(sinks["boxes_ptr"], (B, 100, 4), torch.int32, self.dev)
+            ln.my_box_count = p2p.tensor_from_ptr(sinks["box_count_ptr"], (B,), torch.int32, self.dev)
         ln.tok = torch.zeros(1, device=self.dev)
         if self.is_client:
-            ln.raw_all = torch.zeros((n, self.H, self.W, 3), dtype=torch.uint8, device=self.dev)
-            ln.frames_flat = bufs["frames"].tensor(torch.uint8, (n, st.stride400))
-            ln.frames400 = torch.as_strided(ln.frames_flat, (n, st.h4, st.w4, 3), (st.stride400, st.w4 * 3, 3, 1))
+            if self.mode == "pull_400":
+                ln.raw_all = torch.zeros((n, self.H, self.W, 3), dtype=torch.uint8, device=self.dev)
+                ln.frames_flat = bufs["frames"].tensor(torch.uint8, (n, st.stride400))
+                ln.frames400 = torch.as_strided(ln.frames_flat, (n, st.h4, st.w4, 3), (st.stride400, st.w4 * 3, 3, 1))
+            else:
+                flat = bufs["raw"].tensor(torch.uint8, (n, raw_bytes))
+                ln.raw_all = torch.as_strided(flat, (n, self.H, self.W, 3), (raw_bytes, self.W * 3, 3, 1))
+                ln.frames_flat, ln.frames400 = None, None      # annotated frames stay on the GPU that produced them
             ln.det = bufs["det"].tensor(torch.float32, (n, 100, 7))
             ln.det_count = bufs["det_count"].tensor(torch.int32, (n,))
             ln.boxes_i = bufs["boxes"].tensor(torch.int32, (n, 100, 4))
@@ -93,21 +127,36 @@ class BoxCluster:
     def lane_of(self, step_index: int) -> _Lane:
         return self.lanes[step_index % len(self.lanes)]
 
+    def _annotate(self, ln: _Lane, frames_flat, n_frames: int, boxes, counts):
+        st = ln.st
+        m = st.masks
+        nl, lh, lw = m.label_masks.shape
+        idh, idw = m.id_mask.shape
+        L.check(self.engine.lib.dvc_annotate(L.ptr(frames_flat), st.stride400, None, n_frames, st.h4, st.w4,
+                                             L.ptr(boxes), L.ptr(counts), None, L.ptr(m.id_mask), m.id_xy[0], m.id_xy[1],
+                                             idw, idh, L.ptr(m.label_masks), nl, m.label_xy[0], m.label_xy[1], lw, lh,
+                                             L.stream_ptr()), "annotate")
+
     def _run_lane(self, ln: _Lane, raw_all: Optional[torch.Tensor], annotate: bool):
         st = ln.st
-        if self.is_client:
-            K.resize_u8(ln.raw_all if raw_all is None else raw_all, st.t_area, ln.frames_flat, st.stride400)
-        self.dist.all_reduce(ln.tok, group=ln.group)          # ring filled -> everyone may pull (stream-ordered)
-        self.engine.run(st, annotate=False, resize=False)
-        self.dist.all_reduce(ln.tok, group=ln.group)          # rows pushed -> the client may draw
-        if self.is_client and annotate:
-            m = st.masks
-            nl, lh, lw = m.label_masks.shape
-            idh, idw = m.id_mask.shape
-            L.check(self.engine.lib.dvc_annotate(L.ptr(ln.frames_flat), st.stride400, None, self.n, st.h4, st.w4,
-                                                 L.ptr(ln.boxes_i), L.ptr(ln.box_count), None, L.ptr(m.id_mask), m.id_xy[0],
-                                                 m.id_xy[1], idw, idh, L.ptr(m.label_masks), nl, m.label_xy[0], m.label_xy[1],
-                                                 lw, lh, L.stream_ptr()), "annotate")
+        L.set_device(self.dev)
+        if self.mode == "pull_400":
+            if self.is_client:
+                K.resize_u8(ln.raw_all if raw_all is None else raw_all, st.t_area, ln.frames_flat, st.stride400)
+            self.dist.all_reduce(ln.tok, group=ln.group)      # ring filled -> everyone may pull (stream-ordered)
+            self.engine.run(st, annotate=False, resize=False)
+            self.dist.all_reduce(ln.tok, group=ln.group)      # rows pushed -> the client may draw
+            if self.is_client and annotate:
+                self._annotate(ln, ln.frames_flat, self.n, ln.boxes_i, ln.box_count)
+        else:
+            if self.is_client and raw_all is not None and raw_all.data_ptr() != ln.raw_all.data_ptr():
+                ln.raw_all.copy_(raw_all, non_blocking=True)  # frames enter the client's raw ring
+            self.dist.all_reduce(ln.tok, group=ln.group)      # raw ring filled -> everyone may pull
+            K.resize_u8(ln.raw_mine, st.t_area, st.frames400_flat, st.stride400)     # K1a: peer loads = the scatter
+            self.engine.run(st, annotate=False, resize=False)                        # rows pushed to the client (gather)
+            if annotate:
+                self._annotate(ln, st.frames400_flat, self.B, ln.my_boxes, ln.my_box_count)
+            self.dist.all_reduce(ln.tok, group=ln.group)      # every rank's rows have landed -> the client may read
 
     def step(self, raw_all: Optional[torch.Tensor] = None, annotate: bool = True, overlap: bool = False) -> _Lane:
         """One global batch: world*B frames (on the client GPU) -> detections + annotated frames on the
@@ -131,6 +180,6 @@ class BoxCluster:
 
     def launches_per_step(self) -> int:
         n = self.st.n_ops
-        if self.is_client:
+        if self.mode == "pull_raw" or self.is_client:
             n += 2
         return n

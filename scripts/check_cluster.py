@@ -14,9 +14,9 @@ dev = f"cuda:{local}"
 dist.init_process_group("nccl", device_id=torch.device(dev))
 B, H, W = 8, 240, 320
 graph = SSDGraph.random(seed=1, conf_gain=2.5)
-for use_graph in (False, True):
+for use_graph, mode in ((False, "pull_400"), (True, "pull_400"), (False, "pull_raw"), (True, "pull_raw")):
     eng = NativeEngine(graph, dev, Config(batch=B, sub_batch=4, use_cuda_graph=use_graph), requester_id="127.0.0.1:5554")
-    cl = BoxCluster(eng, B, H, W, client_rank=0)
+    cl = BoxCluster(eng, B, H, W, client_rank=0, mode=mode)
     rng = np.random.default_rng(7)
     frames = torch.from_numpy(rng.integers(0, 256, (world * B, H, W, 3), dtype=np.uint8))
     for it in range(3):
@@ -25,8 +25,11 @@ for use_graph in (False, True):
         cl.step()
         torch.cuda.synchronize()
         dist.barrier()
+    ref = NativeEngine(graph, dev, Config(batch=B, sub_batch=4, use_cuda_graph=False), requester_id="127.0.0.1:5554")
+    if mode == "pull_raw":      # annotated frames stay on the GPU that produced them
+        mine = ref.process(frames[rank * B:(rank + 1) * B]).numpy()
+        assert np.array_equal(mine.frames400, cl.frames400_local.cpu().numpy()), (use_graph, mode, rank, "local frames400")
     if rank == 0:
-        ref = NativeEngine(graph, dev, Config(batch=B, sub_batch=4, use_cuda_graph=False), requester_id="127.0.0.1:5554")
         for r in range(world):
             out = ref.process(frames[r * B:(r + 1) * B]).numpy()
             sl = slice(r * B, (r + 1) * B)
@@ -34,9 +37,10 @@ for use_graph in (False, True):
             assert np.array_equal(out.det_count, cl.det_count[sl].cpu().numpy()), (use_graph, r, "det_count")
             assert np.array_equal(out.boxes_i[:, :1], cl.boxes_i[sl, :1].cpu().numpy()) or True
             assert np.array_equal(out.box_count, cl.box_count[sl].cpu().numpy()), (use_graph, r, "box_count")
-            assert np.array_equal(out.frames400, cl.frames400[sl].cpu().numpy()), (use_graph, r, "frames400")
+            if mode == "pull_400":
+                assert np.array_equal(out.frames400, cl.frames400[sl].cpu().numpy()), (use_graph, r, "frames400")
             assert (cl.flags[sl] == 1).all()
         assert int(cl.det_count.sum()) > 0
-        print(f"cluster check ok: world={world} graph={use_graph} detections={int(cl.det_count.sum())}", flush=True)
+        print(f"cluster check ok: world={world} mode={mode} graph={use_graph} detections={int(cl.det_count.sum())}", flush=True)
     dist.barrier()
 dist.destroy_process_group()
