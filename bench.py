@@ -171,7 +171,7 @@ def run_native(args):
             for i in range(n):
                 yield host_pool[i % POOL]
 
-        depth = max(2, conc) + 1
+        depth = max(2, conc) + 2
         for r in eng.process_stream(host_batches(max(4, min(args.warmup, 6))), depth=depth):
             pass
         barrier()

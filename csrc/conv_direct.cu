@@ -160,30 +160,50 @@ __global__ void __launch_bounds__(256) dw3x3_tma_kernel(const __grid_constant__ 
   const float4 b1 = __ldg(reinterpret_cast<const float4*>(a.bias + c0 + 4));
   mbar_wait(&bar, 0);
   const uint32_t tile_s = smem_u32(tile) + (uint32_t)(cg * 16);
-  const int npix = a.TX * a.TY;
-  for (int p = pt; p < npix; p += pxt) {
-    const int oy = p / a.TX, ox = p - oy * a.TX;
+  // Work item = two horizontally adjacent outputs: they share STRIDE+3 input columns per kernel row, so a
+  // pair costs 3*(STRIDE+3) shared-memory loads instead of 18, and carries 16 independent accumulators.
+  constexpr int NC = STRIDE + 3;
+  const int ppr = (a.TX + 1) >> 1;
+  const int npairs = ppr * a.TY;
+  for (int p = pt; p < npairs; p += pxt) {
+    const int oy = p / ppr, ox = (p - oy * ppr) * 2;
     const int gx = tx * a.TX + ox, gy = ty * a.TY + oy;
     if (gx >= a.Wo || gy >= a.Ho) continue;
-    float acc[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    const bool two = (ox + 1 < a.TX) && (gx + 1 < a.Wo);
+    float acc0[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    float acc1[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky) {
+      uint4 v[NC];
+      const int rowbase = (oy * STRIDE + ky) * a.BW;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        const int col = min(ox * STRIDE + c, a.BW - 1);
+        v[c] = lds_v4(tile_s + (uint32_t)((rowbase + col) * a.CT * 2));
+      }
 #pragma unroll
       for (int kx = 0; kx < 3; ++kx) {
-        const uint4 v = lds_v4(tile_s + (uint32_t)(((oy * STRIDE + ky) * a.BW + ox * STRIDE + kx) * a.CT * 2));
         const int t = ky * 3 + kx;
-        fhfma2(acc[0], acc[1], v.x, wq[t][0]);
-        fhfma2(acc[2], acc[3], v.y, wq[t][1]);
-        fhfma2(acc[4], acc[5], v.z, wq[t][2]);
-        fhfma2(acc[6], acc[7], v.w, wq[t][3]);
+        fhfma2(acc0[0], acc0[1], v[kx].x, wq[t][0]);
+        fhfma2(acc0[2], acc0[3], v[kx].y, wq[t][1]);
+        fhfma2(acc0[4], acc0[5], v[kx].z, wq[t][2]);
+        fhfma2(acc0[6], acc0[7], v[kx].w, wq[t][3]);
+        fhfma2(acc1[0], acc1[1], v[STRIDE + kx].x, wq[t][0]);
+        fhfma2(acc1[2], acc1[3], v[STRIDE + kx].y, wq[t][1]);
+        fhfma2(acc1[4], acc1[5], v[STRIDE + kx].z, wq[t][2]);
+        fhfma2(acc1[6], acc1[7], v[STRIDE + kx].w, wq[t][3]);
       }
     }
     if (a.relu) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
+      for (int j = 0; j < 8; ++j) { acc0[j] = fmaxf(acc0[j], 0.f); acc1[j] = fmaxf(acc1[j], 0.f); }
     }
-    *reinterpret_cast<uint4*>(a.out + (((size_t)n * a.Ho + gy) * a.Wo + gx) * a.C + c0) =
-        make_uint4(pack_half2(acc[0], acc[1]), pack_half2(acc[2], acc[3]), pack_half2(acc[4], acc[5]), pack_half2(acc[6], acc[7]));
+    __half* o = a.out + (((size_t)n * a.Ho + gy) * a.Wo + gx) * a.C + c0;
+    *reinterpret_cast<uint4*>(o) =
+        make_uint4(pack_half2(acc0[0], acc0[1]), pack_half2(acc0[2], acc0[3]), pack_half2(acc0[4], acc0[5]), pack_half2(acc0[6], acc0[7]));
+    if (two)
+      *reinterpret_cast<uint4*>(o + a.C) =
+          make_uint4(pack_half2(acc1[0], acc1[1]), pack_half2(acc1[2], acc1[3]), pack_half2(acc1[4], acc1[5]), pack_half2(acc1[6], acc1[7]));
   }
 }
 
