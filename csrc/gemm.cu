@@ -18,6 +18,8 @@
 // and stores of several tiles in flight per SM, which is what the producer run-ahead and the
 // bulk-async stores are for.
 // Reference op: cv2.dnn Convolution layers, prototxt:76-106 ... 1083-1113, 1147-1775.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace dvc {
@@ -41,6 +43,8 @@ struct GemmArgs {
   const float* bias;
   int out_mode;        // 0: fp16 [M, ldc]   1: SSD head split store (fp32)
   int tma_store;       // out_mode 0 only: epilogue goes through smem + TMA store
+  int cluster;         // CTAs per cluster along M sharing one multicast weight tile (1, 2 or 4)
+  int m_tiles, num_ctiles;
   int b_resident;      // whole weight matrix stays in smem (one N tile, few K blocks): loaded once per CTA
   __half* out;
   int ldc;
@@ -79,7 +83,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (lane == 0) {
       for (int s = 0; s < g.stages; ++s) {
         mbar_init(&full_bar[s], 1);
-        mbar_init(&empty_bar[s], 1);
+        mbar_init(&empty_bar[s], (uint32_t)g.cluster);    // every CTA of the cluster must have drained the stage
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
@@ -93,9 +97,13 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     tmem_relinquish();
   }
   tc_fence_before();
-  __syncthreads();
+  if (g.cluster > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // cluster-tile schedule: a cluster walks (m-group, n-tile) pairs; CTA rank r owns m-tile group*cluster + r
+  const int crank = g.cluster > 1 ? (int)cluster_ctarank() : 0;
+  const int cluster_id = blockIdx.x / g.cluster, num_clusters = gridDim.x / g.cluster;
+  const uint16_t cmask = (uint16_t)((1u << g.cluster) - 1u);
 
   if (warp == 0) {
     // ------------------------------------------------------------- TMA producer
@@ -109,15 +117,22 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int kb = 0; kb < g.num_kb; ++kb) tma_load_2d(sB + kb * b_stage_bytes, &tmB, bres_bar, kb * BK, 0);
       }
       int it = 0;
-      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
-        const int n_tile = tile % g.n_tiles, m_tile = tile / g.n_tiles;
+      const int slice_rows = g.block_n / g.cluster, slice_bytes = b_stage_bytes / g.cluster;
+      for (int ct = cluster_id; ct < g.num_ctiles; ct += num_clusters) {
+        const int n_tile = ct % g.n_tiles, m_tile = (ct / g.n_tiles) * g.cluster + crank;
         for (int kb = 0; kb < g.num_kb; ++kb, ++it) {
           const int s = it % g.stages;
           const uint32_t ph = (uint32_t)(it / g.stages) & 1u;
           mbar_wait(&empty_bar[s], ph ^ 1u);
           mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
           tma_load_2d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], kb * BK, m_tile * BM);
-          if (!g.b_resident) tma_load_2d(sB + s * b_stage_bytes, &tmB, &full_bar[s], kb * BK, n_tile * g.block_n);
+          if (g.cluster > 1) {
+            // this CTA fetches 1/cluster of the weight tile and multicasts it to every CTA of the cluster
+            tma_load_2d_mcast(sB + s * b_stage_bytes + crank * slice_bytes, &tmB, &full_bar[s], kb * BK,
+                              n_tile * g.block_n + crank * slice_rows, cmask);
+          } else if (!g.b_resident) {
+            tma_load_2d(sB + s * b_stage_bytes, &tmB, &full_bar[s], kb * BK, n_tile * g.block_n);
+          }
         }
       }
     }
@@ -128,7 +143,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const uint32_t idesc = umma_idesc_f16(BM, (uint32_t)g.block_n);
       if (g.b_resident) mbar_wait(bres_bar, 0);
       int it = 0, t = 0;
-      for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++t) {
+      for (int ct = cluster_id; ct < g.num_ctiles; ct += num_clusters, ++t) {
         const int acc = t & 1;
         mbar_wait(&tmem_empty_bar[acc], (((uint32_t)t >> 1) & 1u) ^ 1u);   // epilogue has drained this buffer
         tc_fence_after();
@@ -146,7 +161,8 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             // advance 16 fp16 = 32 bytes along K inside the 128-byte swizzle atom (+2 in 16-byte units)
             umma_f16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
           }
-          umma_commit(&empty_bar[s]);          // frees this smem stage once the MMAs above retire
+          // frees this smem stage (in every CTA of the cluster: peers multicast into it) once the MMAs retire
+          if (g.cluster > 1) umma_commit_mcast(&empty_bar[s], cmask); else umma_commit(&empty_bar[s]);
         }
         umma_commit(&tmem_full_bar[acc]);      // accumulator complete -> epilogue
       }
@@ -162,9 +178,9 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint8_t* my_epi = sEpi + (grp * 4 + q) * 2 * EPI_BUF_BYTES;
     int chunk_it = 0;
     for (int t = grp; ; t += 2) {
-      const int tile = blockIdx.x + t * gridDim.x;
-      if (tile >= g.num_tiles) break;
-      const int n_tile = tile % g.n_tiles, m_tile = tile / g.n_tiles;
+      const int ct = cluster_id + t * num_clusters;
+      if (ct >= g.num_ctiles) break;
+      const int n_tile = ct % g.n_tiles, m_tile = (ct / g.n_tiles) * g.cluster + crank;
       const int acc = grp;
       const int n0 = n_tile * g.block_n;
       const int row0 = m_tile * BM + q * 32;
@@ -257,7 +273,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (g.cluster > 1) cluster_sync_all(); else __syncthreads();   // peers may still multicast into / arrive on this CTA
   if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)g.tmem_cols);
 }
 
@@ -320,7 +336,19 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
   g.num_tiles = ceil_div(M, BM) * g.n_tiles;
   g.num_kb = ceil_div(K, BK);
   const int b_tile_bytes = block_n * BK * 2;
+  g.m_tiles = ceil_div(M, BM);
   g.b_resident = (g.n_tiles == 1 && g.num_kb * b_tile_bytes <= 64 * 1024 && g.num_tiles > 1) ? 1 : 0;
+  // Optional clusters along M sharing one multicast weight tile (DVC_GEMM_CLUSTER=2|4).  Measured on B200:
+  // no gain for these shapes (conv7: 24.5 us with 1, 2 or 4 CTAs per cluster) - the main loop is limited by
+  // how many K blocks fit in shared memory (3 stages of 48 KB at block_n=256 cover ~1500 cycles of MMA, less
+  // than the TMA round trip), not by L2 bandwidth, and multicast does not shrink the per-CTA tile.  Off by default.
+  int cluster = 1;
+  if (const char* env = getenv("DVC_GEMM_CLUSTER")) {
+    const int c = atoi(env);
+    if ((c == 1 || c == 2 || c == 4) && !(g.b_resident && c > 1) && (block_n / c) % 8 == 0 && g.m_tiles >= c) cluster = c;
+  }
+  g.cluster = cluster;
+  g.num_ctiles = ceil_div(g.m_tiles, cluster) * g.n_tiles;
   const int stage_bytes = A_STAGE_BYTES + (g.b_resident ? 0 : b_tile_bytes);
   const int fixed = EPI_SMEM + BIAS_SMEM + 1024 + 256 + (g.b_resident ? g.num_kb * b_tile_bytes : 0);
   int stages = (GEMM_MAX_SMEM - fixed) / stage_bytes;
@@ -338,11 +366,13 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
   g.relu = relu;
   if (head) g.head = *head; else g.head = dvc_head_out{};
   const int sms = num_sms();
-  L->grid = g.num_tiles < sms ? g.num_tiles : sms;
+  int num_clusters = (cluster == 4 ? 132 : sms) / cluster;      // 4-CTA clusters cannot use every SM (GPC shapes)
+  if (g.num_ctiles < num_clusters) num_clusters = g.num_ctiles;
+  L->grid = num_clusters * cluster;
   L->smem = g.stages * stage_bytes + fixed;
   int rc = make_tmap_2d_f16(&L->tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
   if (rc) return rc;
-  rc = make_tmap_2d_f16(&L->tmB, Wt, (uint64_t)N, (uint64_t)K, (uint64_t)K, (uint32_t)block_n, BK);
+  rc = make_tmap_2d_f16(&L->tmB, Wt, (uint64_t)N, (uint64_t)K, (uint64_t)K, (uint32_t)(block_n / cluster), BK);
   if (rc) return rc;
   if (g.tma_store) {
     rc = make_tmap_2d_f16(&L->tmC, out, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 32, EPI_CHUNK);
@@ -361,7 +391,23 @@ int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(gemm_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_MAX_SMEM));
     attr_set[dev & 63] = true;
   }
-  gemm_f16_kernel<<<L->grid, GEMM_THREADS, L->smem, st>>>(L->tmA, L->tmB, L->tmC, L->args);
+  if (L->args.cluster > 1) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(L->grid);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = (size_t)L->smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)L->args.cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DVC_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_f16_kernel, L->tmA, L->tmB, L->tmC, L->args));
+  } else {
+    gemm_f16_kernel<<<L->grid, GEMM_THREADS, L->smem, st>>>(L->tmA, L->tmB, L->tmC, L->args);
+  }
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
