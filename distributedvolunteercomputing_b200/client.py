@@ -24,7 +24,7 @@ import numpy as np
 
 from . import protocol as proto
 from .config import Config
-from .session import FrameSource, JobTracker, VideoSink
+from .session import FrameSource, JobJournal, JobTracker, VideoSink
 from .utils.metrics import Logger, Metrics
 
 
@@ -181,7 +181,8 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
                 continue
 
     # ------------------------------------------------------------------ requester role
-    def become_requester(self, path: str):
+    def become_requester(self, path: str, resume: bool = False):
+        self._resume = resume
         reply = proto.control_roundtrip(self.send_sock, self.server_address, proto.make_control("request", self.my_ip),
                                         retry_s=self.cfg.control_retry_s, log=lambda m: print(m, flush=True))
         if reply != "ok":
@@ -201,6 +202,7 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
         numbers: List[int] = []
         k = self.cfg.number_of_frames_in_chunk
         started = False
+        skip_to = 0
         it = iter(src)
         if self.cfg.compat_drop_first:
             next(it, None)                                     # reference reads frame 0 only to size the writer
@@ -209,10 +211,15 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
                 break
             if not started:
                 sink = VideoSink(self.cfg, frame.shape[0], frame.shape[1], self.out_dir, self.path_out_num)
+                jpath = sink.path + ".journal"
+                skip_to = JobJournal.load(jpath) if getattr(self, "_resume", False) else 0
                 self.path_out_num += 1
-                self.tracker = JobTracker(sink, first_frame=1, out=lambda m: print(m, flush=True))
+                self.tracker = JobTracker(sink, first_frame=skip_to + 1, out=lambda m: print(m, flush=True),
+                                          journal=JobJournal(jpath))
                 started = True
             frame_number += 1
+            if frame_number <= skip_to:          # already written by the interrupted run (journal)
+                continue
             if chunk and frame.shape != chunk[0].shape:
                 self._send_request_chunk(numbers, chunk)
                 chunk, numbers = [], []

@@ -113,11 +113,43 @@ class VideoSink:
             self.writer = None
 
 
+class JobJournal:
+    """Tiny resume journal (the reference persists nothing, SURVEY §5 "Checkpoint / resume"): one JSON line
+    with the last frame number that has been written contiguously.  A restarted requester skips those
+    frames (`client.become_requester(path, resume=True)`), so only the unwritten tail is re-sent."""
+
+    def __init__(self, path: str, every: int = 32):
+        self.path = path
+        self.every = max(1, every)
+        self._since = 0
+
+    @staticmethod
+    def load(path: str) -> int:
+        try:
+            with open(path) as f:
+                import json
+                return int(json.loads(f.read().strip() or "{}").get("last_contiguous_frame", 0))
+        except (OSError, ValueError):
+            return 0
+
+    def record(self, last_frame: int, force: bool = False):
+        self._since += 1
+        if not force and self._since < self.every:
+            return
+        self._since = 0
+        import json
+        tmp = self.path + ".tmp"
+        with open(tmp, "w") as f:
+            f.write(json.dumps({"last_contiguous_frame": int(last_frame), "t": time.time()}))
+        os.replace(tmp, self.path)
+
+
 class JobTracker:
     """Reorders processed frames, writes them, and reports the job time exactly like the
     reference prints it."""
 
-    def __init__(self, sink: Optional[VideoSink], first_frame: int = 1, out=print):
+    def __init__(self, sink: Optional[VideoSink], first_frame: int = 1, out=print, journal: Optional[JobJournal] = None):
+        self.journal = journal
         self.sink = sink
         self.reorder = ReorderBuffer(first_frame)
         self.final_sent_frame: Optional[int] = None
@@ -137,6 +169,8 @@ class JobTracker:
                 self.sink.write(item[0])
             if item[1] is not None:
                 self.counts.append(item[1])
+            if self.journal is not None:
+                self.journal.record(k)
         self._maybe_finish()
 
     def _maybe_finish(self):
@@ -146,5 +180,7 @@ class JobTracker:
             self.finished = True
             self.job_seconds = time.time() - self.start_time
             self.out("final frame time taken for the job = " + str(self.job_seconds))
+            if self.journal is not None:
+                self.journal.record(self.reorder.next - 1, force=True)
             if self.sink is not None:
                 self.sink.release()

@@ -137,3 +137,26 @@ def test_idempotent_join_and_compat_drop_modes(tmp_path):
         w.exit_threads(); r.exit_threads()
     finally:
         srv.exit_threads()
+
+
+def test_job_journal_and_resume(tmp_path):
+    from distributedvolunteercomputing_b200.session import JobJournal, JobTracker
+    j = JobJournal(str(tmp_path / "video0.mp4.journal"), every=4)
+    tr = JobTracker(None, first_frame=1, out=lambda m: None, journal=j)
+    for n in (2, 1, 3, 4, 5):
+        tr.push(n, np.zeros((2, 2, 3), np.uint8))
+    assert JobJournal.load(j.path) in (4, 5)          # flushed every 4 contiguous frames
+    tr.set_final(5)
+    assert tr.finished and JobJournal.load(j.path) == 5
+    tr2 = JobTracker(None, first_frame=JobJournal.load(j.path) + 1, out=lambda m: None)
+    assert tr2.reorder.next == 6
+    assert JobJournal.load(str(tmp_path / "missing.journal")) == 0
+
+
+def test_trace_span_records_metrics():
+    from distributedvolunteercomputing_b200.utils.metrics import Metrics
+    from distributedvolunteercomputing_b200.utils.trace import span
+    m = Metrics()
+    with span("batch", m, n=3):
+        time.sleep(0.01)
+    assert m.percentile("batch_ms", 50) >= 5.0
