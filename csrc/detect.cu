@@ -35,9 +35,18 @@ __global__ void priorbox_kernel(float* boxes, float* variances, int prior_off, i
 }
 
 // ------------------------------------------------------------------------------ K7/K8/K9
-constexpr int DET_THREADS = 672;    // 21 warps: one per class for the NMS phase
+// Three launches, all sized to the whole GPU instead of one CTA per frame:
+//   K7  softmax_kernel        thread per prior: 21-way softmax, probabilities written class-major to scratch
+//   K8  class_nms_kernel      CTA per (frame, class): threshold -> compaction -> rank-by-counting top_k ->
+//                             CENTER_SIZE decode -> IoU bit-matrix -> greedy pass over the bit rows;
+//                             survivors (sorted) go to scratch
+//   K9  merge_deliver_kernel  CTA per frame: global keep_top_k by binary search across the per-class sorted
+//                             lists, application filter, rows staged in shared memory and written - possibly
+//                             to a peer GPU - followed by a release.sys flag (the detection gather)
 constexpr int DET_MAXC = 32;      // classes
 constexpr int DET_MAXK = 128;     // per-class top_k capacity
+constexpr int NMS_THREADS = 128;
+constexpr int MERGE_THREADS = 256;
 
 struct DetArgs {
   const float *loc, *conf, *priors, *variances;
@@ -46,19 +55,9 @@ struct DetArgs {
   const int* slot_index;
   float* det; int* det_count; int* boxes_i; int* box_count;
   uint32_t* flags; uint32_t flag_value;
-  float* pool_score; int* pool_idx; long long pool_stride;   // global scratch, per frame
+  // global scratch (per frame): prob [C][P], kept_n [C], kept_score [C][K], kept_idx [C][K], kept_box [C][K][4]
+  float* prob; int* kept_n; float* kept_score; int* kept_idx; float* kept_box;
 };
-
-__device__ __forceinline__ void softmax_row(const float* __restrict__ x, int C, float* prob) {
-  float m = x[0];
-  for (int c = 1; c < C; ++c) m = fmaxf(m, x[c]);
-  float s = 0.f;
-  for (int c = 0; c < C; ++c) {
-    prob[c] = expf(__fsub_rn(x[c], m));
-    s = __fadd_rn(s, prob[c]);
-  }
-  for (int c = 0; c < C; ++c) prob[c] = __fdiv_rn(prob[c], s);
-}
 
 __device__ __forceinline__ bool before(float sa, int ia, int ca, float sb, int ib, int cb) {
   // strict total order: score desc, prior index asc, class asc
@@ -78,80 +77,90 @@ __device__ __forceinline__ float box_iou(const float* a, const float* b) {
   return __fdiv_rn(inter, __fsub_rn(__fadd_rn(box_area(a), box_area(b)), inter));
 }
 
-__global__ void __launch_bounds__(DET_THREADS) detection_kernel(const DetArgs a) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  const int C = a.p.num_classes, P = a.p.num_priors, K = a.p.top_k;
-  int* s_cnt = reinterpret_cast<int*>(smem);           // [DET_MAXC] candidates per class
-  int* s_off = s_cnt + DET_MAXC;                       // [DET_MAXC+1]
-  int* s_fill = s_off + DET_MAXC + 1;                  // [DET_MAXC]
-  int* s_nsel = s_fill + DET_MAXC;                     // [DET_MAXC]
-  int* s_misc = s_nsel + DET_MAXC;                     // [0]=n_kept  [1]=n_boxes
-  float* sel_score = reinterpret_cast<float*>(s_misc + 7);      // [C][DET_MAXK]
-  int* sel_idx = reinterpret_cast<int*>(sel_score + C * DET_MAXK);
-  float* sel_box = reinterpret_cast<float*>(sel_idx + C * DET_MAXK);   // [C][DET_MAXK][4]
-  uint8_t* sel_keep = reinterpret_cast<uint8_t*>(sel_box + C * DET_MAXK * 4);
-  int* kept = reinterpret_cast<int*>(sel_keep + ((C * DET_MAXK + 15) & ~15));   // [C*DET_MAXK] (c<<16 | r)
-  float* s_rows = reinterpret_cast<float*>(kept + C * DET_MAXK);                // [100][7] output staging
-
-  const int f = blockIdx.x;
-  const int tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31;
-  const float* loc = a.loc + (size_t)f * P * 4;
-  const float* conf = a.conf + (size_t)f * P * C;
-  float* pool_score = a.pool_score + (size_t)f * a.pool_stride;
-  int* pool_idx = a.pool_idx + (size_t)f * a.pool_stride;
-  const int slot = a.slot_index ? a.slot_index[f] : f;
-
-  if (tid < DET_MAXC) { s_cnt[tid] = 0; s_fill[tid] = 0; s_nsel[tid] = 0; }
-  if (tid < 2) s_misc[tid] = 0;
-  __syncthreads();
-
-  // ---- phase 1: softmax, count candidates per class
-  float prob[DET_MAXC];
-  for (int i = tid; i < P; i += DET_THREADS) {
-    softmax_row(conf + (size_t)i * C, C, prob);
-    for (int c = 0; c < C; ++c)
-      if (c != a.p.background && prob[c] > a.p.conf_thresh) atomicAdd(&s_cnt[c], 1);
-  }
-  __syncthreads();
-  if (tid == 0) {
-    int acc = 0;
-    for (int c = 0; c < C; ++c) { s_off[c] = acc; acc += s_cnt[c]; }
-    s_off[C] = acc;
-  }
-  __syncthreads();
-  // ---- phase 2: fill the per-class candidate pool (global scratch: worst case P*(C-1) entries)
-  for (int i = tid; i < P; i += DET_THREADS) {
-    softmax_row(conf + (size_t)i * C, C, prob);
-    for (int c = 0; c < C; ++c)
-      if (c != a.p.background && prob[c] > a.p.conf_thresh) {
-        const int pos = s_off[c] + atomicAdd(&s_fill[c], 1);
-        pool_score[pos] = prob[c];
-        pool_idx[pos] = i;
-      }
-  }
-  __syncthreads();
-  // ---- phase 3: per-class rank by counting; ranks < top_k are selected in sorted position
-  const int total = s_off[C];
-  for (int e = tid; e < total; e += DET_THREADS) {
-    int c = 0;
-    while (e >= s_off[c + 1]) ++c;
-    const float s = pool_score[e];
-    const int id = pool_idx[e];
-    int rank = 0;
-    for (int j = s_off[c]; j < s_off[c + 1]; ++j) rank += before(pool_score[j], pool_idx[j], 0, s, id, 0) ? 1 : 0;
-    if (rank < K) {
-      sel_score[c * DET_MAXK + rank] = s;
-      sel_idx[c * DET_MAXK + rank] = id;
+__global__ void __launch_bounds__(256) softmax_kernel(const DetArgs a) {
+  const int C = a.p.num_classes, P = a.p.num_priors;
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)a.B * P) return;
+  const int f = (int)(idx / P), i = (int)(idx - (long long)f * P);
+  const float* x = a.conf + ((size_t)f * P + i) * C;
+  float m = x[0];
+  for (int c = 1; c < C; ++c) m = fmaxf(m, x[c]);
+  float e[DET_MAXC];
+  float s = 0.f;
+#pragma unroll
+  for (int c = 0; c < DET_MAXC; ++c) {
+    if (c < C) {
+      e[c] = expf(__fsub_rn(x[c], m));
+      s = __fadd_rn(s, e[c]);
     }
   }
-  if (tid < C) s_nsel[tid] = min(s_cnt[tid], K);
+  float* out = a.prob + (size_t)f * C * P + i;
+#pragma unroll
+  for (int c = 0; c < DET_MAXC; ++c)
+    if (c < C) out[(size_t)c * P] = __fdiv_rn(e[c], s);
+}
+
+__global__ void __launch_bounds__(NMS_THREADS) class_nms_kernel(const DetArgs a) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int C = a.p.num_classes, P = a.p.num_priors, K = a.p.top_k;
+  const int c = blockIdx.x, f = blockIdx.y;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int P_pad = (P + 3) & ~3;                               // keeps the float4 regions below 16-byte aligned
+  float* cs = reinterpret_cast<float*>(smem);                   // [P] candidate scores
+  int* ci = reinterpret_cast<int*>(cs + P_pad);                 // [P] candidate prior indices
+  float* sel_score = reinterpret_cast<float*>(ci + P_pad);      // [DET_MAXK] sorted
+  int* sel_idx = reinterpret_cast<int*>(sel_score + DET_MAXK);
+  float* sel_box = reinterpret_cast<float*>(sel_idx + DET_MAXK);       // [DET_MAXK][4]
+  uint32_t* mask = reinterpret_cast<uint32_t*>(sel_box + DET_MAXK * 4);  // [DET_MAXK][4]: later boxes this one suppresses
+  uint32_t* keepw = mask + DET_MAXK * 4;                        // [4] survivor bits
+  __shared__ int s_warp[NMS_THREADS / 32 + 1];
+  __shared__ int s_n;
+
+  int* kept_n = a.kept_n + (size_t)f * C;
+  if (c == a.p.background) {
+    if (tid == 0) kept_n[c] = 0;
+    return;
+  }
+  const float* prob = a.prob + ((size_t)f * C + c) * P;
+  // ---- compaction of priors above the confidence threshold (stable: ascending prior index)
+  int base = 0;
+  for (int i0 = 0; i0 < P; i0 += NMS_THREADS) {
+    const int i = i0 + tid;
+    const float sc = i < P ? prob[i] : 0.f;
+    const bool ok = i < P && sc > a.p.conf_thresh;
+    const unsigned bal = __ballot_sync(0xffffffff, ok);
+    if (lane == 0) s_warp[warp] = __popc(bal);
+    __syncthreads();
+    int off = base;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+    if (ok) {
+      const int pos = off + __popc(bal & ((1u << lane) - 1));
+      cs[pos] = sc;
+      ci[pos] = i;
+    }
+    int tot = 0;
+    for (int w = 0; w < NMS_THREADS / 32; ++w) tot += s_warp[w];
+    base += tot;
+    __syncthreads();
+  }
+  const int n_c = base;
+  // ---- rank by counting; ranks < top_k land in sorted position
+  for (int e = tid; e < n_c; e += NMS_THREADS) {
+    const float s = cs[e];
+    const int id = ci[e];
+    int rank = 0;
+    for (int j = 0; j < n_c; ++j) rank += before(cs[j], ci[j], 0, s, id, 0) ? 1 : 0;
+    if (rank < K) {
+      sel_score[rank] = s;
+      sel_idx[rank] = id;
+    }
+  }
+  const int n = min(n_c, K);
   __syncthreads();
-  // ---- phase 4: decode the selected boxes (CENTER_SIZE, variance not encoded, no clip)
-  for (int e = tid; e < C * K; e += DET_THREADS) {
-    const int c = e / K, r = e - c * K;
-    if (r >= s_nsel[c]) continue;
-    const int i = sel_idx[c * DET_MAXK + r];
+  // ---- decode the selected boxes (CENTER_SIZE, variance not encoded, no clip)
+  const float* loc = a.loc + (size_t)f * P * 4;
+  if (tid < n) {
+    const int i = sel_idx[tid];
     const float4 pr = *reinterpret_cast<const float4*>(a.priors + (size_t)i * 4);
     const float4 va = *reinterpret_cast<const float4*>(a.variances + (size_t)i * 4);
     const float4 l = *reinterpret_cast<const float4*>(loc + (size_t)i * 4);
@@ -161,86 +170,108 @@ __global__ void __launch_bounds__(DET_THREADS) detection_kernel(const DetArgs a)
     const float cy = __fadd_rn(__fmul_rn(__fmul_rn(va.y, l.y), ph), pcy);
     const float w = __fmul_rn(expf(__fmul_rn(va.z, l.z)), pw);
     const float h = __fmul_rn(expf(__fmul_rn(va.w, l.w)), ph);
-    float* bx = sel_box + (size_t)(c * DET_MAXK + r) * 4;
+    float* bx = sel_box + tid * 4;
     bx[0] = __fsub_rn(cx, __fmul_rn(w, 0.5f));
     bx[1] = __fsub_rn(cy, __fmul_rn(h, 0.5f));
     bx[2] = __fadd_rn(cx, __fmul_rn(w, 0.5f));
     bx[3] = __fadd_rn(cy, __fmul_rn(h, 0.5f));
-    sel_keep[c * DET_MAXK + r] = 1;
   }
   __syncthreads();
-  // ---- phase 5: greedy NMS, one warp per class; a kept box suppresses every later box it overlaps
-  for (int c = warp; c < C; c += DET_THREADS / 32) {
-    const int n = s_nsel[c];
-    for (int i = 0; i < n; ++i) {
-      __syncwarp();
-      if (!sel_keep[c * DET_MAXK + i]) continue;   // warp-uniform (shared memory value)
-      const float* bi = sel_box + (size_t)(c * DET_MAXK + i) * 4;
-      for (int r = i + 1 + lane; r < n; r += 32) {
-        if (sel_keep[c * DET_MAXK + r] && box_iou(bi, sel_box + (size_t)(c * DET_MAXK + r) * 4) > a.p.nms_thresh)
-          sel_keep[c * DET_MAXK + r] = 0;
+  // ---- IoU bit matrix: row i has bit j set when j > i overlaps i by more than the NMS threshold
+  if (tid < DET_MAXK) {
+    uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+    if (tid < n) {
+      const float* bi = sel_box + tid * 4;
+      for (int j = tid + 1; j < n; ++j) {
+        if (box_iou(bi, sel_box + j * 4) > a.p.nms_thresh) {
+          const uint32_t bit = 1u << (j & 31);
+          if (j < 32) m0 |= bit; else if (j < 64) m1 |= bit; else if (j < 96) m2 |= bit; else m3 |= bit;
+        }
       }
     }
+    mask[tid * 4 + 0] = m0; mask[tid * 4 + 1] = m1; mask[tid * 4 + 2] = m2; mask[tid * 4 + 3] = m3;
   }
   __syncthreads();
-  // ---- phase 6: global keep_top_k.  Survivors of one class are already in rank order, so the global
-  // rank of an entry is the sum over classes of "survivors of that class that sort before it": a
-  // binary search per class over its sorted list plus an exclusive prefix count of the keep flags.
-  int* kprefix = kept;                                   // [C][DET_MAXK] survivors among r' < r
-  for (int c = warp; c < C; c += DET_THREADS / 32) {
-    const int n = s_nsel[c];
+  // ---- greedy pass (one thread, pure bit operations): a kept box removes every later box it suppresses
+  if (tid == 0) {
+    uint32_t alive[4];
+    for (int w = 0; w < 4; ++w) {
+      const int lo = w * 32;
+      alive[w] = n >= lo + 32 ? 0xffffffffu : (n > lo ? ((1u << (n - lo)) - 1u) : 0u);
+    }
     int cnt = 0;
-    int flags4[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int r = lane * 4 + k;
-      flags4[k] = (r < n && sel_keep[c * DET_MAXK + r]) ? 1 : 0;
-      cnt += flags4[k];
+    for (int i = 0; i < n; ++i) {
+      if ((alive[i >> 5] >> (i & 31)) & 1u) {
+        ++cnt;
+        alive[0] &= ~mask[i * 4 + 0]; alive[1] &= ~mask[i * 4 + 1];
+        alive[2] &= ~mask[i * 4 + 2]; alive[3] &= ~mask[i * 4 + 3];
+      }
     }
-    int incl = cnt;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const int up = __shfl_up_sync(0xffffffff, incl, d);
-      if (lane >= d) incl += up;
-    }
-    int run = incl - cnt;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      kprefix[c * DET_MAXK + lane * 4 + k] = run;
-      run += flags4[k];
-    }
-    if (lane == 31) s_fill[c] = incl;                    // survivors of class c (s_fill is free by now)
+    for (int w = 0; w < 4; ++w) keepw[w] = alive[w];
+    s_n = cnt;
+  }
+  __syncthreads();
+  // ---- survivors, still in sorted order, to scratch
+  if (tid < n && ((keepw[tid >> 5] >> (tid & 31)) & 1u)) {
+    int pos = 0;
+    for (int w = 0; w < (tid >> 5); ++w) pos += __popc(keepw[w]);
+    pos += __popc(keepw[tid >> 5] & ((1u << (tid & 31)) - 1u));
+    const size_t o = ((size_t)f * C + c) * DET_MAXK + pos;
+    a.kept_score[o] = sel_score[tid];
+    a.kept_idx[o] = sel_idx[tid];
+    *reinterpret_cast<float4*>(a.kept_box + o * 4) = *reinterpret_cast<const float4*>(sel_box + tid * 4);
+  }
+  if (tid == 0) kept_n[c] = s_n;
+}
+
+__global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetArgs a) {
+  __shared__ int s_n[DET_MAXC];
+  __shared__ int s_tot;
+  __shared__ float s_rows[DVC_MAX_DET * DVC_DET_ROW];
+  extern __shared__ __align__(16) uint8_t msm[];          // survivor scores / indices staged for the binary searches
+  const int C = a.p.num_classes;
+  float* ks = reinterpret_cast<float*>(msm);              // [C][DET_MAXK]
+  int* ki = reinterpret_cast<int*>(ks + C * DET_MAXK);    // [C][DET_MAXK]
+  const int f = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int slot = a.slot_index ? a.slot_index[f] : f;
+  const int* kept_n = a.kept_n + (size_t)f * C;
+  const float* gks = a.kept_score + (size_t)f * C * DET_MAXK;
+  const int* gki = a.kept_idx + (size_t)f * C * DET_MAXK;
+  const float* kb = a.kept_box + (size_t)f * C * DET_MAXK * 4;
+  if (tid < DET_MAXC) s_n[tid] = tid < C ? kept_n[tid] : 0;
+  for (int e = tid; e < DVC_MAX_DET * DVC_DET_ROW; e += MERGE_THREADS) s_rows[e] = 0.f;
+  __syncthreads();
+  for (int e = tid; e < C * DET_MAXK; e += MERGE_THREADS) {
+    const int c = e / DET_MAXK, r = e - c * DET_MAXK;
+    if (r < s_n[c]) { ks[e] = gks[e]; ki[e] = gki[e]; }
   }
   __syncthreads();
   if (tid == 0) {
-    int tot = 0;
-    for (int c = 0; c < C; ++c) tot += s_fill[c];
-    s_misc[0] = tot;
+    int t = 0;
+    for (int c = 0; c < C; ++c) t += s_n[c];
+    s_tot = t;
   }
-  for (int e = tid; e < DVC_MAX_DET * DVC_DET_ROW; e += DET_THREADS) s_rows[e] = 0.f;
   __syncthreads();
-  const int n_kept = s_misc[0];
-  const int n_out = min(n_kept, min(a.p.keep_top_k, DVC_MAX_DET));
-  for (int e = tid; e < C * K; e += DET_THREADS) {
-    const int c = e / K, r = e - c * K;
-    if (r >= s_nsel[c] || !sel_keep[c * DET_MAXK + r]) continue;
-    const float s = sel_score[c * DET_MAXK + r];
-    const int id = sel_idx[c * DET_MAXK + r];
+  const int n_out = min(s_tot, min(a.p.keep_top_k, DVC_MAX_DET));
+  // global rank of a survivor = sum over classes of survivors that sort before it (binary search per class)
+  for (int e = tid; e < C * DET_MAXK; e += MERGE_THREADS) {
+    const int c = e / DET_MAXK, r = e - c * DET_MAXK;
+    if (r >= s_n[c]) continue;
+    const float s = ks[c * DET_MAXK + r];
+    const int id = ki[c * DET_MAXK + r];
     int rank = 0;
     for (int c2 = 0; c2 < C; ++c2) {
-      const int n2 = s_nsel[c2];
-      if (n2 == 0) continue;
-      int lo = 0, hi = n2;                               // first index whose entry does NOT sort before (s,id,c)
+      int lo = 0, hi = s_n[c2];
       while (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        if (before(sel_score[c2 * DET_MAXK + mid], sel_idx[c2 * DET_MAXK + mid], c2, s, id, c)) lo = mid + 1;
+        if (before(ks[c2 * DET_MAXK + mid], ki[c2 * DET_MAXK + mid], c2, s, id, c)) lo = mid + 1;
         else hi = mid;
       }
-      rank += lo == n2 ? s_fill[c2] : kprefix[c2 * DET_MAXK + lo];
+      rank += lo;
     }
     if (rank < n_out) {
       float* row = s_rows + rank * DVC_DET_ROW;
-      const float* bx = sel_box + (size_t)(c * DET_MAXK + r) * 4;
+      const float* bx = kb + (size_t)(c * DET_MAXK + r) * 4;
       row[0] = 0.f; row[1] = (float)c; row[2] = s;
       row[3] = bx[0]; row[4] = bx[1]; row[5] = bx[2]; row[6] = bx[3];
     }
@@ -248,8 +279,8 @@ __global__ void __launch_bounds__(DET_THREADS) detection_kernel(const DetArgs a)
   __syncthreads();
   // rows (zero padded) go out with coalesced stores; `det` may be peer memory (the gather)
   float* det = a.det + (size_t)slot * DVC_MAX_DET * DVC_DET_ROW;
-  for (int e = tid; e < DVC_MAX_DET * DVC_DET_ROW; e += DET_THREADS) det[e] = s_rows[e];
-  // ---- phase 7: application filter (conf > 0.2, class in CONSIDER) -> integer boxes, in row order
+  for (int e = tid; e < DVC_MAX_DET * DVC_DET_ROW; e += MERGE_THREADS) det[e] = s_rows[e];
+  // application filter (conf > 0.2, class in CONSIDER) -> integer boxes, in row order
   if (warp == 0) {
     int base = 0;
     int* bi = a.boxes_i + (size_t)slot * DVC_MAX_DET * 4;
@@ -275,7 +306,7 @@ __global__ void __launch_bounds__(DET_THREADS) detection_kernel(const DetArgs a)
       a.det_count[slot] = n_out;
     }
   }
-  // ---- delivery: make the rows visible system-wide, then publish the slot flag
+  // delivery: make the rows visible system-wide, then publish the slot flag
   __threadfence_system();
   __syncthreads();
   if (tid == 0 && a.flags) st_release_sys_u32(a.flags + slot, a.flag_value);
@@ -283,10 +314,19 @@ __global__ void __launch_bounds__(DET_THREADS) detection_kernel(const DetArgs a)
 
 struct DetLaunch {
   DetArgs args;
-  int smem;
+  int smem_nms;
 };
 
-size_t det_scratch_bytes(int B, int P, int C) { return (size_t)B * P * (C > 1 ? C - 1 : 1) * 8; }
+static size_t det_per_frame_bytes(int P, int C) {
+  // prob [C][P] f32 + kept_n [C] + kept_score/idx [C][K] + kept_box [C][K][4], each region 16-byte aligned
+  size_t b = 0;
+  b += (((size_t)C * P * 4) + 15) & ~size_t(15);
+  b += (((size_t)C * 4) + 15) & ~size_t(15);
+  b += (size_t)C * DET_MAXK * 4 * 2;
+  b += (size_t)C * DET_MAXK * 16;
+  return b;
+}
+size_t det_scratch_bytes(int B, int P, int C) { return (size_t)B * det_per_frame_bytes(P, C); }
 
 int det_prepare(DetLaunch* L, const float* loc, const float* conf, const float* priors, const float* variances, int B,
                 const dvc_det_params* p, const int* slot_index, float* det, int* det_count, int* boxes_i, int* box_count,
@@ -295,19 +335,27 @@ int det_prepare(DetLaunch* L, const float* loc, const float* conf, const float* 
   DVC_REQUIRE(p->num_classes >= 2 && p->num_classes <= DET_MAXC, "detection: num_classes=%d unsupported (max %d)", p->num_classes, DET_MAXC);
   DVC_REQUIRE(p->top_k > 0 && p->top_k <= DET_MAXK, "detection: top_k=%d unsupported (max %d)", p->top_k, DET_MAXK);
   DVC_REQUIRE(p->keep_top_k > 0, "detection: keep_top_k must be positive");
-  DVC_REQUIRE(p->num_priors > 0 && p->num_priors < 65536, "detection: num_priors=%d unsupported", p->num_priors);
+  DVC_REQUIRE(p->num_priors > 0 && p->num_priors <= 8192, "detection: num_priors=%d unsupported (max 8192)", p->num_priors);
   const size_t need = det_scratch_bytes(B, p->num_priors, p->num_classes);
   DVC_REQUIRE(scratch != nullptr && scratch_bytes >= need, "detection: scratch %zu bytes < required %zu", scratch_bytes, need);
   DVC_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 15) == 0, "detection: scratch must be 16-byte aligned");
+  DVC_REQUIRE((reinterpret_cast<uintptr_t>(loc) & 15) == 0 && (reinterpret_cast<uintptr_t>(priors) & 15) == 0 &&
+              (reinterpret_cast<uintptr_t>(variances) & 15) == 0, "detection: loc/priors/variances must be 16-byte aligned");
   DetArgs& a = L->args;
   a.loc = loc; a.conf = conf; a.priors = priors; a.variances = variances; a.B = B; a.p = *p; a.slot_index = slot_index;
   a.det = det; a.det_count = det_count; a.boxes_i = boxes_i; a.box_count = box_count; a.flags = flags; a.flag_value = flag_value;
-  const long long per = (long long)p->num_priors * (p->num_classes - 1);
-  a.pool_stride = per;
-  a.pool_score = reinterpret_cast<float*>(scratch);
-  a.pool_idx = reinterpret_cast<int*>(reinterpret_cast<float*>(scratch) + (size_t)B * per);
-  const int C = p->num_classes;
-  L->smem = (4 * DET_MAXC + 1 + 7) * 4 + C * DET_MAXK * (4 + 4 + 16) + ((C * DET_MAXK + 15) & ~15) + C * DET_MAXK * 4 + DVC_MAX_DET * DVC_DET_ROW * 4 + 64;
+  const int C = p->num_classes, P = p->num_priors;
+  uint8_t* s = reinterpret_cast<uint8_t*>(scratch);
+  a.prob = reinterpret_cast<float*>(s);
+  s += (size_t)B * ((((size_t)C * P * 4) + 15) & ~size_t(15));
+  a.kept_n = reinterpret_cast<int*>(s);
+  s += (size_t)B * ((((size_t)C * 4) + 15) & ~size_t(15));
+  a.kept_score = reinterpret_cast<float*>(s);
+  s += (size_t)B * C * DET_MAXK * 4;
+  a.kept_idx = reinterpret_cast<int*>(s);
+  s += (size_t)B * C * DET_MAXK * 4;
+  a.kept_box = reinterpret_cast<float*>(s);
+  L->smem_nms = ((P + 3) & ~3) * 8 + DET_MAXK * (4 + 4 + 16 + 16) + 16 + 64;
   return DVC_OK;
 }
 
@@ -316,11 +364,15 @@ int det_launch(const DetLaunch* L, cudaStream_t st) {
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    DVC_CHECK_CUDA(cudaFuncSetAttribute(detection_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(class_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_set[dev & 63] = true;
   }
-  detection_kernel<<<L->args.B, DET_THREADS, L->smem, st>>>(L->args);
-  count_launch();
+  const DetArgs& a = L->args;
+  const long long n = (long long)a.B * a.p.num_priors;
+  softmax_kernel<<<(int)ceil_div64(n, 256), 256, 0, st>>>(a);
+  class_nms_kernel<<<dim3(a.p.num_classes, a.B), NMS_THREADS, L->smem_nms, st>>>(a);
+  merge_deliver_kernel<<<a.B, MERGE_THREADS, a.p.num_classes * DET_MAXK * 8, st>>>(a);
+  count_launch(3);
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
 }
@@ -455,7 +507,8 @@ extern "C" int dvc_detection_output(const float* loc, const float* conf, const f
 }
 
 // ---- allocation-free variant of dvc_detection_output -------------------------------------
-// The candidate pool lives in this file-scope device array instead of caller memory.  Every
+// The detection scratch (class-major probabilities and the per-class survivor lists) lives in this
+// file-scope device array instead of caller memory.  Every
 // GPU that loads the library carries these 4 MiB until the process exits.  In host code the
 // symbol below is only a stand-in: its device address is looked up once per device with
 // cudaGetSymbolAddress (with that device current) and that address is what the kernel gets.
@@ -487,7 +540,7 @@ extern "C" int dvc_detection_output_static(const float* loc, const float* conf, 
   DVC_REQUIRE(p && B > 0, "detection (static scratch): bad arguments");
   const size_t need = det_scratch_bytes(B, p->num_priors, p->num_classes);
   DVC_REQUIRE(need <= (size_t)DVC_DET_STATIC_SCRATCH_BYTES,
-              "detection (static scratch): B=%d x %d priors x %d classes needs %zu bytes of candidate pool, the built-in "
+              "detection (static scratch): B=%d x %d priors x %d classes needs %zu bytes of scratch, the built-in "
               "pool holds %zu; split the batch or use dvc_detection_output with your own scratch",
               B, p->num_priors, p->num_classes, need, (size_t)DVC_DET_STATIC_SCRATCH_BYTES);
   void* scratch = nullptr;

@@ -279,7 +279,7 @@ class NativeEngine:
 
     # ------------------------------------------------------------------ execution
     def launches_per_batch(self, st: _ShapeState, annotate: bool = True) -> int:
-        return st.n_ops + 1 + (1 if annotate else 0)   # plan ops + K1a resize + K10 annotate
+        return st.n_ops + 2 + 1 + (1 if annotate else 0)   # plan ops (detection = 3 kernels) + K1a resize + K10 annotate
 
     def _enqueue_resize(self, st: _ShapeState, src: Optional[torch.Tensor] = None):
         """K1a: raw frames (st.raw, or any other device batch of the same shape) -> 400-wide ring."""

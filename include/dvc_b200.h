@@ -109,10 +109,11 @@ int dvc_priorbox(float* boxes, float* variances, int prior_off, int grid_h, int 
  *   boxes_i  [B][100][4] int32 app-filtered boxes scaled by (out_w,out_h) and truncated
  *   box_count[B]               number of app-filtered boxes ("person: N")
  * slot_index (optional) maps batch entry -> output slot.
- * `scratch` is caller-provided global memory for the per-class candidate pool (worst case
- * every prior passes the threshold in every foreground class, which cannot fit in shared
- * memory): dvc_detection_scratch_bytes(B, priors, classes) bytes, 16-byte aligned.  Its
- * contents are fully rewritten by every call; concurrent calls must not share it. */
+ * Three launches: a softmax pass, one CTA per (frame, class) for top-k + NMS, one CTA per frame for
+ * the global top-k, the filter and the delivery.
+ * `scratch` is caller-provided global memory that carries the class-major probabilities and the
+ * per-class survivor lists between those launches: dvc_detection_scratch_bytes(B, priors, classes)
+ * bytes, 16-byte aligned.  Every call rewrites what it reads; concurrent calls must not share it. */
 typedef struct {
   int num_priors, num_classes, background;
   float conf_thresh, nms_thresh;
@@ -134,21 +135,21 @@ int dvc_detection_output(const float* loc, const float* conf, const float* prior
  * Who it is for: embedders that cannot hand this library any device memory beyond the inputs
  * and outputs - a volunteer's host application that reserved the whole GPU in its own pool at
  * start-up, a capture loop that cannot afford the device-wide stall of cudaMalloc/cudaFree, or
- * a plugin host written in C with no allocator to lend.  For them the per-class candidate pool
+ * a plugin host written in C with no allocator to lend.  For them the detection scratch
  * sits in a device array built into the library (DVC_DET_STATIC_SCRATCH_BYTES on every GPU that
  * loads the library, held until the process exits).  Nothing is allocated or freed here, by
  * CUDA or by any other library.
  *
  * Limit: dvc_detection_scratch_bytes(B, num_priors, num_classes) must not exceed
- * DVC_DET_STATIC_SCRATCH_BYTES (the 1917-prior, 21-class SSD fits B <= 13); larger requests
+ * DVC_DET_STATIC_SCRATCH_BYTES (the 1917-prior, 21-class SSD fits B <= 18); larger requests
  * are rejected with DVC_ERR_ARG and a message that names both sizes.
  *
  * The first call on each device looks the array's address up (that device must be current);
  * make that first call before any stream capture begins.  All calls on a device share the one
  * array: two calls whose kernels can overlap on that GPU (different streams, or concurrent
  * host threads) race on it - serialise them.  The array keeps whatever the previous call left;
- * the kernel only ever reads pool entries it wrote earlier in the same launch, so nothing has to
- * be cleared between calls.  Outputs are identical to dvc_detection_output. */
+ * a call only ever reads scratch entries it wrote itself earlier in the same call, so nothing has
+ * to be cleared between calls.  Outputs are identical to dvc_detection_output. */
 #define DVC_DET_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
 int dvc_detection_output_static(const float* loc, const float* conf, const float* priors, const float* variances,
                                 int B, const dvc_det_params* p, const int* slot_index,

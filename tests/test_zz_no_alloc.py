@@ -2,10 +2,10 @@
 
 Some embedders cannot give the library scratch memory (their own pool owns the whole GPU, or
 they cannot tolerate cudaMalloc's device-wide stall, or they are plain C with no allocator to
-lend).  `dvc_detection_output_static` keeps its candidate pool in a device array compiled into
+lend).  `dvc_detection_output_static` keeps its scratch in a device array compiled into
 the library.  This test drives it exactly as such a caller would - raw pointers through ctypes -
 and checks it against the ordinary entry point, twice in a row with different inputs, so that a
-pool still holding the first call's candidates cannot leak into the second.
+pool still holding the first call's data cannot leak into the second.
 
 Collected last on purpose (file name): if it fails under `-x`, every other test has already run.
 """
