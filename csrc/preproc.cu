@@ -23,6 +23,7 @@ struct ResizeArgs {
   const int *xq, *yq; int ix, iy;
   int band;       // output rows per CTA
   int aligned;    // frames 16-byte aligned (base and stride): vectorised staging
+  int tab_off;    // byte offset of the x-tap table inside the dynamic shared memory
 };
 
 // One CTA per (band of output rows, frame).  The source rows the band needs are staged in shared memory
@@ -54,6 +55,15 @@ __global__ void __launch_bounds__(256) resize_u8_kernel(const ResizeArgs a) {
     for (int i = tid; i < nvec; i += 256) sdst[i] = ldg_nc_v4(gsrc + i);
   } else {
     for (int i = tid; i < (int)(end - start); i += 256) rs_band[i] = frame[start + i];
+  }
+  // bilinear x taps for the whole output row live in shared memory too (3 ints per output pixel)
+  int* s_tab = reinterpret_cast<int*>(rs_band + a.tab_off);
+  if (a.mode == 2) {
+    for (int i = tid; i < a.dw; i += 256) {
+      s_tab[3 * i] = a.xs[i];
+      s_tab[3 * i + 1] = a.xq[2 * i];
+      s_tab[3 * i + 2] = a.xq[2 * i + 1];
+    }
   }
   __syncthreads();
   const uint8_t* s = rs_band + skew;          // row y of the frame lives at s + (y - r_lo) * row_bytes
@@ -118,8 +128,8 @@ __global__ void __launch_bounds__(256) resize_u8_kernel(const ResizeArgs a) {
 #pragma unroll
       for (int r = 0; r < RP; ++r) {
         const int dx = dxg + r;
-        const int sx0 = a.xs[dx], sx1 = min(sx0 + 1, a.sw - 1);
-        const int a0 = a.xq[dx * 2], a1 = a.xq[dx * 2 + 1];
+        const int sx0 = s_tab[3 * dx], sx1 = min(sx0 + 1, a.sw - 1);
+        const int a0 = s_tab[3 * dx + 1], a1 = s_tab[3 * dx + 2];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
@@ -557,7 +567,7 @@ extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int
   if (mode == 1) DVC_REQUIRE(ix > 0 && iy > 0 && dw * ix <= sw && dh * iy <= sh, "resize: bad integer ratio");
   if (mode == 2) DVC_REQUIRE(xs && ys && xq && yq, "resize: bilinear tables missing");
   ResizeArgs a{src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps,
-               ys, yc, ya, y_taps, xq, yq, ix, iy, 1, 0};
+               ys, yc, ya, y_taps, xq, yq, ix, iy, 1, 0, 0};
   a.aligned = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && src_frame_stride % 16 == 0) ? 1 : 0;
   // band height: as many output rows as keep the staged source rows within ~64 KB of shared memory
   const long long row_bytes = (long long)sw * 3;
@@ -566,7 +576,8 @@ extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int
   auto rows_for = [&](int bnd) { return (int)(bnd * sy + 0.999) + (mode == 0 ? y_taps : 2) + 1; };
   while (band > 1 && (long long)rows_for(band) * row_bytes > 64 * 1024) band >>= 1;
   a.band = band;
-  const long long smem = (long long)rows_for(band) * row_bytes + 64;
+  a.tab_off = (int)((((long long)rows_for(band) * row_bytes + 64) + 15) & ~15LL);
+  const long long smem = a.tab_off + (long long)dw * 12 + 16;
   DVC_REQUIRE(smem <= 200 * 1024, "resize: one band of source rows (%lld bytes) does not fit shared memory", smem);
   static bool attr_set[64] = {};
   int dev = 0;

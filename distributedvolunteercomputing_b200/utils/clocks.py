@@ -15,7 +15,7 @@ _QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,
 class ClockSampler:
     """Samples `nvidia-smi -lms 200` in a background process between start() and stop()."""
 
-    def __init__(self, gpu_index: int = 0, period_ms: int = 200):
+    def __init__(self, gpu_index: int = 0, period_ms: int = 50):
         self.gpu_index = gpu_index
         self.period_ms = period_ms
         self.proc: Optional[subprocess.Popen] = None
