@@ -40,7 +40,9 @@ def parse_args():
     ap.add_argument("--frame-w", type=int, default=300)
     ap.add_argument("--sub-batch", type=int, default=0)
     ap.add_argument("--no-graph", action="store_true")
-    ap.add_argument("--ingest", default="scatter", choices=["scatter", "local"])
+    ap.add_argument("--ingest", default="both", choices=["scatter", "local", "both"],
+                    help="multi-GPU end-to-end arm: frames enter through the client GPU and are scattered over NVLink, "
+                         "or each rank uploads its own shard over its own PCIe link (sharded reader)")
     ap.add_argument("--concurrency", type=int, default=2, help="batches in flight on separate streams (single-GPU arm)")
     return ap.parse_args()
 
@@ -187,57 +189,73 @@ def run_native(args):
         e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - t_e2e0) * 1e3)
         e2e_api = f"NativeEngine.process_stream (depth {depth}: copy-in, {depth} compute lanes, copy-out)"
         h2d, d2h = B * H * W * 3, B * 100 * 7 * 4 + B * 100 * 4 * 4 + 2 * B * 4
+        e2e_variants = None
     else:
         n_all = world * B
 
-        lane_done = [None] * len(cluster.lanes)
-        if rank == 0:
-            h_det = [torch.empty((n_all, 100, 7), dtype=torch.float32).pin_memory() for _ in cluster.lanes]
-            h_cnt = [torch.empty((n_all,), dtype=torch.int32).pin_memory() for _ in cluster.lanes]
-        consumed = [0]
+        def run_e2e(local: bool):
+            lane_done = [None] * len(cluster.lanes)
+            h_det = [torch.empty((n_all, 100, 7), dtype=torch.float32).pin_memory() for _ in cluster.lanes] if rank == 0 else None
+            h_cnt = [torch.empty((n_all,), dtype=torch.int32).pin_memory() for _ in cluster.lanes] if rank == 0 else None
+            my_pool = torch.from_numpy(synth_frames(POOL * B, H, W, seed=300 + rank)).view(POOL, B, H, W, 3).pin_memory() if local else None
+            my_raw = [torch.empty((B, H, W, 3), dtype=torch.uint8, device=dev) for _ in cluster.lanes] if local else None
 
-        def e2e_step(i):
-            k = cluster.step_id % len(cluster.lanes)
-            ln = cluster.lanes[k]
-            if rank == 0:
-                if lane_done[k] is not None:       # the lane's previous result is read on the host before reuse
+            def e2e_step(i):
+                k = cluster.step_id % len(cluster.lanes)
+                ln = cluster.lanes[k]
+                if rank == 0 and lane_done[k] is not None:   # the lane's previous result is read on the host before reuse
                     lane_done[k].synchronize()
-                    consumed[0] += int(h_cnt[k][0] >= 0)
-                with torch.cuda.stream(ln.stream):
-                    ln.raw_all.copy_(host_pool[i % POOL], non_blocking=True)
-                cluster.step(overlap=True)
-                with torch.cuda.stream(ln.stream):
-                    h_det[k].copy_(ln.det, non_blocking=True)
-                    h_cnt[k].copy_(ln.det_count, non_blocking=True)
-                    ev = torch.cuda.Event()
-                    ev.record(ln.stream)
-                lane_done[k] = ev
-            else:
-                cluster.step(overlap=True)
+                if local:
+                    with torch.cuda.stream(ln.stream):
+                        my_raw[k].copy_(my_pool[i % POOL], non_blocking=True)
+                    cluster.step(overlap=True, local_raw=my_raw[k])
+                else:
+                    if rank == 0:
+                        with torch.cuda.stream(ln.stream):
+                            ln.raw_all.copy_(host_pool[i % POOL], non_blocking=True)
+                    cluster.step(overlap=True)
+                if rank == 0:
+                    with torch.cuda.stream(ln.stream):
+                        h_det[k].copy_(ln.det, non_blocking=True)
+                        h_cnt[k].copy_(ln.det_count, non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(ln.stream)
+                    lane_done[k] = ev
 
-        def e2e_drain():
-            if rank == 0:
-                for k, ev in enumerate(lane_done):
-                    if ev is not None:
-                        ev.synchronize()
-                        consumed[0] += int(h_cnt[k][0] >= 0)
-                        lane_done[k] = None
-            cluster.join()
+            def e2e_drain():
+                if rank == 0:
+                    for k, ev in enumerate(lane_done):
+                        if ev is not None:
+                            ev.synchronize()
+                            lane_done[k] = None
+                cluster.join()
 
-        for i in range(4):
-            e2e_step(i)
-        e2e_drain()
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(args.steps):
-            e2e_step(i)
-        e2e_drain()
-        e1.record()
-        barrier()
-        e2e_ms = e0.elapsed_time(e1)
-        e2e_api = "BoxCluster.step (client GPU uploads the global batch, NVLink pull/push inside the kernels)"
+            for i in range(4):
+                e2e_step(i)
+            e2e_drain()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(args.steps):
+                e2e_step(i)
+            e2e_drain()
+            e1.record()
+            barrier()
+            return e0.elapsed_time(e1)
+
+        e2e_ms_scatter = run_e2e(False) if args.ingest in ("scatter", "both") else None
+        e2e_ms_local = run_e2e(True) if args.ingest in ("local", "both") else None
+        tt = torch.tensor([e2e_ms_scatter or 0.0, e2e_ms_local or 0.0], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms_scatter, e2e_ms_local = (float(tt[0]) or None), (float(tt[1]) or None)
+        use_local = e2e_ms_local is not None and (e2e_ms_scatter is None or e2e_ms_local < e2e_ms_scatter)
+        e2e_ms = e2e_ms_local if use_local else e2e_ms_scatter
+        e2e_api = ("BoxCluster.step(local_raw=...): every rank uploads its own 64 frames over its own PCIe link, detections "
+                   "gathered on the client GPU over NVLink inside the kernels") if use_local else \
+                  "BoxCluster.step: the client GPU uploads the global batch, NVLink pull/push inside the kernels"
         h2d, d2h = n_all * H * W * 3, n_all * 100 * 7 * 4 + n_all * 4
+        e2e_variants = {"scatter_via_client_gpu_fps": round(world * B * args.steps / (e2e_ms_scatter / 1e3), 1) if e2e_ms_scatter else None,
+                        "local_ingest_fps": round(world * B * args.steps / (e2e_ms_local / 1e3), 1) if e2e_ms_local else None}
     clocks = sampler.stop() if sampler else None
 
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
@@ -257,7 +275,8 @@ def run_native(args):
                    "cuda_graph": not args.no_graph, "sub_batch": cfg.sub_batch or B,
                    "batches_in_flight": conc, "p50_batch_latency_ms": round(p50_batch_ms, 4)},
         "e2e": {"value": round(e2e, 1), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": int(d2h), "ms_per_step": round(e2e_ms / args.steps, 4), "api": e2e_api},
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": round(e2e_ms / args.steps, 4), "api": e2e_api,
+                "variants": e2e_variants},
         "gpu_launches": int(per_step_launches * args.steps),
         "gpu_launches_counted_by_library": int(launches_eager),
         "clocks": clocks, "detections_last_batch": det_sum,

@@ -137,7 +137,7 @@ class BoxCluster:
                                              idw, idh, L.ptr(m.label_masks), nl, m.label_xy[0], m.label_xy[1], lw, lh,
                                              L.stream_ptr()), "annotate")
 
-    def _run_lane(self, ln: _Lane, raw_all: Optional[torch.Tensor], annotate: bool):
+    def _run_lane(self, ln: _Lane, raw_all: Optional[torch.Tensor], annotate: bool, local_raw: Optional[torch.Tensor] = None):
         st = ln.st
         L.set_device(self.dev)
         if self.mode == "pull_400":
@@ -148,6 +148,14 @@ class BoxCluster:
             self.dist.all_reduce(ln.tok, group=ln.group)      # rows pushed -> the client may draw
             if self.is_client and annotate:
                 self._annotate(ln, ln.frames_flat, self.n, ln.boxes_i, ln.box_count)
+        elif local_raw is not None:
+            # "local ingest": this rank's frames arrived over its own PCIe link (sharded reader); nothing to
+            # scatter, detections are still gathered on the client over NVLink
+            K.resize_u8(local_raw, st.t_area, st.frames400_flat, st.stride400)
+            self.engine.run(st, annotate=False, resize=False)
+            if annotate:
+                self._annotate(ln, st.frames400_flat, self.B, ln.my_boxes, ln.my_box_count)
+            self.dist.all_reduce(ln.tok, group=ln.group)      # every rank's rows have landed -> the client may read
         else:
             if self.is_client and raw_all is not None and raw_all.data_ptr() != ln.raw_all.data_ptr():
                 ln.raw_all.copy_(raw_all, non_blocking=True)  # frames enter the client's raw ring
@@ -158,7 +166,8 @@ class BoxCluster:
                 self._annotate(ln, st.frames400_flat, self.B, ln.my_boxes, ln.my_box_count)
             self.dist.all_reduce(ln.tok, group=ln.group)      # every rank's rows have landed -> the client may read
 
-    def step(self, raw_all: Optional[torch.Tensor] = None, annotate: bool = True, overlap: bool = False) -> _Lane:
+    def step(self, raw_all: Optional[torch.Tensor] = None, annotate: bool = True, overlap: bool = False,
+             local_raw: Optional[torch.Tensor] = None) -> _Lane:
         """One global batch: world*B frames (on the client GPU) -> detections + annotated frames on the
         client GPU.  Asynchronous.  With ``overlap`` the batch runs on its lane's stream so consecutive
         batches share the GPUs; call ``join()`` (or wait on the lane's stream) before reading results.
@@ -167,11 +176,11 @@ class BoxCluster:
         self.step_id += 1
         with torch.cuda.device(self.dev):
             if not overlap:
-                self._run_lane(ln, raw_all, annotate)
+                self._run_lane(ln, raw_all, annotate, local_raw)
                 return ln
             ln.stream.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(ln.stream):
-                self._run_lane(ln, raw_all, annotate)
+                self._run_lane(ln, raw_all, annotate, local_raw)
         return ln
 
     def join(self):
