@@ -146,6 +146,33 @@ class NativeEngine:
             self.w[f"{h.tap}_mbox"] = torch.from_numpy(w).to(dev, torch.float16).contiguous()
             self.b[f"{h.tap}_mbox"] = torch.from_numpy(b).to(dev, torch.float32)
 
+    def weight_layout(self):
+        """Deterministic flat layout of every packed weight/bias tensor: [(key, kind, offset, nbytes)], total bytes.
+        Each entry is 16-byte aligned so the blob can be pushed with 128-bit stores (K13)."""
+        out, off = [], 0
+        for kind, d in (("w", self.w), ("b", self.b)):
+            for key in sorted(d):
+                t = d[key]
+                n = t.numel() * t.element_size()
+                out.append((key, kind, off, n))
+                off += (n + 15) & ~15
+        return out, off
+
+    def export_weights(self, flat: torch.Tensor):
+        """Copy all packed weights into `flat` (uint8, device) following weight_layout()."""
+        layout, total = self.weight_layout()
+        assert flat.numel() >= total
+        for key, kind, off, n in layout:
+            t = (self.w if kind == "w" else self.b)[key]
+            flat[off:off + n].copy_(t.contiguous().view(torch.uint8).reshape(-1))
+
+    def import_weights(self, flat: torch.Tensor):
+        """Overwrite this engine's packed weights from a blob written by export_weights (same model)."""
+        layout, total = self.weight_layout()
+        for key, kind, off, n in layout:
+            t = (self.w if kind == "w" else self.b)[key]
+            t.view(torch.uint8).reshape(-1).copy_(flat[off:off + n])
+
     def weight_bytes(self) -> int:
         return sum(t.numel() * t.element_size() for t in list(self.w.values()) + list(self.b.values()))
 

@@ -61,6 +61,8 @@ class BoxCluster:
         self.dev = engine.device
         self.n = self.world * B
         self.step_id = 0
+        self.epoch = 0
+        self._setup_control()
         self.lanes: List[_Lane] = [self._make_lane(k) for k in range(max(1, lanes))]
         # convenience aliases to lane 0 (single-lane users and tests)
         l0 = self.lanes[0]
@@ -69,6 +71,42 @@ class BoxCluster:
         if self.is_client:
             self.raw_all, self.frames400, self.det, self.det_count = l0.raw_all, l0.frames400, l0.det, l0.det_count
             self.boxes_i, self.box_count, self.flags = l0.boxes_i, l0.box_count, l0.flags
+
+    # ------------------------------------------------------------------ K13 / K14: weights and membership epoch
+    def _setup_control(self):
+        """Every rank owns a small exported control block: [0] membership epoch word, then the packed-weight
+        blob.  The client pushes into all of them with its own stores (no NCCL, no host copies)."""
+        layout, total = self.engine.weight_layout()
+        self._wbytes = total
+        self.ctrl = p2p.DevBuffer(256 + total, self.dev)
+        ptrs = p2p.exchange({"ctrl": self.ctrl}, self.dev, None)["ctrl"]
+        self.ctrl_ptrs = ptrs
+        self.epoch_word = self.ctrl.tensor(torch.int32, (1,))
+        self.weight_blob = self.ctrl.tensor(torch.uint8, (total,), offset_bytes=256)
+        if self.is_client:
+            self._epoch_targets = p2p.device_ptr_array(ptrs, self.dev)
+            self._weight_targets = p2p.device_ptr_array([p + 256 for r, p in enumerate(ptrs) if r != self.rank], self.dev)
+
+    def broadcast_weights(self):
+        """K13: the client's packed weights are pushed once into every peer (reference: each client loads the
+        caffemodel from disk itself, worker.py:194); peers then adopt them.  Collective: call on every rank."""
+        if self.is_client:
+            self.engine.export_weights(self.weight_blob)
+            if self.world > 1:
+                L.check(self.engine.lib.dvc_push_multicast(L.ptr(self.weight_blob), L.ptr(self._weight_targets), self.world - 1,
+                                                           (self._wbytes + 15) & ~15, L.stream_ptr()), "push_multicast")
+        torch.cuda.current_stream().synchronize()
+        self.dist.barrier()
+        if not self.is_client:
+            self.engine.import_weights(self.weight_blob)
+            torch.cuda.current_stream().synchronize()
+        self.dist.barrier()
+
+    def publish_epoch(self, epoch: int):
+        """K14: write the membership epoch word into every GPU's control block (release at system scope)."""
+        self.epoch = epoch
+        if self.is_client:
+            L.check(self.engine.lib.dvc_epoch_broadcast(L.ptr(self._epoch_targets), self.world, epoch, L.stream_ptr()), "epoch")
 
     def _make_lane(self, k: int) -> _Lane:
         dist, eng, B, n = self.dist, self.engine, self.B, self.n

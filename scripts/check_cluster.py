@@ -17,6 +17,15 @@ graph = SSDGraph.random(seed=1, conf_gain=2.5)
 for use_graph, mode in ((False, "pull_400"), (True, "pull_400"), (False, "pull_raw"), (True, "pull_raw")):
     eng = NativeEngine(graph, dev, Config(batch=B, sub_batch=4, use_cuda_graph=use_graph), requester_id="127.0.0.1:5554")
     cl = BoxCluster(eng, B, H, W, client_rank=0, mode=mode)
+    if mode == "pull_raw" and use_graph:
+        # K13/K14: scramble this rank's weights, then adopt the client's over NVLink; publish an epoch word
+        if rank != 0:
+            for t in eng.w.values():
+                t.zero_()
+        cl.broadcast_weights()
+        cl.publish_epoch(41 + world)
+        torch.cuda.synchronize(); dist.barrier()
+        assert int(cl.epoch_word.item()) == 41 + world, "epoch word did not arrive"
     rng = np.random.default_rng(7)
     frames = torch.from_numpy(rng.integers(0, 256, (world * B, H, W, 3), dtype=np.uint8))
     for it in range(3):
