@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--ingest", default="both", choices=["scatter", "local", "both"],
                     help="multi-GPU end-to-end arm: frames enter through the client GPU and are scattered over NVLink, "
                          "or each rank uploads its own shard over its own PCIe link (sharded reader)")
-    ap.add_argument("--concurrency", type=int, default=2, help="batches in flight on separate streams (single-GPU arm)")
+    ap.add_argument("--concurrency", type=int, default=4, help="batches in flight on separate streams (single-GPU arm)")
     return ap.parse_args()
 
 
