@@ -46,7 +46,7 @@ __global__ void priorbox_kernel(float* boxes, float* variances, int prior_off, i
 constexpr int DET_MAXC = 32;      // classes
 constexpr int DET_MAXK = 128;     // per-class top_k capacity
 constexpr int NMS_THREADS = 128;
-constexpr int MERGE_THREADS = 256;
+constexpr int MERGE_THREADS = 1024;   // the binary searches are dependent shared-memory chains: hide them with warps
 
 struct DetArgs {
   const float *loc, *conf, *priors, *variances;
