@@ -307,27 +307,31 @@ __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const Prep
 // while the next tile is being gathered.
 constexpr int TC_A_BYTES = 128 * 128;     // 128 rows x 64 fp16 (only k < 32 is read)
 constexpr int TC_B_BYTES = 32 * 128;
-constexpr int TC_OFF_B = 0;                                   // 1024-aligned region first
-constexpr int TC_OFF_A = TC_OFF_B + TC_B_BYTES;               // 4096
-constexpr int TC_OFF_PATCH = TC_OFF_A + 2 * TC_A_BYTES;       // fp16 patch [17][301][3]
-constexpr int TC_PATCH_BYTES = ((PC_PROWS * PC_PCOLS * 3 * 2) + 15) & ~15;
-constexpr int TC_OFF_TAB = TC_OFF_PATCH + TC_PATCH_BYTES;     // xs[300], xq[600] ints
-constexpr int TC_OFF_BIAS = TC_OFF_TAB + 3 * PC_NET * 4;
-constexpr int TC_OFF_BAR = TC_OFF_BIAS + 32 * 4;              // 2 mbarriers + tmem slot
-constexpr int TC_OFF_BAND = (TC_OFF_BAR + 32 + 15) & ~15;
+constexpr int TC_OFF_B = 0;                                   // 1024-aligned regions first
+constexpr int TC_OFF_A = TC_OFF_B + TC_B_BYTES;               // 4096: the two A buffers ALIAS the staged source band
+constexpr int TC_PATCH_BYTES = ((PC_PROWS * PC_PCOLS * 3 * 2) + 15) & ~15;   // fp16 patch [17][301][3]
+__host__ __device__ inline int tc_ab_bytes(int band_bytes) {     // A buffers (32 KB) or the band, whichever is larger
+  const int a = 2 * TC_A_BYTES;
+  return ((band_bytes > a ? band_bytes : a) + 15) & ~15;
+}
 
-__global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_tc_kernel(const PreprocArgs a) {
+__global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const PreprocArgs a) {
   extern __shared__ uint8_t tc_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~uintptr_t(1023));
+  // the staged source band is dead once the patch has been computed, so the im2col A buffers reuse its space
+  const int off_patch = TC_OFF_A + tc_ab_bytes(a.band_bytes);
+  const int off_tab = off_patch + TC_PATCH_BYTES;
+  const int off_bias = off_tab + 3 * PC_NET * 4;
+  const int off_bar = off_bias + 32 * 4;
   uint8_t* sB = smem + TC_OFF_B;
   uint8_t* sA = smem + TC_OFF_A;
-  __half* s_patch = reinterpret_cast<__half*>(smem + TC_OFF_PATCH);
-  int* s_xs = reinterpret_cast<int*>(smem + TC_OFF_TAB);
+  uint8_t* s_band = smem + TC_OFF_A;
+  __half* s_patch = reinterpret_cast<__half*>(smem + off_patch);
+  int* s_xs = reinterpret_cast<int*>(smem + off_tab);
   int* s_xq = s_xs + PC_NET;
-  float* s_b = reinterpret_cast<float*>(smem + TC_OFF_BIAS);
-  uint64_t* mma_done = reinterpret_cast<uint64_t*>(smem + TC_OFF_BAR);
+  float* s_b = reinterpret_cast<float*>(smem + off_bias);
+  uint64_t* mma_done = reinterpret_cast<uint64_t*>(smem + off_bar);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_done + 2);
-  uint8_t* s_band = smem + TC_OFF_BAND;
 
   const int band = blockIdx.x, b = blockIdx.y;
   const int tid = threadIdx.x;
@@ -523,9 +527,9 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
   if (band_rows_max > sh) band_rows_max = sh;
   a.band_bytes = ((band_rows_max * sw * 3 + 31) & ~15) + 16;
   L->smem = PC_BAND_OFF + a.band_bytes;
-  L->smem_tc = TC_OFF_BAND + a.band_bytes + 1024;
+  L->smem_tc = TC_OFF_A + tc_ab_bytes(a.band_bytes) + TC_PATCH_BYTES + 3 * PC_NET * 4 + 32 * 4 + 64 + 1024;
   const char* env = getenv("DVC_CONV0_CUDA_CORES");            // A/B switch: the fp32 CUDA-core variant
-  L->use_tc = !(env && env[0] == '1') && L->smem_tc <= 110 * 1024;
+  L->use_tc = !(env && env[0] == '1') && L->smem_tc <= 110 * 1024;   // taller source frames fall back to the CUDA-core variant
   DVC_REQUIRE(L->smem <= 227 * 1024, "preproc: source band of %d rows x %d px does not fit shared memory", band_rows_max, sw);
   L->grid = dim3((PC_OUT + PC_BAND - 1) / PC_BAND, B);
   return DVC_OK;
