@@ -174,7 +174,7 @@ def run_native(args):
                 yield host_pool[i % POOL]
 
         depth = max(2, conc) + 2
-        for r in eng.process_stream(host_batches(max(4, min(args.warmup, 6))), depth=depth):
+        for r in eng.process_stream(host_batches(max(depth + 2, args.warmup)), depth=depth):   # every slot built + captured
             pass
         barrier()
         t_e2e0 = time.perf_counter()

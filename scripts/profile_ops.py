@@ -1,5 +1,5 @@
 """One launch of each hot kernel at flagship shapes (after one warm-up launch each) - the ncu --set full target.
-Order: resize, preproc_conv0, dw(conv1/dw), gemm(conv1), dw(conv7/dw), gemm(conv7), gemm(conv13), gemm head(conv11_mbox), detection, annotate."""
+Order: resize, preproc_conv0, dw(conv1/dw), gemm(conv1), dw(conv7/dw), gemm(conv7), gemm(conv13), gemm head(conv11_mbox), softmax, class_nms, merge_deliver, annotate (12 launches)."""
 import sys
 import numpy as np, torch
 sys.path.insert(0, '.')

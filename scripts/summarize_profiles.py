@@ -10,10 +10,10 @@ peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.ex
 
 LABELS = ["K1a resize 64x300x300->400x400", "K1b preproc+conv0, 16 frames", "K3 dw conv1/dw 16x150x150x32", "K2 gemm conv1 M=360000 N=64 K=32",
           "K3 dw conv7/dw 64x19x19x512", "K2 gemm conv7 M=23104 N=512 K=512", "K2 gemm conv13 M=6400 N=1024 K=1024",
-          "K5 head gemm conv11_mbox M=23104 N=80 K=512", "K7-K9 detection 64 frames (dense random scores)", "K10 annotate 64 frames"]
-FLOPS = [None, 16 * 19.44e6 * 2, None, 2.0 * 360000 * 64 * 32, None, 2.0 * 23104 * 512 * 512, 2.0 * 6400 * 1024 * 1024, 2.0 * 23104 * 80 * 512, None, None]
+          "K5 head gemm conv11_mbox M=23104 N=80 K=512", "K7 softmax 64x1917x21", "K8 per-class NMS 64 frames x 20 classes (dense random scores)", "K9 merge+deliver 64 frames", "K10 annotate 64 frames"]
+FLOPS = [None, 16 * 19.44e6 * 2, None, 2.0 * 360000 * 64 * 32, None, 2.0 * 23104 * 512 * 512, 2.0 * 6400 * 1024 * 1024, 2.0 * 23104 * 80 * 512, None, None, None, None]
 BYTES = [64 * (270000 + 480000), 16 * (480000 + 1440000), 16 * 22500 * 32 * 2 * 2, 360000 * (32 + 64) * 2, 64 * 361 * 512 * 2 * 2,
-         23104 * 1024 * 2 + 512 * 512 * 2, 6400 * 2048 * 2 + 1024 * 1024 * 2, 23104 * 512 * 2 + 23104 * 75 * 4, None, None]
+         23104 * 1024 * 2 + 512 * 512 * 2, 6400 * 2048 * 2 + 1024 * 1024 * 2, 23104 * 512 * 2 + 23104 * 75 * 4, 64 * 1917 * 21 * 4 * 2, None, None, None]
 
 if os.path.exists(rep):
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
