@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(256) dw3x3_tma_kernel(const __grid_constant__ 
     tma_load_4d(tile, &tm, &bar, cc * a.CT, tx * a.TX * STRIDE - 1, ty * a.TY * STRIDE - 1, n);
   }
   const int cgs = a.CT >> 3;
-  const int cg = tid % cgs, pt = tid / cgs, pxt = 256 / cgs;
+  const int cg = tid % cgs, pt = tid / cgs, pxt = (int)blockDim.x / cgs;
   const int c0 = cc * a.CT + cg * 8;
   // weights of this thread's 8 channels as packed fp16 pairs, bias as fp32 (overlaps the TMA flight)
   uint32_t wq[9][4];
@@ -210,12 +210,20 @@ __global__ void __launch_bounds__(256) dw3x3_tma_kernel(const __grid_constant__ 
 struct DwLaunch {
   CUtensorMap tm;
   DwArgs args;
-  int grid, smem, stride;
+  int grid, smem, stride, threads;
   bool tma;
   const void* in;
 };
 
 constexpr int DW_SMEM_LIMIT = 56 * 1024;
+
+// Tuning overrides for sweeps (scripts/sweep_dw.py): DVC_DW_SMEM_KB caps the input tile, DVC_DW_THREADS sets the CTA size.
+static int dw_env_int(const char* name, int dflt, int lo, int hi) {
+  const char* e = getenv(name);
+  if (!e || !*e) return dflt;
+  const int v = atoi(e);
+  return v < lo ? lo : (v > hi ? hi : v);
+}
 
 int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stride, const float* w, const float* b, int relu,
                void* out) {
@@ -227,17 +235,22 @@ int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stri
   a.Ho = (H + 2 - 3) / stride + 1; a.Wo = (W + 2 - 3) / stride + 1;
   L->stride = stride; L->in = in;
   a.CT = C % 64 == 0 ? 64 : (C % 32 == 0 ? 32 : (C % 16 == 0 ? 16 : 8));
+  const int ct_env = dw_env_int("DVC_DW_CT", 0, 0, 128);
+  if (ct_env >= 8 && (ct_env & (ct_env - 1)) == 0 && C % ct_env == 0) a.CT = ct_env;
   a.cchunks = C / a.CT;
   // tile search: minimise (input pixels fetched incl. halo + output pixels covered incl. edge waste)
   double best = 1e30;
   int bx = 0, by = 0;
+  const int smem_limit = dw_env_int("DVC_DW_SMEM_KB", DW_SMEM_LIMIT / 1024, 4, DW_SMEM_LIMIT / 1024) * 1024;
+  L->threads = dw_env_int("DVC_DW_THREADS", 128, 64, 256) & ~31;   // 128: 4 CTAs per SM (register-bound), ~200 KB of TMA in flight per SM
+  const int min_outs = L->threads / 4;
   for (int TY = 1; TY <= (a.Ho < 64 ? a.Ho : 64); ++TY) {
     for (int TX = 1; TX <= (a.Wo < 64 ? a.Wo : 64); ++TX) {
       const int outs = TX * TY;
       if (outs > 1024) continue;
-      if (outs < 64 && (TX < a.Wo || TY < a.Ho)) continue;
+      if (outs < min_outs && (TX < a.Wo || TY < a.Ho)) continue;
       const int BW = (TX - 1) * stride + 3, BH = (TY - 1) * stride + 3;
-      if (BW > 256 || BH > 256 || BW * BH * a.CT * 2 > DW_SMEM_LIMIT) continue;
+      if (BW > 256 || BH > 256 || BW * BH * a.CT * 2 > smem_limit) continue;
       const int ntx = ceil_div(a.Wo, TX), nty = ceil_div(a.Ho, TY);
       const double cost = (double)ntx * nty * BW * BH / ((double)H * W) + 1.5 * (double)ntx * TX * nty * TY / ((double)a.Wo * a.Ho)
                           + 0.02 * (256.0 / outs);
@@ -265,8 +278,8 @@ int dw_launch(const DwLaunch* L, cudaStream_t st) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
     attr_set[dev & 63] = true;
   }
-  if (L->stride == 1) dw3x3_tma_kernel<1><<<L->grid, 256, L->smem, st>>>(L->tm, L->args);
-  else dw3x3_tma_kernel<2><<<L->grid, 256, L->smem, st>>>(L->tm, L->args);
+  if (L->stride == 1) dw3x3_tma_kernel<1><<<L->grid, L->threads, L->smem, st>>>(L->tm, L->args);
+  else dw3x3_tma_kernel<2><<<L->grid, L->threads, L->smem, st>>>(L->tm, L->args);
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
