@@ -44,6 +44,7 @@ struct GemmArgs {
   int out_mode;        // 0: fp16 [M, ldc]   1: SSD head split store (fp32)
   int tma_store;       // out_mode 0 only: epilogue goes through smem + TMA store
   int cluster;         // CTAs per cluster along M sharing one multicast weight tile (1, 2 or 4)
+  int two_cta;         // cta_group::2: a CTA pair multiplies one 256 x block_n tile (cluster == 2, no multicast)
   int m_tiles, num_ctiles;
   int b_resident;      // whole weight matrix stays in smem (one N tile, few K blocks): loaded once per CTA
   __half* out;
@@ -52,6 +53,9 @@ struct GemmArgs {
   dvc_head_out head;
 };
 
+// PAIR = 1 is the cta_group::2 build: ptxas marks a kernel containing cta_group::2 instructions as needing an even
+// cluster, so the single-CTA path is a separate instantiation.
+template <int PAIR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmC, const GemmArgs g) {
@@ -59,7 +63,8 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = __shfl_sync(0xffffffff, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
-  const int b_stage_bytes = g.block_n * BK * 2;
+  // pair mode: each CTA holds only its half of the weight tile (block_n / 2 rows)
+  const int b_stage_bytes = (PAIR ? g.block_n / 2 : g.block_n) * BK * 2;
 
   uint8_t* sEpi = smem;                                   // [4 warps][2][32 rows x 128 B], 1024-aligned
   float* sBias = reinterpret_cast<float*>(smem + EPI_SMEM);
@@ -83,18 +88,24 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (lane == 0) {
       for (int s = 0; s < g.stages; ++s) {
         mbar_init(&full_bar[s], 1);
-        mbar_init(&empty_bar[s], (uint32_t)g.cluster);    // every CTA of the cluster must have drained the stage
+        // multicast clusters: every CTA must have drained the stage; pair mode: one multicast commit from the leader
+        mbar_init(&empty_bar[s], PAIR ? 1u : (uint32_t)g.cluster);
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
-        mbar_init(&tmem_empty_bar[a], 4);     // one arrive per epilogue warp
+        mbar_init(&tmem_empty_bar[a], PAIR ? 8u : 4u);     // one arrive per epilogue warp (of both CTAs in pair mode)
       }
       mbar_init(bres_bar, 1);
       fence_mbar_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_slot, (uint32_t)g.tmem_cols);
-    tmem_relinquish();
+    if (PAIR) {
+      tmem_alloc_pair(tmem_slot, (uint32_t)g.tmem_cols);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(tmem_slot, (uint32_t)g.tmem_cols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   if (g.cluster > 1) cluster_sync_all(); else __syncthreads();
@@ -124,6 +135,15 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const int s = it % g.stages;
           const uint32_t ph = (uint32_t)(it / g.stages) & 1u;
           mbar_wait(&empty_bar[s], ph ^ 1u);
+          if (PAIR) {
+            // both CTAs load their own A rows and their half of the weight tile; all bytes are credited to the
+            // leader's barrier, which the leader arms for the pair
+            if (crank == 0) mbar_arrive_expect_tx(&full_bar[s], 2u * stage_bytes);
+            const uint32_t lead_bar = mapa_u32(smem_u32(&full_bar[s]), 0);
+            tma_load_2d_pair(sA + s * A_STAGE_BYTES, &tmA, lead_bar, kb * BK, m_tile * BM);
+            tma_load_2d_pair(sB + s * b_stage_bytes, &tmB, lead_bar, kb * BK, n_tile * g.block_n + crank * slice_rows);
+            continue;
+          }
           mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
           tma_load_2d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], kb * BK, m_tile * BM);
           if (g.cluster > 1) {
@@ -139,8 +159,10 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------- MMA issuer
-    if (elect_one()) {
-      const uint32_t idesc = umma_idesc_f16(BM, (uint32_t)g.block_n);
+    if (PAIR && crank != 0) {
+      // pair mode: only the leader CTA issues MMAs (they drive both SMs' tensor cores)
+    } else if (elect_one()) {
+      const uint32_t idesc = umma_idesc_f16(PAIR ? 2 * BM : BM, (uint32_t)g.block_n);
       if (g.b_resident) mbar_wait(bres_bar, 0);
       int it = 0, t = 0;
       for (int ct = cluster_id; ct < g.num_ctiles; ct += num_clusters, ++t) {
@@ -159,12 +181,16 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           ksteps = ksteps > 4 ? 4 : ksteps;
           for (int k = 0; k < ksteps; ++k) {
             // advance 16 fp16 = 32 bytes along K inside the 128-byte swizzle atom (+2 in 16-byte units)
-            umma_f16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+            if (PAIR) umma_f16_pair(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+            else umma_f16(d_tmem, a_desc + (uint64_t)(k * 2), b_desc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
           }
           // frees this smem stage (in every CTA of the cluster: peers multicast into it) once the MMAs retire
-          if (g.cluster > 1) umma_commit_mcast(&empty_bar[s], cmask); else umma_commit(&empty_bar[s]);
+          if (PAIR) umma_commit_pair(&empty_bar[s], 3);
+          else if (g.cluster > 1) umma_commit_mcast(&empty_bar[s], cmask);
+          else umma_commit(&empty_bar[s]);
         }
-        umma_commit(&tmem_full_bar[acc]);      // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (of both CTAs in pair mode)
+        if (PAIR) umma_commit_pair(&tmem_full_bar[acc], 3); else umma_commit(&tmem_full_bar[acc]);
       }
     }
     __syncwarp();
@@ -267,14 +293,20 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       // all tcgen05.ld of this accumulator have completed (wait::ld above): hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty_bar[acc]), 0));   // the leader's MMA warp waits
+        else mbar_arrive(&tmem_empty_bar[acc]);
+      }
     }
     if (g.tma_store && lane == 0) tma_store_wait_all<0>();
   }
 
   tc_fence_before();
   if (g.cluster > 1) cluster_sync_all(); else __syncthreads();   // peers may still multicast into / arrive on this CTA
-  if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)g.tmem_cols);
+  if (warp == 1) {
+    if (PAIR) tmem_dealloc_pair(tmem_base, (uint32_t)g.tmem_cols);
+    else tmem_dealloc(tmem_base, (uint32_t)g.tmem_cols);
+  }
 }
 
 // ------------------------------------------------------------------------------------ host
@@ -292,8 +324,9 @@ static int num_sms() {
 }
 
 static int pick_block_n(int M, int N) {
-  // Persistent kernel: the widest tile that still gives every SM a tile (fewer re-reads of A,
-  // wider TMA stores); otherwise the narrowest tile that is still >= 64 columns.
+  // Persistent kernel: the widest tile that still gives most SMs a tile (fewer re-reads of A,
+  // wider TMA stores); otherwise the narrowest tile that is still >= 64 columns.  The 60% threshold is from
+  // scripts/sweep_gemm.py: conv14_1 (50 M tiles, N=256) runs 16.4 us with 100 tiles of 128 vs 20.5 us with 200 of 64.
   const int cand[] = {256, 160, 128, 80, 64};
   const int m_tiles = ceil_div(M, BM);
   const int sms = num_sms();
@@ -301,7 +334,7 @@ static int pick_block_n(int M, int N) {
   for (int c : cand) {
     if (N % c) continue;
     last = c;
-    if (m_tiles * (N / c) >= sms) return c;
+    if (m_tiles * (N / c) * 10 >= sms * 6) return c;
   }
   if (last) return last;
   return N <= 256 ? N : 16;     // N in {16, 32, 48}
@@ -347,9 +380,24 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
     const int c = atoi(env);
     if ((c == 1 || c == 2 || c == 4) && !(g.b_resident && c > 1) && (block_n / c) % 8 == 0 && g.m_tiles >= c) cluster = c;
   }
+  // CTA pairs (tcgen05 cta_group::2, DVC_GEMM_2CTA=<min K blocks>): one 256 x block_n tile per pair, each CTA stages
+  // its 128 rows of A and half of the weight tile, so a stage is 16 + block_n/8 KB instead of 16 + block_n/4 KB, more
+  // K blocks fit in flight and each SM reads 8 KB instead of 12 KB of operands per MMA.  Measured on B200
+  // (scripts/check_2cta.py, bit-identical outputs): M=23104 N=512 K=4096 105.5 -> 95.0 us, conv13 26.6 -> 25.4 us,
+  // conv7 24.6 -> 24.6 us, K<=256 shapes 2-3 us slower (cluster launch + cross-CTA barriers).  The network's K is at
+  // most 1024, where fill/drain and wave quantisation dominate, so the pair path is opt-in (off by default).
+  g.two_cta = 0;
+  {
+    const char* env = getenv("DVC_GEMM_2CTA");
+    const int want = env ? atoi(env) : 0;
+    if (want && cluster == 1 && !g.b_resident && block_n % 32 == 0 && g.m_tiles >= 2 && g.num_kb >= want) {
+      g.two_cta = 1;
+      cluster = 2;
+    }
+  }
   g.cluster = cluster;
   g.num_ctiles = ceil_div(g.m_tiles, cluster) * g.n_tiles;
-  const int stage_bytes = A_STAGE_BYTES + (g.b_resident ? 0 : b_tile_bytes);
+  const int stage_bytes = A_STAGE_BYTES + (g.b_resident ? 0 : (g.two_cta ? b_tile_bytes / 2 : b_tile_bytes));
   const int fixed = EPI_SMEM + BIAS_SMEM + 1024 + 256 + (g.b_resident ? g.num_kb * b_tile_bytes : 0);
   int stages = (GEMM_MAX_SMEM - fixed) / stage_bytes;
   if (stages > 8) stages = 8;
@@ -388,7 +436,8 @@ int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    DVC_CHECK_CUDA(cudaFuncSetAttribute(gemm_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_MAX_SMEM));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(gemm_f16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_MAX_SMEM));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(gemm_f16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_MAX_SMEM));
     attr_set[dev & 63] = true;
   }
   if (L->args.cluster > 1) {
@@ -404,9 +453,13 @@ int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    DVC_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_f16_kernel, L->tmA, L->tmB, L->tmC, L->args));
+    cudaError_t le = L->args.two_cta ? cudaLaunchKernelEx(&cfg, gemm_f16_kernel<1>, L->tmA, L->tmB, L->tmC, L->args)
+                                     : cudaLaunchKernelEx(&cfg, gemm_f16_kernel<0>, L->tmA, L->tmB, L->tmC, L->args);
+    if (le != cudaSuccess) (void)cudaGetLastError();
+    DVC_REQUIRE(le == cudaSuccess, "gemm: cluster launch failed (%s): grid=%d cluster=%d smem=%d pair=%d block_n=%d stages=%d",
+                cudaGetErrorString(le), L->grid, L->args.cluster, L->smem, L->args.two_cta, L->args.block_n, L->args.stages);
   } else {
-    gemm_f16_kernel<<<L->grid, GEMM_THREADS, L->smem, st>>>(L->tmA, L->tmB, L->tmC, L->args);
+    gemm_f16_kernel<0><<<L->grid, GEMM_THREADS, L->smem, st>>>(L->tmA, L->tmB, L->tmC, L->args);
   }
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());

@@ -47,6 +47,23 @@ def test_gemm_matches_fp32(K, M, N, K_, bn):
     assert (out2.float() - ref2).abs().max().item() <= 2e-3 * max(1.0, ref2.abs().max().item()) + 2e-3
 
 
+@pytest.mark.parametrize("M,N,K_,bn", [(1000, 256, 256, 128), (23104 // 4 + 77, 512, 512, 256), (900, 1024, 1024, 256)])
+def test_gemm_cta_pair_matches_single(K, M, N, K_, bn, monkeypatch):
+    """tcgen05 cta_group::2: a CTA pair multiplies one 256 x block_n tile (odd M-tile counts and an M tail included);
+    must be bit-identical to the single-CTA path (same K order) and match fp32."""
+    a = _rand((M, K_), 1.0, 11).half().to(DEV)
+    w = _rand((N, K_), 1.0 / np.sqrt(K_), 12).half().to(DEV)
+    bias = _rand((N,), 0.5, 13).to(DEV)
+    monkeypatch.setenv("DVC_GEMM_2CTA", "0")
+    solo = K.gemm_f16(a, w, bias, relu=True, block_n=bn)
+    monkeypatch.setenv("DVC_GEMM_2CTA", "1")
+    pair = K.gemm_f16(a, w, bias, relu=True, block_n=bn)
+    torch.cuda.synchronize()
+    assert torch.equal(solo, pair)
+    ref = torch.relu(a.float() @ w.float().t() + bias)
+    assert (pair.float() - ref).abs().max().item() <= 2e-3 * max(1.0, ref.abs().max().item()) + 2e-3
+
+
 def test_gemm_head_split_store(K):
     B, hw, Cin, A_, ncls, P_ = 3, 19 * 19, 512, 3, 21, 1917
     n_loc, n_conf = A_ * 4, A_ * ncls
