@@ -135,11 +135,13 @@ __global__ void __launch_bounds__(256) dw3x3_tma_kernel(const __grid_constant__ 
   const int tx = bid % a.tiles_x; bid /= a.tiles_x;
   const int ty = bid % a.tiles_y;
   const int n = bid / a.tiles_y;
+  pdl_launch_dependents();
   if (tid == 0) {
     mbar_init(&bar, 1);
     fence_mbar_init();
   }
   __syncthreads();
+  pdl_wait();                   // the input activation is the previous kernel's output
   if (tid == 0) {
     mbar_arrive_expect_tx(&bar, (uint32_t)(a.BH * a.BW * a.CT * 2));
     tma_load_4d(tile, &tm, &bar, cc * a.CT, tx * a.TX * STRIDE - 1, ty * a.TY * STRIDE - 1, n);
@@ -278,8 +280,8 @@ int dw_launch(const DwLaunch* L, cudaStream_t st) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
     attr_set[dev & 63] = true;
   }
-  if (L->stride == 1) dw3x3_tma_kernel<1><<<L->grid, L->threads, L->smem, st>>>(L->tm, L->args);
-  else dw3x3_tma_kernel<2><<<L->grid, L->threads, L->smem, st>>>(L->tm, L->args);
+  if (L->stride == 1) DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<1>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));
+  else DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<2>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
@@ -298,8 +300,10 @@ int dwconv_launch(const void* in, int B, int H, int W, int C, int stride, const 
 
 // ---- im2col for the dense 3x3 stride-2 pad-1 extras (conv14_2 .. conv17_2, prototxt:922-1146)
 __global__ void __launch_bounds__(256)
-im2col3x3s2_kernel(const __half* __restrict__ in, int B, int H, int W, int C, int Ho, int Wo, __half* __restrict__ out,
+im2col3x3s2_kernel(const __half* in, int B, int H, int W, int C, int Ho, int Wo, __half* __restrict__ out,
                    long long total) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
   if (idx >= total) return;
   const int CG = C >> 3;
@@ -312,7 +316,7 @@ im2col3x3s2_kernel(const __half* __restrict__ in, int B, int H, int W, int C, in
   const int iy = oy * 2 - 1 + tap / 3, ix = ox * 2 - 1 + tap % 3;
   uint4 v = make_uint4(0, 0, 0, 0);
   if (iy >= 0 && iy < H && ix >= 0 && ix < W)
-    v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)b * H + iy) * W + ix) * C + cg * 8));
+    v = ldg_v4(in + (((size_t)b * H + iy) * W + ix) * C + cg * 8);
   const size_t m = ((size_t)b * Ho + oy) * Wo + ox;
   *reinterpret_cast<uint4*>(out + m * (size_t)(9 * C) + (size_t)tap * C + cg * 8) = v;
 }
@@ -321,7 +325,8 @@ int im2col_launch(const void* in, int B, int H, int W, int C, void* out, cudaStr
   DVC_REQUIRE(C % 8 == 0 && B > 0 && H > 0 && W > 0, "im2col: bad shape C=%d", C);
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const long long total = (long long)B * Ho * Wo * 9 * (C / 8);
-  im2col3x3s2_kernel<<<(int)ceil_div64(total, 256), 256, 0, st>>>((const __half*)in, B, H, W, C, Ho, Wo, (__half*)out, total);
+  DVC_CHECK_CUDA(launch_pdl(im2col3x3s2_kernel, dim3((unsigned)ceil_div64(total, 256)), dim3(256), 0, st, 1, (const __half*)in, B, H, W, C,
+                            Ho, Wo, (__half*)out, total));
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;

@@ -78,6 +78,8 @@ __device__ __forceinline__ float box_iou(const float* a, const float* b) {
 }
 
 __global__ void __launch_bounds__(256) softmax_kernel(const DetArgs a) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int C = a.p.num_classes, P = a.p.num_priors;
   const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
   if (idx >= (long long)a.B * P) return;
@@ -102,6 +104,8 @@ __global__ void __launch_bounds__(256) softmax_kernel(const DetArgs a) {
 
 __global__ void __launch_bounds__(NMS_THREADS) class_nms_kernel(const DetArgs a) {
   extern __shared__ __align__(16) uint8_t smem[];
+  pdl_launch_dependents();
+  pdl_wait();
   const int C = a.p.num_classes, P = a.p.num_priors, K = a.p.top_k;
   const int c = blockIdx.x, f = blockIdx.y;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -229,6 +233,8 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
   __shared__ int s_tot;
   __shared__ float s_rows[DVC_MAX_DET * DVC_DET_ROW];
   extern __shared__ __align__(16) uint8_t msm[];          // survivor scores / indices staged for the binary searches
+  pdl_launch_dependents();
+  pdl_wait();
   const int C = a.p.num_classes;
   float* ks = reinterpret_cast<float*>(msm);              // [C][DET_MAXK]
   int* ki = reinterpret_cast<int*>(ks + C * DET_MAXK);    // [C][DET_MAXK]
@@ -369,9 +375,9 @@ int det_launch(const DetLaunch* L, cudaStream_t st) {
   }
   const DetArgs& a = L->args;
   const long long n = (long long)a.B * a.p.num_priors;
-  softmax_kernel<<<(int)ceil_div64(n, 256), 256, 0, st>>>(a);
-  class_nms_kernel<<<dim3(a.p.num_classes, a.B), NMS_THREADS, L->smem_nms, st>>>(a);
-  merge_deliver_kernel<<<a.B, MERGE_THREADS, a.p.num_classes * DET_MAXK * 8, st>>>(a);
+  DVC_CHECK_CUDA(launch_pdl(softmax_kernel, dim3((unsigned)ceil_div64(n, 256)), dim3(256), 0, st, 1, a));
+  DVC_CHECK_CUDA(launch_pdl(class_nms_kernel, dim3(a.p.num_classes, a.B), dim3(NMS_THREADS), (size_t)L->smem_nms, st, 1, a));
+  DVC_CHECK_CUDA(launch_pdl(merge_deliver_kernel, dim3(a.B), dim3(MERGE_THREADS), (size_t)(a.p.num_classes * DET_MAXK * 8), st, 1, a));
   count_launch(3);
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
@@ -413,6 +419,8 @@ constexpr int ANN_THREADS = 512;
 __global__ void __launch_bounds__(ANN_THREADS) annotate_kernel(const AnnArgs a) {
   __shared__ int s_box[DVC_MAX_DET * 4];
   __shared__ int s_n;
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.x;
   const int tid = threadIdx.x;
   const int slot = a.slot_index ? a.slot_index[b] : b;
@@ -562,7 +570,7 @@ extern "C" int dvc_annotate(uint8_t* frames, long long frame_stride, const int* 
   DVC_REQUIRE(!label_masks || n_labels > 0, "annotate: n_labels must be positive");
   AnnArgs a{frames, frame_stride, frame_index, B, h, w, boxes_i, box_count, slot_index, id_mask, id_x, id_y, id_w, id_h,
             label_masks, n_labels, lab_x, lab_y, lab_w, lab_h};
-  annotate_kernel<<<B, ANN_THREADS, 0, (cudaStream_t)stream>>>(a);
+  DVC_CHECK_CUDA(launch_pdl(annotate_kernel, dim3(B), dim3(ANN_THREADS), 0, (cudaStream_t)stream, 1, a));
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;

@@ -78,6 +78,9 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* bres_bar = tmem_empty_bar + 2;                // weights resident
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_bar + 1);
 
+  pdl_launch_dependents();
+  // everything up to pdl_wait() touches only constants (bias, weights, descriptors) and on-chip state, so it overlaps
+  // the tail of the previous kernel when this one was launched programmatically
   for (int i = threadIdx.x; i < g.N; i += GEMM_THREADS) sBias[i] = __ldg(g.bias + i);
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -127,6 +130,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         mbar_arrive_expect_tx(bres_bar, (uint32_t)(g.num_kb * b_stage_bytes));
         for (int kb = 0; kb < g.num_kb; ++kb) tma_load_2d(sB + kb * b_stage_bytes, &tmB, bres_bar, kb * BK, 0);
       }
+      pdl_wait();               // A is the previous kernel's output; the (constant) resident weights are already in flight
       int it = 0;
       const int slice_rows = g.block_n / g.cluster, slice_bytes = b_stage_bytes / g.cluster;
       for (int ct = cluster_id; ct < g.num_ctiles; ct += num_clusters) {
@@ -159,6 +163,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------- MMA issuer
+    pdl_wait();
     if (PAIR && crank != 0) {
       // pair mode: only the leader CTA issues MMAs (they drive both SMs' tensor cores)
     } else if (elect_one()) {
@@ -198,6 +203,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ------------------------------------------------------------- epilogue (2 groups x 4 warps)
     // Group e drains accumulator buffer e, i.e. every second tile of this CTA, so two tiles are in
     // the epilogue at once while the MMA warp fills the buffer the other group has just released.
+    pdl_wait();                                // the output buffer may still be read by an earlier kernel
     const int q = warp & 3;                    // TMEM lane quadrant this warp may access
     const int grp = (warp - 2) >> 2;
     const uint32_t bias_s = smem_u32(sBias);
@@ -441,25 +447,15 @@ int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
     attr_set[dev & 63] = true;
   }
   if (L->args.cluster > 1) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(L->grid);
-    cfg.blockDim = dim3(GEMM_THREADS);
-    cfg.dynamicSmemBytes = (size_t)L->smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)L->args.cluster;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    cudaError_t le = L->args.two_cta ? cudaLaunchKernelEx(&cfg, gemm_f16_kernel<1>, L->tmA, L->tmB, L->tmC, L->args)
-                                     : cudaLaunchKernelEx(&cfg, gemm_f16_kernel<0>, L->tmA, L->tmB, L->tmC, L->args);
+    cudaError_t le = L->args.two_cta ? launch_pdl(gemm_f16_kernel<1>, dim3(L->grid), dim3(GEMM_THREADS), (size_t)L->smem, st, L->args.cluster,
+                                                  L->tmA, L->tmB, L->tmC, L->args)
+                                     : launch_pdl(gemm_f16_kernel<0>, dim3(L->grid), dim3(GEMM_THREADS), (size_t)L->smem, st, L->args.cluster,
+                                                  L->tmA, L->tmB, L->tmC, L->args);
     if (le != cudaSuccess) (void)cudaGetLastError();
     DVC_REQUIRE(le == cudaSuccess, "gemm: cluster launch failed (%s): grid=%d cluster=%d smem=%d pair=%d block_n=%d stages=%d",
                 cudaGetErrorString(le), L->grid, L->args.cluster, L->smem, L->args.two_cta, L->args.block_n, L->args.stages);
   } else {
-    gemm_f16_kernel<0><<<L->grid, GEMM_THREADS, L->smem, st>>>(L->tmA, L->tmB, L->tmC, L->args);
+    DVC_CHECK_CUDA(launch_pdl(gemm_f16_kernel<0>, dim3(L->grid), dim3(GEMM_THREADS), (size_t)L->smem, st, 1, L->tmA, L->tmB, L->tmC, L->args));
   }
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());

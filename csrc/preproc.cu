@@ -33,6 +33,8 @@ struct ResizeArgs {
 template <int RP>
 __global__ void __launch_bounds__(256) resize_u8_kernel(const ResizeArgs a) {
   extern __shared__ __align__(16) uint8_t rs_band[];
+  pdl_launch_dependents();
+  pdl_wait();                   // the destination may still be read by the previous batch's overlay kernel
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
   const int dy0 = blockIdx.x * a.band;
@@ -333,14 +335,13 @@ __global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const P
   uint64_t* mma_done = reinterpret_cast<uint64_t*>(smem + off_bar);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mma_done + 2);
 
+  pdl_launch_dependents();
   const int band = blockIdx.x, b = blockIdx.y;
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   const int oy0 = band * PC_BAND;
   const int iy_first = max(2 * oy0 - 1, 0);
   const int iy_last = min(2 * oy0 + 2 * PC_BAND - 1, PC_NET - 1);
-  const int slot = a.frame_index ? a.frame_index[a.slot0 + b] : a.slot0 + b;
-  const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
   const int row_bytes = a.sw * 3;
 
   if (warp == 0) {
@@ -353,6 +354,9 @@ __global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const P
     tmem_alloc(tmem_slot, 64);
     tmem_relinquish();
   }
+  pdl_wait();                   // the source frames are the resize kernel's output (or a peer's, ordered by the stream)
+  const int slot = a.frame_index ? a.frame_index[a.slot0 + b] : a.slot0 + b;
+  const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
   // ---- stage the source rows this band needs (the NVLink pull when src is a peer pointer)
   const int r_lo = a.ys[iy_first];
   const int r_hi = min(a.ys[iy_last] + 1, a.sh - 1);
@@ -364,7 +368,7 @@ __global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const P
   {
     const uint4* gsrc = reinterpret_cast<const uint4*>(frame + start_al);
     uint4* sdst = reinterpret_cast<uint4*>(s_band);
-    for (int i = tid; i < nvec; i += PC_THREADS) sdst[i] = ldg_nc_v4(gsrc + i);
+    for (int i = tid; i < nvec; i += PC_THREADS) sdst[i] = ldg_v4(gsrc + i);
   }
   if (tid < 32) s_b[tid] = a.b0[tid];
   for (int i = tid; i < PC_NET; i += PC_THREADS) {
@@ -544,7 +548,7 @@ int preproc_launch(const PreprocLaunch* L, cudaStream_t st) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     attr_set[dev & 63] = true;
   }
-  if (L->use_tc) preproc_conv0_tc_kernel<<<L->grid, PC_THREADS, L->smem_tc, st>>>(L->args);
+  if (L->use_tc) DVC_CHECK_CUDA(launch_pdl(preproc_conv0_tc_kernel, L->grid, dim3(PC_THREADS), (size_t)L->smem_tc, st, 1, L->args));
   else preproc_conv0_kernel<<<L->grid, PC_THREADS, L->smem, st>>>(L->args);
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
@@ -593,8 +597,8 @@ extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int
   }
   const bool vec4 = dw % 4 == 0 && dst_frame_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0;
   dim3 grid(ceil_div(dh, band), B);
-  if (vec4) resize_u8_kernel<4><<<grid, 256, (size_t)smem, (cudaStream_t)stream>>>(a);
-  else resize_u8_kernel<1><<<grid, 256, (size_t)smem, (cudaStream_t)stream>>>(a);
+  if (vec4) DVC_CHECK_CUDA(launch_pdl(resize_u8_kernel<4>, grid, dim3(256), (size_t)smem, (cudaStream_t)stream, 1, a));
+  else DVC_CHECK_CUDA(launch_pdl(resize_u8_kernel<1>, grid, dim3(256), (size_t)smem, (cudaStream_t)stream, 1, a));
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;

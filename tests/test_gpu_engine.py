@@ -133,6 +133,37 @@ def test_process_stream_matches_sync(engines):
             assert np.array_equal(a[2][k, : a[3][k]], b[2][k, : b[3][k]])
 
 
+def test_programmatic_dependent_launch_equals_serialized(graph, monkeypatch):
+    """Every hot kernel is launched with programmatic stream serialization (next kernel resident while this one
+    drains, griddepcontrol.wait before it touches produced data).  Results must be bit-identical to fully
+    serialized launches (DVC_PDL=0), eagerly and through CUDA-graph replays, on back-to-back batches."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    frames = [torch.from_numpy(_frames(16, 300, 300, seed=40 + i)).cuda() for i in range(3)]
+    monkeypatch.setenv("DVC_PDL", "0")
+    ser = NativeEngine(graph, "cuda:0", Config(), requester_id="127.0.0.1:5554")
+    st0 = ser.state(16, 300, 300)
+    want = []
+    for f in frames:
+        ser.run(st0, use_graph=False, src=f)
+        torch.cuda.synchronize()
+        want.append([t.clone() for t in (st0.det, st0.det_count, st0.box_count, st0.frames400)])
+    monkeypatch.setenv("DVC_PDL", "1")
+    pdl = NativeEngine(graph, "cuda:0", Config(), requester_id="127.0.0.1:5554")
+    st1 = pdl.state(16, 300, 300)
+    for use_graph in (False, True):
+        for rep in range(4):
+            got = []
+            for f in frames:                      # back to back, no sync between batches: the chain spans batches
+                pdl.run(st1, use_graph=use_graph, src=f)
+                got.append([t.clone() for t in (st1.det, st1.det_count, st1.box_count, st1.frames400)])
+            torch.cuda.synchronize()
+            for w, g in zip(want, got):
+                for a, b in zip(w, g):
+                    assert torch.equal(a, b), (use_graph, rep)
+    ser.close(); pdl.close()
+
+
 def test_graft_entry_smoke():
     import __graft_entry__ as g
     g.smoke()
