@@ -55,6 +55,9 @@ struct DetArgs {
   const int* slot_index;
   float* det; int* det_count; int* boxes_i; int* box_count;
   uint32_t* flags; uint32_t flag_value;
+  // K14 epoch gate (all optional): deliver only if this GPU's membership epoch word still equals the epoch the
+  // batch was dispatched under; otherwise count the frame in *stale_count and leave the sinks untouched
+  const uint32_t* epoch_now; const uint32_t* epoch_expect; uint32_t* stale_count;
   // global scratch (per frame): prob [C][P], kept_n [C], kept_score [C][K], kept_idx [C][K], kept_box [C][K][4]
   float* prob; int* kept_n; float* kept_score; int* kept_idx; float* kept_box;
 };
@@ -231,11 +234,21 @@ __global__ void __launch_bounds__(NMS_THREADS) class_nms_kernel(const DetArgs a)
 __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetArgs a) {
   __shared__ int s_n[DET_MAXC];
   __shared__ int s_tot;
+  __shared__ int s_stale;
   __shared__ float s_rows[DVC_MAX_DET * DVC_DET_ROW];
   extern __shared__ __align__(16) uint8_t msm[];          // survivor scores / indices staged for the binary searches
   pdl_launch_dependents();
   pdl_wait();
   const int C = a.p.num_classes;
+  if (threadIdx.x == 0) {
+    // a dispatch made under an older membership epoch must not land in rings that may have been re-assigned
+    int stale = 0;
+    if (a.epoch_now && a.epoch_expect) stale = ld_acquire_sys_u32(a.epoch_now) != ld_acquire_sys_u32(a.epoch_expect);
+    if (stale && a.stale_count) atomicAdd(a.stale_count, 1u);
+    s_stale = stale;
+  }
+  __syncthreads();
+  if (s_stale) return;
   float* ks = reinterpret_cast<float*>(msm);              // [C][DET_MAXK]
   int* ki = reinterpret_cast<int*>(ks + C * DET_MAXK);    // [C][DET_MAXK]
   const int f = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -350,6 +363,7 @@ int det_prepare(DetLaunch* L, const float* loc, const float* conf, const float* 
   DetArgs& a = L->args;
   a.loc = loc; a.conf = conf; a.priors = priors; a.variances = variances; a.B = B; a.p = *p; a.slot_index = slot_index;
   a.det = det; a.det_count = det_count; a.boxes_i = boxes_i; a.box_count = box_count; a.flags = flags; a.flag_value = flag_value;
+  a.epoch_now = nullptr; a.epoch_expect = nullptr; a.stale_count = nullptr;      // gate off until det_set_epoch_gate
   const int C = p->num_classes, P = p->num_priors;
   uint8_t* s = reinterpret_cast<uint8_t*>(scratch);
   a.prob = reinterpret_cast<float*>(s);
@@ -386,6 +400,9 @@ int det_launch(const DetLaunch* L, cudaStream_t st) {
 DetLaunch* det_alloc() { return new DetLaunch(); }
 void det_free(DetLaunch* L) { delete L; }
 void det_set_flag_value(DetLaunch* L, uint32_t v) { L->args.flag_value = v; }
+void det_set_epoch_gate(DetLaunch* L, const uint32_t* now, const uint32_t* expect, uint32_t* stale_count) {
+  L->args.epoch_now = now; L->args.epoch_expect = expect; L->args.stale_count = stale_count;
+}
 void det_set_sinks(DetLaunch* L, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index) {
   L->args.det = det; L->args.det_count = det_count; L->args.boxes_i = boxes_i; L->args.box_count = box_count;
   L->args.flags = flags; L->args.slot_index = slot_index;

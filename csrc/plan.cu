@@ -34,6 +34,7 @@ int det_launch(const DetLaunch* L, cudaStream_t st);
 DetLaunch* det_alloc();
 void det_free(DetLaunch*);
 void det_set_flag_value(DetLaunch*, uint32_t);
+void det_set_epoch_gate(DetLaunch*, const uint32_t* now, const uint32_t* expect, uint32_t* stale_count);
 void det_set_sinks(DetLaunch*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index);
 
 struct DwLaunch;
@@ -154,6 +155,14 @@ extern "C" int dvc_plan_set_flag_value(dvc_plan* p, uint32_t flag_value) {
   DVC_REQUIRE(p, "plan is null");
   for (auto& op : p->ops)
     if (op.kind == OP_DET) det_set_flag_value(op.det, flag_value);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_set_epoch_gate(dvc_plan* p, const uint32_t* epoch_now, const uint32_t* epoch_expect, uint32_t* stale_count) {
+  DVC_REQUIRE(p, "plan is null");
+  DVC_REQUIRE((epoch_now == nullptr) == (epoch_expect == nullptr), "epoch gate: give both epoch words or neither");
+  for (auto& op : p->ops)
+    if (op.kind == OP_DET) det_set_epoch_gate(op.det, epoch_now, epoch_expect, stale_count);
   return DVC_OK;
 }
 

@@ -341,6 +341,24 @@ class NativeEngine:
                 delattr(st, key)
         st.remote = True
 
+    def set_epoch_gate(self, st: _ShapeState, epoch_now: Optional[torch.Tensor], epoch_expect: Optional[torch.Tensor],
+                       stale_count: Optional[torch.Tensor] = None):
+        """K14: gate this state's delivery on the membership epoch.  ``epoch_now`` is the int32 device word
+        `publish_epoch` / `dvc_epoch_broadcast` writes on this GPU, ``epoch_expect`` the int32 device word the
+        dispatcher sets to the epoch a batch is sent under; when they differ the deliver kernel writes nothing
+        (no rows, counts or flags) and adds one per frame to ``stale_count``.  Pointers are baked into the plan
+        (and any CUDA graph captured later), the values are read at run time.  ``None`` switches the gate off."""
+        L = self.L
+        for t in (epoch_now, epoch_expect, stale_count):
+            assert t is None or (t.is_cuda and t.dtype == torch.int32 and t.numel() >= 1)
+        st.epoch_gate = (epoch_now, epoch_expect, stale_count)        # keep the tensors alive
+        L.check(self.lib.dvc_plan_set_epoch_gate(st.plan, L.ptr(epoch_now) if epoch_now is not None else None,
+                                                 L.ptr(epoch_expect) if epoch_expect is not None else None,
+                                                 L.ptr(stale_count) if stale_count is not None else None), "plan_set_epoch_gate")
+        for key in ("graph_ann", "graph_noann"):
+            if hasattr(st, key):
+                delattr(st, key)
+
     def run(self, st: _ShapeState, annotate: bool = True, use_graph: Optional[bool] = None,
             src: Optional[torch.Tensor] = None, resize: bool = True):
         """Process the frames in ``st.raw`` (or in ``src``, a device batch of the same shape).

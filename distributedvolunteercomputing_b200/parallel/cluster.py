@@ -82,6 +82,12 @@ class BoxCluster:
         ptrs = p2p.exchange({"ctrl": self.ctrl}, self.dev, None)["ctrl"]
         self.ctrl_ptrs = ptrs
         self.epoch_word = self.ctrl.tensor(torch.int32, (1,))
+        self.epoch_word.zero_()
+        # K14 gate: every lane's deliver kernel compares epoch_word (written by the client's broadcast) with
+        # epoch_expect (the epoch this rank dispatches under) and counts rejected frames in stale_frames
+        self.epoch_expect = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        self.stale_frames = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        torch.cuda.synchronize(self.dev)
         self.weight_blob = self.ctrl.tensor(torch.uint8, (total,), offset_bytes=256)
         if self.is_client:
             self._epoch_targets = p2p.device_ptr_array(ptrs, self.dev)
@@ -103,10 +109,24 @@ class BoxCluster:
         self.dist.barrier()
 
     def publish_epoch(self, epoch: int):
-        """K14: write the membership epoch word into every GPU's control block (release at system scope)."""
+        """K14: write the membership epoch word into every GPU's control block (release at system scope), then every
+        rank adopts it as the epoch it dispatches under.  Collective (barrier inside): batches already in flight
+        that reach their deliver kernel after the word changed are rejected and counted in ``stale_frames``."""
         self.epoch = epoch
-        if self.is_client:
-            L.check(self.engine.lib.dvc_epoch_broadcast(L.ptr(self._epoch_targets), self.world, epoch, L.stream_ptr()), "epoch")
+        with torch.cuda.device(self.dev):
+            if self.is_client:
+                L.check(self.engine.lib.dvc_epoch_broadcast(L.ptr(self._epoch_targets), self.world, epoch, L.stream_ptr()), "epoch")
+                torch.cuda.current_stream().synchronize()
+            self.dist.barrier()
+            self.dispatch_epoch(epoch)
+
+    def dispatch_epoch(self, epoch: int):
+        """The epoch this rank's following steps are dispatched under (stream-ordered device word)."""
+        self.epoch_expect.fill_(int(epoch))
+
+    def stale_count(self) -> int:
+        """Frames this rank's deliver kernels rejected so far because the membership epoch had moved on."""
+        return int(self.stale_frames.item())
 
     def _make_lane(self, k: int) -> _Lane:
         dist, eng, B, n = self.dist, self.engine, self.B, self.n
@@ -145,6 +165,7 @@ class BoxCluster:
             ln.raw_mine = torch.as_strided(ln.raw_mine, (B, self.H, self.W, 3), (raw_bytes, self.W * 3, 3, 1))
             ln.my_boxes = p2p.tensor_from_ptr(sinks["boxes_ptr"], (B, 100, 4), torch.int32, self.dev)
             ln.my_box_count = p2p.tensor_from_ptr(sinks["box_count_ptr"], (B,), torch.int32, self.dev)
+        eng.set_epoch_gate(st, self.epoch_word, self.epoch_expect, self.stale_frames)
         ln.tok = torch.zeros(1, device=self.dev)
         if self.is_client:
             if self.mode == "pull_400":

@@ -192,6 +192,11 @@ int dvc_plan_set_source(dvc_plan*, const uint8_t* src400, long long src_frame_st
 int dvc_plan_set_sinks(dvc_plan*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags,
                        const int* slot_index);
 int dvc_plan_set_flag_value(dvc_plan*, uint32_t flag_value);
+/* K14 epoch gate (server.py:104-154 has only host-side lists): the deliver kernel compares the membership epoch
+ * word of this GPU (written by dvc_epoch_broadcast) with the epoch the batch was dispatched under (a device word
+ * the dispatcher writes); on mismatch the frame is not delivered (sinks and flags untouched) and *stale_count is
+ * incremented once per frame so the scheduler can re-dispatch.  Pass NULLs to switch the gate off. */
+int dvc_plan_set_epoch_gate(dvc_plan*, const uint32_t* epoch_now, const uint32_t* epoch_expect, uint32_t* stale_count);
 int dvc_plan_run(dvc_plan*, void* stream);
 
 /* ---- P2P substrate (csrc/p2p.cu).  These DO allocate / map device memory (set-up time only).

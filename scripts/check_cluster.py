@@ -52,4 +52,21 @@ for use_graph, mode in ((False, "pull_400"), (True, "pull_400"), (False, "pull_r
         assert int(cl.det_count.sum()) > 0
         print(f"cluster check ok: world={world} mode={mode} graph={use_graph} detections={int(cl.det_count.sum())}", flush=True)
     dist.barrier()
+    if mode == "pull_raw" and use_graph and world > 1:
+        # K14 gate: the last rank dispatches one batch under an old epoch -> its rows must not land on the client
+        if rank == 0:
+            cl.det_count.fill_(-7); cl.flags.zero_(); cl.raw_all.copy_(frames)
+        torch.cuda.synchronize(); dist.barrier()
+        if rank == world - 1:
+            cl.dispatch_epoch(1)
+        cl.step()
+        torch.cuda.synchronize(); dist.barrier()
+        assert cl.stale_count() == (B if rank == world - 1 else 0), (rank, cl.stale_count())
+        if rank == 0:
+            last = slice((world - 1) * B, world * B)
+            assert (cl.det_count[last] == -7).all() and (cl.flags[last] == 0).all(), "stale rows were delivered"
+            assert (cl.det_count[: (world - 1) * B] >= 0).all() and (cl.flags[: (world - 1) * B] == 1).all()
+            print(f"epoch gate ok: world={world} stale frames rejected on rank {world - 1}", flush=True)
+        cl.dispatch_epoch(cl.epoch)
+        dist.barrier()
 dist.destroy_process_group()

@@ -164,6 +164,42 @@ def test_programmatic_dependent_launch_equals_serialized(graph, monkeypatch):
     ser.close(); pdl.close()
 
 
+def test_epoch_gate_rejects_stale_dispatch(graph):
+    """K14: the deliver kernel compares this GPU's membership epoch word with the epoch the batch was sent under;
+    a stale batch delivers nothing and is counted, a current one is delivered (eager and through a CUDA graph)."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    eng = NativeEngine(graph, "cuda:0", Config(), requester_id="127.0.0.1:5554")
+    frames = torch.from_numpy(_frames(5, 300, 300, seed=77)).cuda()
+    st = eng.state(5, 300, 300)
+    eng.run(st, use_graph=False, src=frames)
+    torch.cuda.synchronize()
+    want = (st.det.clone(), st.det_count.clone(), st.box_count.clone())
+    now = torch.tensor([3], dtype=torch.int32, device="cuda:0")
+    expect = torch.tensor([3], dtype=torch.int32, device="cuda:0")
+    stale = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    eng.set_epoch_gate(st, now, expect, stale)
+    for use_graph in (False, True):
+        stale.zero_(); expect.fill_(3)
+        st.det.fill_(-5.0); st.det_count.fill_(-9); st.box_count.fill_(-9)
+        eng.run(st, use_graph=use_graph, src=frames)
+        torch.cuda.synchronize()
+        assert int(stale.item()) == 0
+        assert torch.equal(st.det, want[0]) and torch.equal(st.det_count, want[1]) and torch.equal(st.box_count, want[2])
+        now.fill_(4)                                    # membership changed after the dispatch
+        st.det.fill_(-5.0); st.det_count.fill_(-9); st.box_count.fill_(-9)
+        eng.run(st, use_graph=use_graph, src=frames)
+        torch.cuda.synchronize()
+        assert int(stale.item()) == 5                   # one per frame
+        assert (st.det == -5.0).all() and (st.det_count == -9).all() and (st.box_count == -9).all()
+        now.fill_(3)
+    eng.set_epoch_gate(st, None, None, None)
+    eng.run(st, use_graph=False, src=frames)
+    torch.cuda.synchronize()
+    assert torch.equal(st.det_count, want[1])
+    eng.close()
+
+
 def test_graft_entry_smoke():
     import __graft_entry__ as g
     g.smoke()
