@@ -58,6 +58,7 @@ struct DetArgs {
   // K14 epoch gate (all optional): deliver only if this GPU's membership epoch word still equals the epoch the
   // batch was dispatched under; otherwise count the frame in *stale_count and leave the sinks untouched
   const uint32_t* epoch_now; const uint32_t* epoch_expect; uint32_t* stale_count;
+  unsigned long long* t_done;      // optional [B]: %globaltimer when a frame's rows have been delivered
   // global scratch (per frame): prob [C][P], kept_n [C], kept_score [C][K], kept_idx [C][K], kept_box [C][K][4]
   float* prob; int* kept_n; float* kept_score; int* kept_idx; float* kept_box;
 };
@@ -329,6 +330,7 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
   __threadfence_system();
   __syncthreads();
   if (tid == 0 && a.flags) st_release_sys_u32(a.flags + slot, a.flag_value);
+  if (tid == 0 && a.t_done) a.t_done[f] = globaltimer_ns();
 }
 
 struct DetLaunch {
@@ -364,6 +366,7 @@ int det_prepare(DetLaunch* L, const float* loc, const float* conf, const float* 
   a.loc = loc; a.conf = conf; a.priors = priors; a.variances = variances; a.B = B; a.p = *p; a.slot_index = slot_index;
   a.det = det; a.det_count = det_count; a.boxes_i = boxes_i; a.box_count = box_count; a.flags = flags; a.flag_value = flag_value;
   a.epoch_now = nullptr; a.epoch_expect = nullptr; a.stale_count = nullptr;      // gate off until det_set_epoch_gate
+  a.t_done = nullptr;
   const int C = p->num_classes, P = p->num_priors;
   uint8_t* s = reinterpret_cast<uint8_t*>(scratch);
   a.prob = reinterpret_cast<float*>(s);
@@ -400,6 +403,7 @@ int det_launch(const DetLaunch* L, cudaStream_t st) {
 DetLaunch* det_alloc() { return new DetLaunch(); }
 void det_free(DetLaunch* L) { delete L; }
 void det_set_flag_value(DetLaunch* L, uint32_t v) { L->args.flag_value = v; }
+void det_set_timestamps(DetLaunch* L, unsigned long long* t_done) { L->args.t_done = t_done; }
 void det_set_epoch_gate(DetLaunch* L, const uint32_t* now, const uint32_t* expect, uint32_t* stale_count) {
   L->args.epoch_now = now; L->args.epoch_expect = expect; L->args.stale_count = stale_count;
 }

@@ -34,6 +34,8 @@ int det_launch(const DetLaunch* L, cudaStream_t st);
 DetLaunch* det_alloc();
 void det_free(DetLaunch*);
 void det_set_flag_value(DetLaunch*, uint32_t);
+void det_set_timestamps(DetLaunch*, unsigned long long* t_done);
+void preproc_set_timestamps(PreprocLaunch*, unsigned long long* t_ingest);
 void det_set_epoch_gate(DetLaunch*, const uint32_t* now, const uint32_t* expect, uint32_t* stale_count);
 void det_set_sinks(DetLaunch*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index);
 
@@ -155,6 +157,15 @@ extern "C" int dvc_plan_set_flag_value(dvc_plan* p, uint32_t flag_value) {
   DVC_REQUIRE(p, "plan is null");
   for (auto& op : p->ops)
     if (op.kind == OP_DET) det_set_flag_value(op.det, flag_value);
+  return DVC_OK;
+}
+
+extern "C" int dvc_plan_set_timestamps(dvc_plan* p, unsigned long long* t_ingest, unsigned long long* t_done) {
+  DVC_REQUIRE(p, "plan is null");
+  for (auto& op : p->ops) {
+    if (op.kind == OP_PREPROC) preproc_set_timestamps(op.pre, t_ingest);
+    if (op.kind == OP_DET) det_set_timestamps(op.det, t_done);
+  }
   return DVC_OK;
 }
 

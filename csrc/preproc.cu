@@ -170,6 +170,7 @@ struct PreprocArgs {
   __half* out;
   int band_bytes;     // smem bytes reserved for the staged source rows
   int slot0;          // first source slot of this launch (sub-batch offset inside the ring)
+  unsigned long long* t_ingest;   // optional [B]: %globaltimer when the first CTA of a frame starts pulling it
 };
 
 __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const PreprocArgs a) {
@@ -188,6 +189,7 @@ __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const Prep
   const int iy_last = min(2 * oy0 + 2 * PC_BAND - 1, PC_NET - 1);
   const int slot = a.frame_index ? a.frame_index[a.slot0 + b] : a.slot0 + b;
   const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
+  if (a.t_ingest && band == 0 && tid == 0) a.t_ingest[a.slot0 + b] = globaltimer_ns();
   const int row_bytes = a.sw * 3;
 
   // ---- stage the source rows this band needs (the NVLink pull when src is a peer pointer)
@@ -357,6 +359,7 @@ __global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const P
   pdl_wait();                   // the source frames are the resize kernel's output (or a peer's, ordered by the stream)
   const int slot = a.frame_index ? a.frame_index[a.slot0 + b] : a.slot0 + b;
   const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
+  if (a.t_ingest && band == 0 && tid == 0) a.t_ingest[a.slot0 + b] = globaltimer_ns();
   // ---- stage the source rows this band needs (the NVLink pull when src is a peer pointer)
   const int r_lo = a.ys[iy_first];
   const int r_hi = min(a.ys[iy_last] + 1, a.sh - 1);
@@ -526,6 +529,7 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
   a.mean0 = h_mean3[0]; a.mean1 = h_mean3[1]; a.mean2 = h_mean3[2]; a.scale = scale;
   a.out = reinterpret_cast<__half*>(out);
   a.slot0 = slot0;
+  a.t_ingest = nullptr;
   // worst-case staged rows for one band: 17 net rows span at most ceil(17*sh/300)+2 source rows
   if (band_rows_max <= 0) band_rows_max = (PC_PROWS * sh + PC_NET - 1) / PC_NET + 3;
   if (band_rows_max > sh) band_rows_max = sh;
@@ -557,6 +561,7 @@ int preproc_launch(const PreprocLaunch* L, cudaStream_t st) {
 
 PreprocLaunch* preproc_alloc() { return new PreprocLaunch(); }
 void preproc_free(PreprocLaunch* L) { delete L; }
+void preproc_set_timestamps(PreprocLaunch* L, unsigned long long* t_ingest) { L->args.t_ingest = t_ingest; }
 void preproc_set_source(PreprocLaunch* L, const uint8_t* src, long long stride, const int* frame_index) {
   L->args.src = src;
   L->args.src_stride = stride;

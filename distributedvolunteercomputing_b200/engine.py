@@ -341,6 +341,28 @@ class NativeEngine:
                 delattr(st, key)
         st.remote = True
 
+    def enable_timestamps(self, st: _ShapeState, on: bool = True):
+        """Device-side trace points: per frame, the %globaltimer nanosecond when K1b starts pulling it and when K9
+        has delivered its rows (``st.t_ingest`` / ``st.t_done``, int64 [B] on the device).  The reference only
+        prints one wall-clock line per job (worker.py:105,219).  Must precede graph capture of this state."""
+        L = self.L
+        if on:
+            B = st.raw.shape[0]
+            st.t_ingest = torch.zeros(B, dtype=torch.int64, device=self.device)
+            st.t_done = torch.zeros(B, dtype=torch.int64, device=self.device)
+            L.check(self.lib.dvc_plan_set_timestamps(st.plan, L.ptr(st.t_ingest), L.ptr(st.t_done)), "plan_set_timestamps")
+        else:
+            L.check(self.lib.dvc_plan_set_timestamps(st.plan, None, None), "plan_set_timestamps")
+            st.t_ingest = st.t_done = None
+        for key in ("graph_ann", "graph_noann"):
+            if hasattr(st, key):
+                delattr(st, key)
+
+    def frame_latency_us(self, st: _ShapeState) -> np.ndarray:
+        """Per-frame device latency (ingest -> delivered) of the last batch run on ``st``, in microseconds."""
+        assert getattr(st, "t_done", None) is not None, "call enable_timestamps(st) first"
+        return ((st.t_done - st.t_ingest).cpu().numpy().astype(np.float64)) / 1e3
+
     def set_epoch_gate(self, st: _ShapeState, epoch_now: Optional[torch.Tensor], epoch_expect: Optional[torch.Tensor],
                        stale_count: Optional[torch.Tensor] = None):
         """K14: gate this state's delivery on the membership epoch.  ``epoch_now`` is the int32 device word

@@ -25,7 +25,7 @@ class ClockSampler:
     def __init__(self, gpu_index: int = 0, period_ms: Optional[int] = None, backend: Optional[str] = None,
                  pci_bus_id: Optional[str] = None):
         self.gpu_index = gpu_index
-        self.period_ms = int(period_ms if period_ms is not None else os.environ.get("DVC_CLOCK_PERIOD_MS", 100))
+        self.period_ms = int(period_ms if period_ms is not None else os.environ.get("DVC_CLOCK_PERIOD_MS", 50))
         self.backend = backend or os.environ.get("DVC_CLOCK_BACKEND", "smi")
         self.pci_bus_id = pci_bus_id
         self.proc: Optional[subprocess.Popen] = None

@@ -192,6 +192,10 @@ int dvc_plan_set_source(dvc_plan*, const uint8_t* src400, long long src_frame_st
 int dvc_plan_set_sinks(dvc_plan*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags,
                        const int* slot_index);
 int dvc_plan_set_flag_value(dvc_plan*, uint32_t flag_value);
+/* Device-side trace points (the reference has one wall-clock line per job, worker.py:105,219): two optional arrays of
+ * B nanosecond %globaltimer stamps indexed by the frame's position in the batch - when K1b starts pulling the frame,
+ * and when K9 has delivered its rows.  NULL switches a stamp off. */
+int dvc_plan_set_timestamps(dvc_plan*, unsigned long long* t_ingest, unsigned long long* t_done);
 /* K14 epoch gate (server.py:104-154 has only host-side lists): the deliver kernel compares the membership epoch
  * word of this GPU (written by dvc_epoch_broadcast) with the epoch the batch was dispatched under (a device word
  * the dispatcher writes); on mismatch the frame is not delivered (sinks and flags untouched) and *stale_count is

@@ -200,6 +200,27 @@ def test_epoch_gate_rejects_stale_dispatch(graph):
     eng.close()
 
 
+def test_device_timestamps(graph):
+    """%globaltimer trace points written by K1b (ingest) and K9 (delivered): ordered, plausible, refreshed per run."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    eng = NativeEngine(graph, "cuda:0", Config(), requester_id="127.0.0.1:5554")
+    frames = torch.from_numpy(_frames(6, 300, 300, seed=5)).cuda()
+    st = eng.state(6, 300, 300)
+    eng.enable_timestamps(st)
+    last = None
+    for use_graph in (False, True, True):
+        eng.run(st, use_graph=use_graph, src=frames)
+        torch.cuda.synchronize()
+        lat = eng.frame_latency_us(st)
+        assert lat.shape == (6,) and (lat > 1.0).all() and (lat < 1e6).all(), lat
+        done = st.t_done.clone()
+        if last is not None:
+            assert (done > last).all()
+        last = done
+    eng.close()
+
+
 def test_graft_entry_smoke():
     import __graft_entry__ as g
     g.smoke()
