@@ -46,7 +46,7 @@ __global__ void priorbox_kernel(float* boxes, float* variances, int prior_off, i
 constexpr int DET_MAXC = 32;      // classes
 constexpr int DET_MAXK = 128;     // per-class top_k capacity
 constexpr int NMS_THREADS = 128;
-constexpr int MERGE_THREADS = 1024;   // the binary searches are dependent shared-memory chains: hide them with warps
+constexpr int MERGE_THREADS = 1024;   // one compare-exchange per thread and stage for up to 2048 survivors
 
 struct DetArgs {
   const float *loc, *conf, *priors, *variances;
@@ -234,10 +234,11 @@ __global__ void __launch_bounds__(NMS_THREADS) class_nms_kernel(const DetArgs a)
 
 __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetArgs a) {
   __shared__ int s_n[DET_MAXC];
+  __shared__ int s_off[DET_MAXC];
   __shared__ int s_tot;
   __shared__ int s_stale;
   __shared__ float s_rows[DVC_MAX_DET * DVC_DET_ROW];
-  extern __shared__ __align__(16) uint8_t msm[];          // survivor scores / indices staged for the binary searches
+  extern __shared__ __align__(16) uint8_t msm[];          // sort keys of the survivors
   pdl_launch_dependents();
   pdl_wait();
   const int C = a.p.num_classes;
@@ -250,8 +251,7 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
   }
   __syncthreads();
   if (s_stale) return;
-  float* ks = reinterpret_cast<float*>(msm);              // [C][DET_MAXK]
-  int* ki = reinterpret_cast<int*>(ks + C * DET_MAXK);    // [C][DET_MAXK]
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(msm);   // survivors of all classes, one sort key each
   const int f = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int slot = a.slot_index ? a.slot_index[f] : f;
   const int* kept_n = a.kept_n + (size_t)f * C;
@@ -261,40 +261,49 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
   if (tid < DET_MAXC) s_n[tid] = tid < C ? kept_n[tid] : 0;
   for (int e = tid; e < DVC_MAX_DET * DVC_DET_ROW; e += MERGE_THREADS) s_rows[e] = 0.f;
   __syncthreads();
-  for (int e = tid; e < C * DET_MAXK; e += MERGE_THREADS) {
-    const int c = e / DET_MAXK, r = e - c * DET_MAXK;
-    if (r < s_n[c]) { ks[e] = gks[e]; ki[e] = gki[e]; }
-  }
-  __syncthreads();
   if (tid == 0) {
     int t = 0;
-    for (int c = 0; c < C; ++c) t += s_n[c];
+    for (int c = 0; c < C; ++c) { s_off[c] = t; t += s_n[c]; }
     s_tot = t;
   }
   __syncthreads();
-  const int n_out = min(s_tot, min(a.p.keep_top_k, DVC_MAX_DET));
-  // global rank of a survivor = sum over classes of survivors that sort before it (binary search per class)
+  // Global keep-top-k = one bitonic sort of all survivors in shared memory.  Key (ascending = output order):
+  // [63:32] ~orderable(score) (score desc), [24:12] prior index asc, [11:7] class asc, [6:0] slot in the class list.
+  int ns = 2;
+  while (ns < s_tot) ns <<= 1;
   for (int e = tid; e < C * DET_MAXK; e += MERGE_THREADS) {
     const int c = e / DET_MAXK, r = e - c * DET_MAXK;
-    if (r >= s_n[c]) continue;
-    const float s = ks[c * DET_MAXK + r];
-    const int id = ki[c * DET_MAXK + r];
-    int rank = 0;
-    for (int c2 = 0; c2 < C; ++c2) {
-      int lo = 0, hi = s_n[c2];
-      while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        if (before(ks[c2 * DET_MAXK + mid], ki[c2 * DET_MAXK + mid], c2, s, id, c)) lo = mid + 1;
-        else hi = mid;
+    if (r < s_n[c]) {
+      uint32_t u = __float_as_uint(gks[e]);
+      u ^= (u >> 31) ? 0xFFFFFFFFu : 0x80000000u;                  // monotonic in the float order
+      keys[s_off[c] + r] = ((unsigned long long)(~u) << 32) | ((unsigned long long)(uint32_t)gki[e] << 12) |
+                           ((unsigned long long)c << 7) | (unsigned long long)r;
+    }
+  }
+  for (int i = s_tot + tid; i < ns; i += MERGE_THREADS) keys[i] = ~0ull;
+  __syncthreads();
+  for (int k = 2; k <= ns; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < ns; i += MERGE_THREADS) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const unsigned long long x = keys[i], y = keys[ixj];
+          if ((x > y) == ((i & k) == 0)) { keys[i] = y; keys[ixj] = x; }
+        }
       }
-      rank += lo;
+      __syncthreads();
     }
-    if (rank < n_out) {
-      float* row = s_rows + rank * DVC_DET_ROW;
-      const float* bx = kb + (size_t)(c * DET_MAXK + r) * 4;
-      row[0] = 0.f; row[1] = (float)c; row[2] = s;
-      row[3] = bx[0]; row[4] = bx[1]; row[5] = bx[2]; row[6] = bx[3];
-    }
+  }
+  const int n_out = min(s_tot, min(a.p.keep_top_k, DVC_MAX_DET));
+  if (tid < n_out) {
+    const unsigned long long key = keys[tid];
+    const int r = (int)(key & 127u), c = (int)((key >> 7) & 31u);
+    uint32_t u = ~(uint32_t)(key >> 32);
+    u = (u & 0x80000000u) ? (u ^ 0x80000000u) : ~u;
+    float* row = s_rows + tid * DVC_DET_ROW;
+    const float* bx = kb + (size_t)(c * DET_MAXK + r) * 4;
+    row[0] = 0.f; row[1] = (float)c; row[2] = __uint_as_float(u);
+    row[3] = bx[0]; row[4] = bx[1]; row[5] = bx[2]; row[6] = bx[3];
   }
   __syncthreads();
   // rows (zero padded) go out with coalesced stores; `det` may be peer memory (the gather)
@@ -331,6 +340,13 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
   __syncthreads();
   if (tid == 0 && a.flags) st_release_sys_u32(a.flags + slot, a.flag_value);
   if (tid == 0 && a.t_done) a.t_done[f] = globaltimer_ns();
+}
+
+// one 8-byte sort key per per-class survivor slot, padded to a power of two for the bitonic network
+static int merge_smem_bytes(int C) {
+  int n = 2;
+  while (n < C * DET_MAXK) n <<= 1;
+  return n * 8;
 }
 
 struct DetLaunch {
@@ -394,7 +410,7 @@ int det_launch(const DetLaunch* L, cudaStream_t st) {
   const long long n = (long long)a.B * a.p.num_priors;
   DVC_CHECK_CUDA(launch_pdl(softmax_kernel, dim3((unsigned)ceil_div64(n, 256)), dim3(256), 0, st, 1, a));
   DVC_CHECK_CUDA(launch_pdl(class_nms_kernel, dim3(a.p.num_classes, a.B), dim3(NMS_THREADS), (size_t)L->smem_nms, st, 1, a));
-  DVC_CHECK_CUDA(launch_pdl(merge_deliver_kernel, dim3(a.B), dim3(MERGE_THREADS), (size_t)(a.p.num_classes * DET_MAXK * 8), st, 1, a));
+  DVC_CHECK_CUDA(launch_pdl(merge_deliver_kernel, dim3(a.B), dim3(MERGE_THREADS), (size_t)merge_smem_bytes(a.p.num_classes), st, 1, a));
   count_launch(3);
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
