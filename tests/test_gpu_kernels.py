@@ -111,7 +111,7 @@ def test_im2col_matches_unfold(K, B, H, W, C):
     assert torch.equal(col.float(), u)
 
 
-@pytest.mark.parametrize("H,W", [(300, 300), (480, 640), (720, 1280), (600, 800), (1080, 1920), (333, 517)])
+@pytest.mark.parametrize("H,W", [(300, 300), (480, 640), (720, 1280), (600, 800), (1080, 1920), (333, 517), (240, 320), (200, 301), (150, 202), (97, 399)])
 def test_resize_area_matches_cv2(K, H, W):
     cv2 = pytest.importorskip("cv2")
     rng = np.random.default_rng(H)
