@@ -18,13 +18,13 @@ import queue
 import socket
 import threading
 import time
-from typing import Dict, List, Optional, Set, Tuple
+from typing import Dict, List, Optional, Set
 
 import numpy as np
 
 from . import protocol as proto
 from .config import Config
-from .parallel.scheduler import Batch, Scheduler
+from .parallel.scheduler import Scheduler
 from .utils.metrics import Logger, Metrics
 
 

@@ -11,7 +11,7 @@ CPU and GPU agree exactly and set-comparison against cv2 is stable.
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np

@@ -14,9 +14,7 @@ timeout (the reference hangs forever on a dead peer and on quit), and ports are 
 """
 from __future__ import annotations
 
-import json
 import socket
-import time
 from dataclasses import dataclass
 from typing import List, Optional, Sequence, Tuple
 

@@ -13,7 +13,7 @@ from __future__ import annotations
 
 import os
 import time
-from typing import Iterator, List, Optional, Tuple
+from typing import Iterator, List, Optional
 
 import numpy as np
 

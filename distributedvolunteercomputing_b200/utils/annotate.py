@@ -6,7 +6,7 @@ FONT_HERSHEY_SIMPLEX scale 0.5 thickness 2.
 """
 from __future__ import annotations
 
-from typing import Iterable, Sequence, Tuple
+from typing import Sequence, Tuple
 
 import numpy as np
 

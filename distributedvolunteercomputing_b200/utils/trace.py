@@ -8,7 +8,6 @@ from __future__ import annotations
 
 import contextlib
 import time
-from typing import Optional
 
 try:
     import torch
