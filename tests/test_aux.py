@@ -1,0 +1,174 @@
+"""Auxiliary subsystems: thread-safety of the scheduler under real threads (the reference shares plain
+lists between threads without locks, server.py:20-24 / worker.py:33-38), property tests for the reorder buffer and the
+wire header, metrics / trace / clock-sampler helpers.  CPU only."""
+import json
+import random
+import threading
+import time
+
+import numpy as np
+from hypothesis import given, settings, strategies as st
+
+from distributedvolunteercomputing_b200 import protocol as proto
+from distributedvolunteercomputing_b200.parallel.scheduler import ReorderBuffer, Scheduler
+from distributedvolunteercomputing_b200.utils.clocks import ClockSampler
+from distributedvolunteercomputing_b200.utils.metrics import Logger, Metrics
+from distributedvolunteercomputing_b200.utils.trace import span
+
+
+def test_scheduler_under_real_threads_exactly_once():
+    """Six worker threads pull, 'compute' and complete concurrently while a chaos thread makes workers leave and
+    re-join and a submitter keeps adding batches: every frame is delivered exactly once, nothing is left in flight."""
+    s = Scheduler(worker_timeout_s=30.0)
+    workers = [f"w{i}" for i in range(6)]
+    for w in workers:
+        s.join(w, capacity=2)
+    s.join("client"); s.become_requester("client")
+    n_batches, bs = 300, 8
+    delivered = []                    # frame ids, appended under lock by whoever completes
+    dl = threading.Lock()
+    stop = threading.Event()
+    errors = []
+
+    def dispatcher_and_workers():
+        # one dispatcher hands work to per-worker inboxes, like coordinator.send_request
+        inbox = {w: [] for w in workers}
+        il = threading.Lock()
+
+        def dispatch():
+            while not stop.is_set():
+                d = s.wait_dispatch(timeout=0.01)
+                if d is None:
+                    continue
+                b, w, _ = d
+                with il:
+                    inbox[w.addr].append(b)
+
+        def work(name, seed):
+            rng = random.Random(seed)
+            while not stop.is_set():
+                with il:
+                    b = inbox[name].pop(0) if inbox[name] else None
+                if b is None:
+                    time.sleep(0.0005)
+                    continue
+                time.sleep(rng.random() * 0.002)
+                try:
+                    done = s.complete(b.batch_id, name)     # None when the batch was re-dispatched meanwhile
+                except Exception as e:                       # pragma: no cover
+                    errors.append(e)
+                    return
+                if done is not None:
+                    with dl:
+                        delivered.extend(done.frame_ids)
+
+        ts = [threading.Thread(target=dispatch, daemon=True)]
+        ts += [threading.Thread(target=work, args=(w, i), daemon=True) for i, w in enumerate(workers)]
+        return ts
+
+    def chaos():
+        rng = random.Random(99)
+        while not stop.is_set():
+            w = rng.choice(workers[2:])
+            s.leave(w)
+            time.sleep(0.003)
+            s.join(w, capacity=2)
+            time.sleep(0.003)
+
+    def submitter():
+        for b in range(n_batches):
+            s.submit("client", range(b * bs + 1, (b + 1) * bs + 1))
+            if b % 50 == 0:
+                time.sleep(0.002)
+
+    threads = dispatcher_and_workers() + [threading.Thread(target=chaos, daemon=True), threading.Thread(target=submitter, daemon=True)]
+    for t in threads:
+        t.start()
+    deadline = time.time() + 60
+    while time.time() < deadline:
+        with dl:
+            if len(delivered) >= n_batches * bs:
+                break
+        time.sleep(0.01)
+    stop.set()
+    for t in threads:
+        t.join(timeout=2)
+    assert not errors
+    assert sorted(delivered) == list(range(1, n_batches * bs + 1))      # exactly once, none lost
+    assert s.outstanding() == 0 and s.pending() == 0
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.permutations(list(range(1, 41))), st.lists(st.integers(1, 40), max_size=15))
+def test_reorder_buffer_any_arrival_order_with_duplicates(order, dups):
+    """In-order writer (worker.py:214-239): any arrival order plus late duplicates yields 1..n exactly once, in order."""
+    rb = ReorderBuffer(1)
+    out = []
+    arrivals = list(order)
+    rng = random.Random(len(dups))
+    for d in dups:
+        arrivals.insert(rng.randrange(len(arrivals) + 1), d)
+    for n in arrivals:
+        out.extend(k for k, _ in rb.push(n, None))
+    assert out == list(range(1, 41)) and len(rb) == 0 and rb.next == 41
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.sampled_from(["request", "processed"]), st.lists(st.integers(1, 10**6), min_size=1, max_size=100, unique=True),
+       st.integers(1, 2160), st.integers(1, 3840), st.integers(1, 255), st.integers(1024, 65535))
+def test_header_roundtrip(cmd, frames, h, w, ip_tail, port):
+    """Wire header `id||cmd||n1-...-nk||H||W` (worker.py:153-155) survives encode/parse for any contents."""
+    hdr = proto.Header(f"10.0.0.{ip_tail}:{port}", cmd, frames, h, w)
+    back = proto.parse_header(hdr.encode())
+    assert (back.requester, back.cmd, list(back.frames), back.height, back.width) == (hdr.requester, cmd, frames, h, w)
+
+
+@settings(max_examples=25, deadline=None)
+@given(st.integers(1, 7), st.integers(1, 9), st.integers(1, 11))
+def test_chunk_pack_unpack_roundtrip(k, h, w):
+    """Side-by-side chunk canvas (worker.py:141-156, 172-177) is lossless for any frame count and size."""
+    rng = np.random.default_rng(k * 100 + h * 10 + w)
+    frames = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for _ in range(k)]
+    canvas = proto.pack_chunk(frames)
+    assert canvas.shape == (h, k * w, 3)
+    back = proto.unpack_chunk(canvas, k, h, w)
+    assert all(np.array_equal(a, b) for a, b in zip(frames, back))
+
+
+def test_metrics_counters_percentiles_and_jsonl(tmp_path):
+    path = tmp_path / "m.jsonl"
+    m = Metrics(str(path))
+
+    def bump():
+        for i in range(1000):
+            m.inc("frames", 2)
+            m.observe("lat_ms", i % 100)
+
+    ts = [threading.Thread(target=bump) for _ in range(4)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert m.counters["frames"] == 8000
+    assert m.percentile("lat_ms", 50) in (49.0, 50.0) and m.percentile("lat_ms", 99) in (98.0, 99.0)
+    assert m.percentile("missing", 50) is None
+    with span("batch", m, frames=64):
+        time.sleep(0.001)
+    s = m.summary()
+    assert s["batch_ms"]["n"] == 1 and s["batch_ms"]["p50"] >= 1.0 and s["counters"]["frames"] == 8000
+    recs = [json.loads(l) for l in path.read_text().splitlines()]
+    assert recs and recs[-1]["event"] == "batch" and recs[-1]["frames"] == 64 and recs[-1]["ms"] >= 1.0
+
+
+def test_logger_is_gated_by_verbose(capsys):
+    Logger(False, "[x] ").log("hidden")
+    Logger(True, "[x] ").log("shown")
+    out = capsys.readouterr().out
+    assert "hidden" not in out and "[x] shown" in out
+
+
+def test_clock_sampler_degrades_without_a_gpu():
+    """No nvidia-smi / NVML on the CPU box: start/stop still work and report zero samples (bench.py relies on it)."""
+    for backend in ("smi", "nvml"):
+        r = ClockSampler(0, period_ms=50, backend=backend).start().stop()
+        assert set(r) >= {"sm_mhz", "sm_max_mhz", "reasons", "samples"} and r["samples"] >= 0
