@@ -5,6 +5,8 @@
 // pixels, slides the 3x3 window along the strip in registers and leans on L1 for the
 // row overlap.  Accumulation is fp32.  Reference op: cv2.dnn Convolution with
 // group == channels, prototxt:42-75, 107-141, ... 826-859 (engine: CAFFE, prototxt:60).
+#include <atomic>
+
 #include "common.cuh"
 
 namespace dvc {
@@ -272,13 +274,13 @@ int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stri
 }
 
 int dw_launch(const DwLaunch* L, cudaStream_t st) {
-  static bool attr_set[64] = {};
+  static std::atomic<bool> attr_set[64];   // zero-initialised; engine threads of different GPUs may race here
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
-  if (!attr_set[dev & 63]) {
+  if (!attr_set[dev & 63].load(std::memory_order_acquire)) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
     DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
-    attr_set[dev & 63] = true;
+    attr_set[dev & 63].store(true, std::memory_order_release);
   }
   if (L->stride == 1) DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<1>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));
   else DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<2>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));

@@ -29,20 +29,21 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-static EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    // The driver symbol is resolved through the runtime so libcuda is not a link-time dependency
-    // (the build box has no driver).
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess) {
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-    }
+static EncodeTiledFn resolve_encode_fn() {
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  // The driver symbol is resolved through the runtime so libcuda is not a link-time dependency
+  // (the build box has no driver).
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+      qres == cudaDriverEntryPointSuccess) {
+    return reinterpret_cast<EncodeTiledFn>(p);
   }
+  return nullptr;
+}
+
+static EncodeTiledFn get_encode_fn() {
+  // function-local static: initialised exactly once even when several engine threads build plans at the same time
+  static const EncodeTiledFn fn = resolve_encode_fn();
   return fn;
 }
 

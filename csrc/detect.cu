@@ -6,6 +6,8 @@
 // worker.py:253-269 and the cv2.rectangle / cv2.putText overlay of worker.py:268-276.
 #include <mutex>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace dvc {
@@ -399,12 +401,12 @@ int det_prepare(DetLaunch* L, const float* loc, const float* conf, const float* 
 }
 
 int det_launch(const DetLaunch* L, cudaStream_t st) {
-  static bool attr_set[64] = {};
+  static std::atomic<bool> attr_set[64];   // zero-initialised; engine threads of different GPUs may race here
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
-  if (!attr_set[dev & 63]) {
+  if (!attr_set[dev & 63].load(std::memory_order_acquire)) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(class_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    attr_set[dev & 63] = true;
+    attr_set[dev & 63].store(true, std::memory_order_release);
   }
   const DetArgs& a = L->args;
   const long long n = (long long)a.B * a.p.num_priors;

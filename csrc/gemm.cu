@@ -20,6 +20,8 @@
 // Reference op: cv2.dnn Convolution layers, prototxt:76-106 ... 1083-1113, 1147-1775.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace dvc {
@@ -318,15 +320,15 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 // ------------------------------------------------------------------------------------ host
 
 static int num_sms() {
-  static int cached[64] = {};
+  static std::atomic<int> cached[64];
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-  if (!cached[dev & 63]) {
+  if (!cached[dev & 63].load(std::memory_order_relaxed)) {
     int n = 0;
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-    cached[dev & 63] = n;
+    cached[dev & 63].store(n, std::memory_order_relaxed);
   }
-  return cached[dev & 63];
+  return cached[dev & 63].load(std::memory_order_relaxed);
 }
 
 static int pick_block_n(int M, int N) {
@@ -438,13 +440,13 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
 }
 
 int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
-  static bool attr_set[64] = {};
+  static std::atomic<bool> attr_set[64];   // zero-initialised; engine threads of different GPUs may race here
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
-  if (!attr_set[dev & 63]) {
+  if (!attr_set[dev & 63].load(std::memory_order_acquire)) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(gemm_f16_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_MAX_SMEM));
     DVC_CHECK_CUDA(cudaFuncSetAttribute(gemm_f16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_MAX_SMEM));
-    attr_set[dev & 63] = true;
+    attr_set[dev & 63].store(true, std::memory_order_release);
   }
   if (L->args.cluster > 1) {
     cudaError_t le = L->args.two_cta ? launch_pdl(gemm_f16_kernel<1>, dim3(L->grid), dim3(GEMM_THREADS), (size_t)L->smem, st, L->args.cluster,

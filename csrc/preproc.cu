@@ -10,6 +10,8 @@
 // 3x3/s2 convolution + bias + ReLU from shared memory, writing NHWC fp16.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace dvc {
@@ -544,13 +546,13 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
 }
 
 int preproc_launch(const PreprocLaunch* L, cudaStream_t st) {
-  static bool attr_set[64] = {};
+  static std::atomic<bool> attr_set[64];   // zero-initialised; engine threads of different GPUs may race here
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
-  if (!attr_set[dev & 63]) {
+  if (!attr_set[dev & 63].load(std::memory_order_acquire)) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-    attr_set[dev & 63] = true;
+    attr_set[dev & 63].store(true, std::memory_order_release);
   }
   if (L->use_tc) DVC_CHECK_CUDA(launch_pdl(preproc_conv0_tc_kernel, L->grid, dim3(PC_THREADS), (size_t)L->smem_tc, st, 1, L->args));
   else preproc_conv0_kernel<<<L->grid, PC_THREADS, L->smem, st>>>(L->args);
@@ -592,13 +594,13 @@ extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int
   a.tab_off = (int)((((long long)rows_for(band) * row_bytes + 64) + 15) & ~15LL);
   const long long smem = a.tab_off + (long long)dw * 12 + 16;
   DVC_REQUIRE(smem <= 200 * 1024, "resize: one band of source rows (%lld bytes) does not fit shared memory", smem);
-  static bool attr_set[64] = {};
+  static std::atomic<bool> attr_set[64];   // zero-initialised; engine threads of different GPUs may race here
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
-  if (!attr_set[dev & 63]) {
+  if (!attr_set[dev & 63].load(std::memory_order_acquire)) {
     DVC_CHECK_CUDA(cudaFuncSetAttribute(resize_u8_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DVC_CHECK_CUDA(cudaFuncSetAttribute(resize_u8_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set[dev & 63] = true;
+    attr_set[dev & 63].store(true, std::memory_order_release);
   }
   const bool vec4 = dw % 4 == 0 && dst_frame_stride % 4 == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0;
   dim3 grid(ceil_div(dh, band), B);
