@@ -1,6 +1,8 @@
 #!/bin/bash
 mkdir -p gpurun_out
-PT="python -m pytest -q --timeout 300 --timeout-method=thread -p no:cacheprovider"
-timeout 500 $PT tests -m gpu -x > gpurun_out/t_all_gpu.log 2>&1; echo "gpu tests rc=$?"; tail -3 gpurun_out/t_all_gpu.log
-timeout 100 python -c "import __graft_entry__ as g; g.build(); g.smoke()" 2>&1 | tail -1
-timeout 200 python bench.py > gpurun_out/bench_n1.log 2>gpurun_out/bench_n1.err; echo "bench rc=$?"; tail -1 gpurun_out/bench_n1.log | cut -c1-300
+timeout 100 python scripts/sweep_dw_split.py 2>&1 | tail -15
+PT="python -m pytest -q --timeout 120 --timeout-method=thread -p no:cacheprovider"
+timeout 200 $PT tests/test_gpu_kernels.py -m gpu -x -k "dwconv" 2>&1 | tail -2
+for sp in 1 0; do DVC_DW_SPLIT=$sp timeout 120 python bench.py 2>/dev/null | python -c "
+import json,sys
+d=json.loads(sys.stdin.readlines()[-1]); print('split=$sp', d['value'], d['e2e']['value'], d['config']['p50_batch_latency_ms'])"; done
