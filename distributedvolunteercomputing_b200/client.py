@@ -51,6 +51,7 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
         self.send_q: "queue.Queue[Tuple[str, np.ndarray]]" = queue.Queue(maxsize=64)
         self.tracker: Optional[JobTracker] = None
         self.path_out_num = 0
+        self.chunks_taken = 0
         self.final_sent_frame = 0
         self.threads: List[threading.Thread] = []
         self.ready = threading.Event()
@@ -162,6 +163,13 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
             elif hdr.cmd == "request":
                 if self.engine is None:
                     continue
+                self.chunks_taken += 1
+                if self.cfg.inject_leave_after and self.chunks_taken > self.cfg.inject_leave_after:
+                    self._vanish()                              # fault injection: no `end`, the chunk is lost
+                    break
+                if self.cfg.inject_stall_after and self.chunks_taken > self.cfg.inject_stall_after:
+                    self.log("fault injection: chunk swallowed")
+                    continue                                    # fault injection: accepted, never answered
                 t0 = time.time()
                 res = self.engine.process(np.stack(frames), requester_id=hdr.requester).numpy()
                 self.metrics.observe("batch_ms", (time.time() - t0) * 1e3)
@@ -171,6 +179,12 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
                 reply = proto.Header(hdr.requester, "processed", hdr.frames, h, w)
                 self._enqueue_send(reply.encode(), proto.pack_chunk(out))
         print("worker terminated.", flush=True)
+
+    def _vanish(self):
+        """Fault injection: stop like a killed process - no `end` to the server, sockets just go away."""
+        self.log("fault injection: leaving without `end`")
+        self.continue_requesting = False
+        self.running = False
 
     def _enqueue_send(self, info: str, chunk: np.ndarray):
         while self.running:

@@ -46,6 +46,9 @@ class Config:
     dispatch_policy: str = "least_loaded"   # or "round_robin" (reference, server.py:89-90)
     worker_timeout_s: float = 10.0      # in-flight batches older than this are re-dispatched
     verbose: bool = False
+    # ---- fault injection (the reference has none)
+    inject_stall_after: int = 0         # worker: after this many chunks, keep accepting chunks but never answer
+    inject_leave_after: int = 0         # worker: after this many chunks, vanish without sending `end` (process death)
     # ---- B200 engine
     device: str = "auto"                # "auto" | "cpu" | "cuda:N"
     batch: int = 64                     # frames per GPU batch (BASELINE.json config 2)

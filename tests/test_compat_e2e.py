@@ -115,6 +115,31 @@ def test_worker_leaving_midstream_does_not_strand_the_job(tmp_path):
         srv.exit_threads()
 
 
+@pytest.mark.parametrize("fault", ["inject_stall_after", "inject_leave_after"])
+def test_fault_injection_flags_job_still_completes(tmp_path, fault):
+    """`--inject-stall-after N` (accepts chunks, never answers) and `--inject-leave-after N` (dies without `end`):
+    the coordinator's in-flight timeout re-dispatches the lost chunks and the output is complete and in order."""
+    port = _udp_port()
+    srv = coordinator("127.0.0.1", _cfg(port, worker_timeout_s=1.5))
+    video = write_synthetic_video(str(tmp_path / "in.mp4"), 48, 96, 128)
+    try:
+        bad = client("127.0.0.1", "127.0.0.1", _cfg(port, **{fault: 1}), engine=StubEngine(delay=0.02), out_dir=str(tmp_path))
+        good = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(delay=0.02), out_dir=str(tmp_path))
+        req = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        for c in (bad, good, req):
+            assert c.ready.wait(5)
+        req.become_requester(video)
+        secs = req.wait_job(60)
+        assert secs is not None, srv.sched.snapshot()
+        assert _count_frames(str(tmp_path / "video0.mp4")) == 48
+        assert srv.sched.stats["redispatched"] >= 1 and bad.chunks_taken >= 2
+        good.exit_threads(); req.exit_threads()
+        if fault == "inject_stall_after":
+            bad.exit_threads()
+    finally:
+        srv.exit_threads()
+
+
 def test_idempotent_join_and_compat_drop_modes(tmp_path):
     port = _udp_port()
     srv = coordinator("127.0.0.1", _cfg(port))
