@@ -55,6 +55,7 @@ class Config:
     sub_batch: int = 0                  # 0 = whole batch per launch; >0 runs conv0..conv6 in sub-batches of this size
     use_cuda_graph: bool = True
     metrics_jsonl: Optional[str] = None
+    metrics_port: int = -1              # >= 0: serve /metrics (Prometheus text) and /summary on this port (0 = any free port)
 
     @staticmethod
     def from_env(**overrides) -> "Config":

@@ -65,10 +65,24 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
             t = threading.Thread(target=target, daemon=True)
             t.start()
             self.threads.append(t)
+        self.metrics_http = None
+        if self.cfg.metrics_port >= 0:
+            self.metrics_http = self.metrics.serve_http(self.cfg.metrics_port, gauges=self._gauges)
+            print("metrics on http://127.0.0.1:%d/metrics" % self.metrics_http.server_address[1], flush=True)
+
+    def _gauges(self) -> Dict[str, float]:
+        snap = self.sched.snapshot()
+        return {"workers_alive": sum(1 for w in snap["workers"].values() if w["alive"]), "membership_epoch": snap["epoch"],
+                "chunks_pending": snap["pending"], "chunks_in_flight": snap["inflight"],
+                "chunks_redispatched": snap["stats"].get("redispatched", 0)}
 
     def exit_threads(self):
         """`quit` (server.py:160-163) - and the threads really stop."""
         self.running = False
+        if getattr(self, "metrics_http", None) is not None:
+            self.metrics_http.shutdown()
+            self.metrics_http.server_close()
+            self.metrics_http = None
         for ev in list(self.ingest_stop.values()) + list(self.reply_stop.values()):
             ev.set()
         with self.sched.cv:

@@ -160,6 +160,27 @@ def test_metrics_counters_percentiles_and_jsonl(tmp_path):
     assert recs and recs[-1]["event"] == "batch" and recs[-1]["frames"] == 64 and recs[-1]["ms"] >= 1.0
 
 
+def test_metrics_http_endpoint_on_the_coordinator():
+    """`--metrics-port` serves Prometheus text and a JSON summary next to the reference's stdout lines."""
+    import socket
+    import urllib.request
+    from distributedvolunteercomputing_b200.config import Config
+    from distributedvolunteercomputing_b200.coordinator import coordinator
+    s = socket.socket(socket.AF_INET, socket.SOCK_DGRAM); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    srv = coordinator("127.0.0.1", Config(control_port=port, metrics_port=0, data_port_lo=0, data_port_hi=-1))
+    try:
+        srv.metrics.inc("frames_in", 128)
+        srv.metrics.observe("batch_ms", 1.5)
+        http_port = srv.metrics_http.server_address[1]
+        text = urllib.request.urlopen(f"http://127.0.0.1:{http_port}/metrics", timeout=5).read().decode()
+        assert "dvc_frames_in_total 128" in text and 'dvc_batch_ms{quantile="0.5"} 1.5' in text
+        assert "dvc_workers_alive 0" in text and "dvc_chunks_pending 0" in text
+        summ = json.loads(urllib.request.urlopen(f"http://127.0.0.1:{http_port}/summary", timeout=5).read())
+        assert summ["counters"]["frames_in"] == 128
+    finally:
+        srv.exit_threads()
+
+
 def test_logger_is_gated_by_verbose(capsys):
     Logger(False, "[x] ").log("hidden")
     Logger(True, "[x] ").log("shown")
