@@ -36,6 +36,7 @@ void det_free(DetLaunch*);
 void det_set_flag_value(DetLaunch*, uint32_t);
 void det_set_timestamps(DetLaunch*, unsigned long long* t_done);
 void preproc_set_timestamps(PreprocLaunch*, unsigned long long* t_ingest);
+void preproc_set_epoch_gate(PreprocLaunch*, const uint32_t* now, const uint32_t* expect);
 void det_set_epoch_gate(DetLaunch*, const uint32_t* now, const uint32_t* expect, uint32_t* stale_count);
 void det_set_sinks(DetLaunch*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index);
 
@@ -172,8 +173,10 @@ extern "C" int dvc_plan_set_timestamps(dvc_plan* p, unsigned long long* t_ingest
 extern "C" int dvc_plan_set_epoch_gate(dvc_plan* p, const uint32_t* epoch_now, const uint32_t* epoch_expect, uint32_t* stale_count) {
   DVC_REQUIRE(p, "plan is null");
   DVC_REQUIRE((epoch_now == nullptr) == (epoch_expect == nullptr), "epoch gate: give both epoch words or neither");
-  for (auto& op : p->ops)
+  for (auto& op : p->ops) {
     if (op.kind == OP_DET) det_set_epoch_gate(op.det, epoch_now, epoch_expect, stale_count);
+    if (op.kind == OP_PREPROC) preproc_set_epoch_gate(op.pre, epoch_now, epoch_expect);     // K1b: do not pull a stale batch
+  }
   return DVC_OK;
 }
 

@@ -26,7 +26,18 @@ struct ResizeArgs {
   int band;       // output rows per CTA
   int aligned;    // frames 16-byte aligned (base and stride): vectorised staging
   int tab_off;    // byte offset of the x-tap table inside the dynamic shared memory
+  const uint32_t* epoch_now;      // K14 gate (optional): skip the pull when the membership epoch has moved on
+  const uint32_t* epoch_expect;
 };
+
+// CTA-uniform "is this dispatch stale?" (thread 0 reads the two words, everyone gets the same answer).
+__device__ __forceinline__ bool epoch_stale(const uint32_t* now, const uint32_t* expect) {
+  __shared__ int s_epoch_stale;
+  if (now == nullptr || expect == nullptr) return false;
+  if (threadIdx.x == 0) s_epoch_stale = ld_acquire_sys_u32(now) != ld_acquire_sys_u32(expect);
+  __syncthreads();
+  return s_epoch_stale != 0;
+}
 
 // One CTA per (band of output rows, frame).  The source rows the band needs are staged in shared memory
 // with coalesced 16-byte loads (every source byte is fetched once per band), then each thread produces RP
@@ -37,6 +48,7 @@ __global__ void __launch_bounds__(256) resize_u8_kernel(const ResizeArgs a) {
   extern __shared__ __align__(16) uint8_t rs_band[];
   pdl_launch_dependents();
   pdl_wait();                   // the destination may still be read by the previous batch's overlay kernel
+  if (epoch_stale(a.epoch_now, a.epoch_expect)) return;        // stale dispatch: do not pull the frames over NVLink
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
   const int dy0 = blockIdx.x * a.band;
@@ -173,6 +185,8 @@ struct PreprocArgs {
   int band_bytes;     // smem bytes reserved for the staged source rows
   int slot0;          // first source slot of this launch (sub-batch offset inside the ring)
   unsigned long long* t_ingest;   // optional [B]: %globaltimer when the first CTA of a frame starts pulling it
+  const uint32_t* epoch_now;      // K14 gate (optional), as in ResizeArgs
+  const uint32_t* epoch_expect;
 };
 
 __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const PreprocArgs a) {
@@ -189,6 +203,7 @@ __global__ void __launch_bounds__(PC_THREADS, 2) preproc_conv0_kernel(const Prep
   const int oy0 = band * PC_BAND;
   const int iy_first = max(2 * oy0 - 1, 0);
   const int iy_last = min(2 * oy0 + 2 * PC_BAND - 1, PC_NET - 1);
+  if (epoch_stale(a.epoch_now, a.epoch_expect)) return;
   const int slot = a.frame_index ? a.frame_index[a.slot0 + b] : a.slot0 + b;
   const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
   if (a.t_ingest && band == 0 && tid == 0) a.t_ingest[a.slot0 + b] = globaltimer_ns();
@@ -359,6 +374,12 @@ __global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const P
     tmem_relinquish();
   }
   pdl_wait();                   // the source frames are the resize kernel's output (or a peer's, ordered by the stream)
+  tc_fence_before();
+  if (epoch_stale(a.epoch_now, a.epoch_expect)) {               // stale dispatch: no pull; release TMEM and leave
+    tc_fence_after();
+    if (warp == 0) tmem_dealloc(*tmem_slot, 64);
+    return;
+  }
   const int slot = a.frame_index ? a.frame_index[a.slot0 + b] : a.slot0 + b;
   const uint8_t* frame = a.src + (size_t)slot * a.src_stride;
   if (a.t_ingest && band == 0 && tid == 0) a.t_ingest[a.slot0 + b] = globaltimer_ns();
@@ -532,6 +553,7 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
   a.out = reinterpret_cast<__half*>(out);
   a.slot0 = slot0;
   a.t_ingest = nullptr;
+  a.epoch_now = nullptr; a.epoch_expect = nullptr;
   // worst-case staged rows for one band: 17 net rows span at most ceil(17*sh/300)+2 source rows
   if (band_rows_max <= 0) band_rows_max = (PC_PROWS * sh + PC_NET - 1) / PC_NET + 3;
   if (band_rows_max > sh) band_rows_max = sh;
@@ -540,7 +562,7 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
   L->smem_tc = TC_OFF_A + tc_ab_bytes(a.band_bytes) + TC_PATCH_BYTES + 3 * PC_NET * 4 + 32 * 4 + 64 + 1024;
   const char* env = getenv("DVC_CONV0_CUDA_CORES");            // A/B switch: the fp32 CUDA-core variant
   L->use_tc = !(env && env[0] == '1') && L->smem_tc <= 110 * 1024;   // taller source frames fall back to the CUDA-core variant
-  DVC_REQUIRE(L->smem <= 227 * 1024, "preproc: source band of %d rows x %d px does not fit shared memory", band_rows_max, sw);
+  DVC_REQUIRE(L->smem <= 226 * 1024, "preproc: source band of %d rows x %d px does not fit shared memory", band_rows_max, sw);
   L->grid = dim3((PC_OUT + PC_BAND - 1) / PC_BAND, B);
   return DVC_OK;
 }
@@ -550,7 +572,7 @@ int preproc_launch(const PreprocLaunch* L, cudaStream_t st) {
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63].load(std::memory_order_acquire)) {
-    DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
     DVC_CHECK_CUDA(cudaFuncSetAttribute(preproc_conv0_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     attr_set[dev & 63].store(true, std::memory_order_release);
   }
@@ -564,6 +586,9 @@ int preproc_launch(const PreprocLaunch* L, cudaStream_t st) {
 PreprocLaunch* preproc_alloc() { return new PreprocLaunch(); }
 void preproc_free(PreprocLaunch* L) { delete L; }
 void preproc_set_timestamps(PreprocLaunch* L, unsigned long long* t_ingest) { L->args.t_ingest = t_ingest; }
+void preproc_set_epoch_gate(PreprocLaunch* L, const uint32_t* now, const uint32_t* expect) {
+  L->args.epoch_now = now; L->args.epoch_expect = expect;
+}
 void preproc_set_source(PreprocLaunch* L, const uint8_t* src, long long stride, const int* frame_index) {
   L->args.src = src;
   L->args.src_stride = stride;
@@ -572,17 +597,19 @@ void preproc_set_source(PreprocLaunch* L, const uint8_t* src, long long stride, 
 
 }  // namespace dvc
 
-extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int B, int sh, int sw, uint8_t* dst,
-                             long long dst_frame_stride, int dh, int dw, int mode, const int* xs, const int* xc,
-                             const float* xa, int x_taps, const int* ys, const int* yc, const float* ya, int y_taps,
-                             const int* xq, const int* yq, int ix, int iy, void* stream) {
+static int resize_u8_impl(const uint8_t* src, long long src_frame_stride, int B, int sh, int sw, uint8_t* dst,
+                          long long dst_frame_stride, int dh, int dw, int mode, const int* xs, const int* xc,
+                          const float* xa, int x_taps, const int* ys, const int* yc, const float* ya, int y_taps,
+                          const int* xq, const int* yq, int ix, int iy, const uint32_t* epoch_now,
+                          const uint32_t* epoch_expect, void* stream) {
   using namespace dvc;
+  DVC_REQUIRE((epoch_now == nullptr) == (epoch_expect == nullptr), "resize: give both epoch words or neither");
   DVC_REQUIRE(B > 0 && sh > 0 && sw > 0 && dh > 0 && dw > 0 && mode >= 0 && mode <= 2, "resize: bad arguments");
   if (mode == 0) DVC_REQUIRE(xs && xc && xa && ys && yc && ya, "resize: area tables missing");
   if (mode == 1) DVC_REQUIRE(ix > 0 && iy > 0 && dw * ix <= sw && dh * iy <= sh, "resize: bad integer ratio");
   if (mode == 2) DVC_REQUIRE(xs && ys && xq && yq, "resize: bilinear tables missing");
   ResizeArgs a{src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps,
-               ys, yc, ya, y_taps, xq, yq, ix, iy, 1, 0, 0};
+               ys, yc, ya, y_taps, xq, yq, ix, iy, 1, 0, 0, epoch_now, epoch_expect};
   a.aligned = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && src_frame_stride % 16 == 0) ? 1 : 0;
   // band height: as many output rows as keep the staged source rows within ~64 KB of shared memory
   const long long row_bytes = (long long)sw * 3;
@@ -609,6 +636,22 @@ extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
+}
+
+extern "C" int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int B, int sh, int sw, uint8_t* dst,
+                             long long dst_frame_stride, int dh, int dw, int mode, const int* xs, const int* xc,
+                             const float* xa, int x_taps, const int* ys, const int* yc, const float* ya, int y_taps,
+                             const int* xq, const int* yq, int ix, int iy, void* stream) {
+  return resize_u8_impl(src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps, ys, yc, ya,
+                        y_taps, xq, yq, ix, iy, nullptr, nullptr, stream);
+}
+extern "C" int dvc_resize_u8_gated(const uint8_t* src, long long src_frame_stride, int B, int sh, int sw, uint8_t* dst,
+                                   long long dst_frame_stride, int dh, int dw, int mode, const int* xs, const int* xc,
+                                   const float* xa, int x_taps, const int* ys, const int* yc, const float* ya, int y_taps,
+                                   const int* xq, const int* yq, int ix, int iy, const uint32_t* epoch_now,
+                                   const uint32_t* epoch_expect, void* stream) {
+  return resize_u8_impl(src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps, ys, yc, ya,
+                        y_taps, xq, yq, ix, iy, epoch_now, epoch_expect, stream);
 }
 
 extern "C" int dvc_preproc_conv0(const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B, int sh,

@@ -77,7 +77,9 @@ def make_linear_tables(sh: int, sw: int, dh: int, dw: int, device, area_mode: bo
 
 
 def resize_u8(src: torch.Tensor, t: ResizeTables, dst: Optional[torch.Tensor] = None, dst_frame_stride: int = 0,
-              stream=None) -> torch.Tensor:
+              stream=None, epoch_gate=None) -> torch.Tensor:
+    """cv2 INTER_AREA on the device.  ``epoch_gate=(epoch_now, epoch_expect)`` (two int32 device words) makes the
+    kernel skip the read of ``src`` - the NVLink pull in the multi-GPU path - when the membership epoch moved on."""
     assert src.dtype == torch.uint8 and src.is_cuda and src.dim() == 4 and src.shape[3] == 3
     B = src.shape[0]
     assert (src.shape[1], src.shape[2]) == (t.sh, t.sw)
@@ -86,9 +88,13 @@ def resize_u8(src: torch.Tensor, t: ResizeTables, dst: Optional[torch.Tensor] = 
         dst = torch.empty((B, t.dh, t.dw, 3), dtype=torch.uint8, device=src.device)
         dst_frame_stride = t.dh * t.dw * 3
     lib = L.load()
-    L.check(lib.dvc_resize_u8(L.ptr(src), src.stride(0), B, t.sh, t.sw, L.ptr(dst), dst_frame_stride, t.dh, t.dw, t.mode,
-                              L.ptr(t.xs), L.ptr(t.xc), L.ptr(t.xa), t.x_taps, L.ptr(t.ys), L.ptr(t.yc), L.ptr(t.ya),
-                              t.y_taps, L.ptr(t.xq), L.ptr(t.yq), t.ix, t.iy, L.stream_ptr(stream)), "resize_u8")
+    args = (L.ptr(src), src.stride(0), B, t.sh, t.sw, L.ptr(dst), dst_frame_stride, t.dh, t.dw, t.mode,
+            L.ptr(t.xs), L.ptr(t.xc), L.ptr(t.xa), t.x_taps, L.ptr(t.ys), L.ptr(t.yc), L.ptr(t.ya),
+            t.y_taps, L.ptr(t.xq), L.ptr(t.yq), t.ix, t.iy)
+    if epoch_gate is None:
+        L.check(lib.dvc_resize_u8(*args, L.stream_ptr(stream)), "resize_u8")
+    else:
+        L.check(lib.dvc_resize_u8_gated(*args, L.ptr(epoch_gate[0]), L.ptr(epoch_gate[1]), L.stream_ptr(stream)), "resize_u8_gated")
     return dst
 
 

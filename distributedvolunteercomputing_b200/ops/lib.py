@@ -41,6 +41,7 @@ _SIGS = {
     "dvc_launch_count": ([], _LL),
     "dvc_set_device": ([_I], _I),
     "dvc_resize_u8": ([_P, _LL, _I, _I, _I, _P, _LL, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _P], _I),
+    "dvc_resize_u8_gated": ([_P, _LL, _I, _I, _I, _P, _LL, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _P, _P, _P], _I),
     "dvc_preproc_conv0": ([_P, _LL, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _F, _P, _P], _I),
     "dvc_dwconv3x3": ([_P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P], _I),
     "dvc_gemm_f16": ([_P, _P, _P, _I, _I, _I, _I, _I, _P, _I, _I, _P, _I, _P], _I),

@@ -219,7 +219,8 @@ class BoxCluster:
             if self.is_client and raw_all is not None and raw_all.data_ptr() != ln.raw_all.data_ptr():
                 ln.raw_all.copy_(raw_all, non_blocking=True)  # frames enter the client's raw ring
             self.dist.all_reduce(ln.tok, group=ln.group)      # raw ring filled -> everyone may pull
-            K.resize_u8(ln.raw_mine, st.t_area, st.frames400_flat, st.stride400)     # K1a: peer loads = the scatter
+            K.resize_u8(ln.raw_mine, st.t_area, st.frames400_flat, st.stride400,      # K1a: peer loads = the scatter,
+                        epoch_gate=(self.epoch_word, self.epoch_expect))               # skipped for a stale dispatch
             self.engine.run(st, annotate=False, resize=False)                        # rows pushed to the client (gather)
             if annotate:
                 self._annotate(ln, st.frames400_flat, self.B, ln.my_boxes, ln.my_box_count)

@@ -46,6 +46,14 @@ int dvc_resize_u8(const uint8_t* src, long long src_frame_stride, int B, int sh,
                   const int* xs, const int* xc, const float* xa, int x_taps,
                   const int* ys, const int* yc, const float* ya, int y_taps,
                   const int* xq, const int* yq, int ix, int iy, void* stream);
+/* Same, gated on the K14 membership epoch: when *epoch_now != *epoch_expect (two device words, read by the kernel)
+ * nothing is read from `src` (no NVLink pull of a stale batch) and `dst` is left untouched. */
+int dvc_resize_u8_gated(const uint8_t* src, long long src_frame_stride, int B, int sh, int sw,
+                        uint8_t* dst, long long dst_frame_stride, int dh, int dw, int mode,
+                        const int* xs, const int* xc, const float* xa, int x_taps,
+                        const int* ys, const int* yc, const float* ya, int y_taps,
+                        const int* xq, const int* yq, int ix, int iy,
+                        const uint32_t* epoch_now, const uint32_t* epoch_expect, void* stream);
 
 /* ---- K1b: fused frame fetch + cv2.resize(300x300, INTER_LINEAR) + (x-mean_c)*scale +
  * conv0 3x3/s2 + bias + ReLU (worker.py:245-246, prototxt:9-41).  `src400` may be a peer

@@ -193,6 +193,17 @@ def test_epoch_gate_rejects_stale_dispatch(graph):
         assert int(stale.item()) == 5                   # one per frame
         assert (st.det == -5.0).all() and (st.det_count == -9).all() and (st.box_count == -9).all()
         now.fill_(3)
+    # K1a / K1b side of the gate: a stale dispatch does not read its frames
+    from distributedvolunteercomputing_b200.ops import kernels as K
+    dst = torch.full((5, st.h4, st.w4, 3), 7, dtype=torch.uint8, device="cuda:0")
+    now.fill_(9); expect.fill_(3)
+    K.resize_u8(frames, st.t_area, dst, st.h4 * st.w4 * 3, epoch_gate=(now, expect))
+    torch.cuda.synchronize()
+    assert (dst == 7).all()
+    now.fill_(3)
+    K.resize_u8(frames, st.t_area, dst, st.h4 * st.w4 * 3, epoch_gate=(now, expect))
+    torch.cuda.synchronize()
+    assert torch.equal(dst, K.resize_u8(frames, st.t_area))
     eng.set_epoch_gate(st, None, None, None)
     eng.run(st, use_graph=False, src=frames)
     torch.cuda.synchronize()
