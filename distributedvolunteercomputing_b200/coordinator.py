@@ -44,6 +44,7 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
         self.senders: Dict[str, proto.ImageSender] = {}
         self.sender_locks: Dict[str, threading.Lock] = {}
         self.ingest_stop: Dict[str, threading.Event] = {}
+        self.outbox: Dict[str, "queue.Queue"] = {}      # per-worker dispatch queue: one slow link does not stall the rest
         self.results: Dict[str, "queue.Queue"] = {}
         self.reply_stop: Dict[str, threading.Event] = {}
         # frame bookkeeping: requester -> frame number -> batch id ; batch id -> frames still missing
@@ -118,6 +119,12 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
     def handle_control(self, cmd: Optional[str], address: str) -> Optional[str]:
         if cmd == "join":
             with self.lock:
+                known = address in self.port_of
+            if known and not any(w.addr == address for w in self.sched.members.alive()):
+                # a worker we had declared dead (send timeout / watchdog) is back, e.g. restarted on the same
+                # ip:port: drop its old port, sockets and threads and start from a clean slate
+                self._remove_client(address)
+            with self.lock:
                 _, new = self.sched.join(address, capacity=2)
                 if not new and address in self.port_of:
                     return "ok||" + str(self.port_of[address])          # idempotent retry
@@ -130,6 +137,10 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
                 ev = threading.Event()
                 self.ingest_stop[address] = ev
                 t = threading.Thread(target=self.server, args=["", port, address, ev], daemon=True)
+                t.start()
+                self.threads.append(t)
+                self.outbox[address] = queue.Queue()
+                t = threading.Thread(target=self.worker_sender, args=[address, ev], daemon=True)
                 t.start()
                 self.threads.append(t)
             self.metrics.inc("joins")
@@ -180,6 +191,7 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
             if s:
                 s.close()
             self.sender_locks.pop(address, None)
+            self.outbox.pop(address, None)
             self.results.pop(address, None)
         if address in self.frame_owner:
             self.sched.drop_requester(address)
@@ -244,14 +256,34 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
 
     # ------------------------------------------------------------------ data plane: dispatch / return
     def send_request(self):
+        """Dispatcher (server.py:77-91): takes scheduling decisions and hands each chunk to its worker's own sender
+        thread, so a slow or dead link never blocks dispatch to the others (the reference's single loop blocks in
+        `send_image`)."""
         while self.running:
             d = self.sched.wait_dispatch(timeout=0.2)
             if d is None:
                 continue
             batch, worker, epoch = d
+            box = self.outbox.get(worker.addr)
+            if box is None:
+                self.sched.fail(batch.batch_id, "no_sender")
+                continue
+            box.put(batch)
+        print("send_request terminated.", flush=True)
+
+    def worker_sender(self, address: str, stop: threading.Event):
+        """One per worker: blocking REQ/REP sends of the chunks the dispatcher assigned to `address`."""
+        while self.running and not stop.is_set():
+            box = self.outbox.get(address)
+            if box is None:
+                break
+            try:
+                batch = box.get(timeout=0.25)
+            except queue.Empty:
+                continue
             info, frame = batch.payload
-            sender = self.senders.get(worker.addr)
-            lock = self.sender_locks.get(worker.addr)
+            sender = self.senders.get(address)
+            lock = self.sender_locks.get(address)
             if sender is None or lock is None:
                 self.sched.fail(batch.batch_id, "no_sender")
                 continue
@@ -260,10 +292,10 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
                     sender.send_image(info, frame)
                 self.metrics.inc("chunks_dispatched")
             except TimeoutError:
-                self.log(f"worker {worker.addr} did not acknowledge a chunk: marking it gone")
+                self.log(f"worker {address} did not acknowledge a chunk: marking it gone")
                 self.metrics.inc("dispatch_timeouts")
-                self.sched.leave(worker.addr)          # re-queues this batch and anything else it held
-        print("send_request terminated.", flush=True)
+                self.sched.leave(address)              # re-queues this batch and anything else it held
+                break
 
     def send_reply(self, address: str, stop: threading.Event):
         while self.running and not stop.is_set():

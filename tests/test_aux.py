@@ -181,6 +181,28 @@ def test_metrics_http_endpoint_on_the_coordinator():
         srv.exit_threads()
 
 
+def test_worker_declared_dead_can_rejoin_cleanly():
+    """A worker the coordinator gave up on (send timeout) that joins again gets a fresh port, sender and threads; a
+    repeated join of a live worker stays idempotent (worker.py:50-58 retries the datagram)."""
+    import socket
+    from distributedvolunteercomputing_b200.config import Config
+    from distributedvolunteercomputing_b200.coordinator import coordinator
+    s = socket.socket(socket.AF_INET, socket.SOCK_DGRAM); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    srv = coordinator("127.0.0.1", Config(control_port=port, data_port_lo=0, data_port_hi=-1))
+    try:
+        addr = "127.0.0.1:%d" % proto.free_tcp_port()
+        r1 = srv.handle_control("join", addr)
+        assert r1.startswith("ok||") and srv.handle_control("join", addr) == r1          # idempotent while alive
+        old_stop = srv.ingest_stop[addr]
+        srv.sched.leave(addr)                                                            # what a send timeout does
+        r2 = srv.handle_control("join", addr)
+        assert r2.startswith("ok||") and old_stop.is_set() and not srv.ingest_stop[addr].is_set()
+        assert [w.addr for w in srv.sched.members.alive()] == [addr] and addr in srv.outbox and addr in srv.senders
+        assert srv.handle_control("end", addr) == "ok" and addr not in srv.port_of and addr not in srv.outbox
+    finally:
+        srv.exit_threads()
+
+
 def test_logger_is_gated_by_verbose(capsys):
     Logger(False, "[x] ").log("hidden")
     Logger(True, "[x] ").log("shown")
