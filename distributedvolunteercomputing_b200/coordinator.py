@@ -219,6 +219,9 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
     def _on_chunk(self, info: str, frame: np.ndarray, sender_addr: str):
         hdr = proto.parse_header(info)
         self.sched.members.touch(sender_addr)
+        if self.sched.revive(sender_addr):              # presumed dead (silence / send timeout) but evidently not
+            self.metrics.inc("workers_revived")
+            self.log(f"{sender_addr} is back: accepting work again")
         if hdr.cmd == "request":
             while self.running and self.sched.pending() > self.cfg.max_buffer_chunks:
                 time.sleep(0.02)                                        # backpressure (server.py:54)
@@ -292,10 +295,14 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
                     sender.send_image(info, frame)
                 self.metrics.inc("chunks_dispatched")
             except TimeoutError:
-                self.log(f"worker {address} did not acknowledge a chunk: marking it gone")
+                self.log(f"worker {address} did not acknowledge a chunk: presuming it dead")
                 self.metrics.inc("dispatch_timeouts")
-                self.sched.leave(address)              # re-queues this batch and anything else it held
-                break
+                self.sched.leave(address, reason="timeout")     # re-queues this batch and anything else it held
+                while True:                                     # ...including what still waits in this outbox
+                    try:
+                        box.get_nowait()
+                    except queue.Empty:
+                        break
 
     def send_reply(self, address: str, stop: threading.Event):
         while self.running and not stop.is_set():

@@ -76,12 +76,27 @@ class Membership:
             self.workers[addr] = w
             return w, True
 
-    def leave(self, addr: str) -> bool:
+    def leave(self, addr: str, reason: str = "leave") -> bool:
         with self.lock:
             w = self.workers.get(addr)
             if w is None or not w.alive:
                 return False
             w.alive = False
+            w.meta["left"] = reason
+            self.epoch += 1
+            return True
+
+    def revive(self, addr: str, now: Optional[float] = None) -> bool:
+        """A worker that was only *presumed* dead (silence / send timeout) has spoken again: take it back.
+        A worker that left on its own (`end`) must join again."""
+        with self.lock:
+            w = self.workers.get(addr)
+            if w is None or w.alive or w.meta.get("left") != "timeout":
+                return False
+            w.alive = True
+            w.inflight = 0
+            w.meta.pop("left", None)
+            w.last_seen = time.monotonic() if now is None else now
             self.epoch += 1
             return True
 
@@ -149,11 +164,20 @@ class Scheduler:
             self.cv.notify_all()
         return w, new
 
-    def leave(self, addr: str) -> List[Batch]:
-        """A worker leaves (voluntarily or declared dead): its in-flight batches go back to the
-        FRONT of their requesters' queues. Returns the re-queued batches."""
-        self.members.leave(addr)
-        return self._requeue_where(lambda f: f.worker == addr, reason="leave")
+    def leave(self, addr: str, reason: str = "leave") -> List[Batch]:
+        """A worker leaves (voluntarily, ``reason="leave"``) or is declared dead (``"timeout"``): its in-flight
+        batches go back to the FRONT of their requesters' queues. Returns the re-queued batches."""
+        self.members.leave(addr, reason)
+        return self._requeue_where(lambda f: f.worker == addr, reason=reason)
+
+    def revive(self, addr: str) -> bool:
+        """See `Membership.revive`; wakes the dispatcher when the worker is taken back."""
+        ok = self.members.revive(addr, now=self.clock())
+        if ok:
+            self.stats["revived"] += 1
+            with self.cv:
+                self.cv.notify_all()
+        return ok
 
     def become_requester(self, addr: str) -> bool:
         ok = self.members.set_role(addr, "requester")
@@ -253,6 +277,17 @@ class Scheduler:
         with self.cv:
             f = self.inflight.get(batch_id)
             if f is None:
+                # not in flight: either a duplicate, or the late result of a batch that was re-queued because its
+                # owner was presumed dead - then the result is good and the pending re-dispatch is cancelled
+                for q in self.queues.values():
+                    for b in q:
+                        if b.batch_id == batch_id:
+                            q.remove(b)
+                            self.done[b.requester].add(batch_id)
+                            self.stats["completed"] += 1
+                            self.stats["late_results"] += 1
+                            self.cv.notify_all()
+                            return b
                 self.stats["duplicate_results"] += 1
                 return None
             if worker is not None and worker != f.worker:
@@ -289,7 +324,7 @@ class Scheduler:
         out: List[Batch] = []
         for addr in dead:
             self.stats["timeouts"] += 1
-            out.extend(self.leave(addr))
+            out.extend(self.leave(addr, reason="timeout"))
         return out
 
     def _requeue_where(self, pred, reason: str) -> List[Batch]:

@@ -28,14 +28,21 @@ except Exception:  # pragma: no cover
 
 
 class FrameSource:
-    """Iterator of BGR uint8 frames. `path` may be a video file, ``live`` (headless: a synthetic
-    camera, there is no capture device or window system on the box) or ``synthetic:N:HxW``."""
+    """Iterator of BGR uint8 frames. `path` may be a video file, ``live`` (capture device 0 as in worker.py:96 when one
+    exists and ``DVC_LIVE_CAMERA`` is not 0; otherwise - e.g. on a headless GPU box - a synthetic camera) or
+    ``synthetic:N:HxW``."""
 
     def __init__(self, path: str, max_frames: Optional[int] = None):
         self.path = path
         self.max_frames = max_frames
         self.cap = None
         self.synthetic = None
+        if path == "live" and cv2 is not None and os.environ.get("DVC_LIVE_CAMERA", "1") != "0" and os.path.exists("/dev/video0"):
+            cap = cv2.VideoCapture(0)
+            if cap.isOpened():
+                self.cap = cap
+                return
+            cap.release()
         if path == "live" or path.startswith("synthetic"):
             n, h, w = (max_frames or 300), 480, 640
             if path.startswith("synthetic:"):

@@ -140,6 +140,29 @@ def test_fault_injection_flags_job_still_completes(tmp_path, fault):
         srv.exit_threads()
 
 
+def test_slow_only_worker_is_revived_and_the_job_finishes(tmp_path):
+    """The only worker needs longer per chunk than the in-flight timeout: it is presumed dead, its late results are
+    still accepted (cancelling the re-dispatch) and it is taken back, so the job completes instead of stalling."""
+    port = _udp_port()
+    srv = coordinator("127.0.0.1", _cfg(port, worker_timeout_s=0.6))
+    video = write_synthetic_video(str(tmp_path / "in.mp4"), 24, 96, 128)
+    try:
+        slow = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(delay=1.3), out_dir=str(tmp_path))
+        req = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        assert slow.ready.wait(5) and req.ready.wait(5)
+        req.become_requester(video)
+        secs = req.wait_job(90)
+        assert secs is not None, srv.sched.snapshot()
+        assert _count_frames(str(tmp_path / "video0.mp4")) == 24
+        st = srv.sched.stats
+        assert st["timeouts"] >= 1 and st["revived"] >= 1 and st["late_results"] >= 1, dict(st)
+        snap = srv.sched.snapshot()
+        assert snap["inflight"] == 0 and snap["pending"] == 0
+        slow.exit_threads(); req.exit_threads()
+    finally:
+        srv.exit_threads()
+
+
 def test_idempotent_join_and_compat_drop_modes(tmp_path):
     port = _udp_port()
     srv = coordinator("127.0.0.1", _cfg(port))

@@ -148,6 +148,30 @@ def test_elastic_8_4_8_no_lost_frames_randomized():
     assert s.stats["redispatched"] > 0 and s.outstanding() == 0
 
 
+def test_late_result_cancels_redispatch_and_presumed_dead_worker_is_revived():
+    """A slow worker is declared dead by the timeout and its batch re-queued; when its result arrives after all the
+    result counts (once), the queued copy is dropped, and the worker is taken back.  A worker that said `end` is not."""
+    t = [0.0]
+    s = Scheduler(worker_timeout_s=5.0, clock=lambda: t[0])
+    s.join("slow"); s.join("client"); s.become_requester("client")
+    b = s.submit("client", [1, 2, 3])
+    d = s.next_dispatch()
+    assert d is not None and d[1].addr == "slow"
+    t[0] = 6.0
+    assert [x.batch_id for x in s.check_timeouts()] == [b.batch_id]
+    assert s.pending() == 1 and not s.members.workers["slow"].alive and s.next_dispatch() is None
+    done = s.complete(b.batch_id, "slow")                      # the late result
+    assert done is not None and done.batch_id == b.batch_id and s.pending() == 0 and s.outstanding() == 0
+    assert s.complete(b.batch_id, "slow") is None              # and only once
+    assert s.stats["late_results"] == 1 and s.stats["duplicate_results"] == 1
+    assert s.revive("slow") and s.members.workers["slow"].alive and not s.revive("slow")
+    b2 = s.submit("client", [4])
+    d2 = s.next_dispatch()
+    assert d2 is not None and d2[1].addr == "slow" and s.complete(b2.batch_id, "slow") is not None
+    s.leave("slow")                                            # voluntary `end`: must join again
+    assert not s.revive("slow") and not s.members.workers["slow"].alive
+
+
 def test_reorder_buffer():
     rb = ReorderBuffer(1)
     assert rb.push(2, "b") == []
