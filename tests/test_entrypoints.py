@@ -79,5 +79,6 @@ def test_new_clients_against_unmodified_reference_server(tmp_path):
         import signal
         try:
             os.killpg(os.getpgid(srv.pid), signal.SIGKILL)     # the reference server never exits on its own
+            srv.wait(timeout=10)                               # its fixed ports are free again for the next test
         except Exception:
             pass

@@ -35,14 +35,20 @@ def _frames_of(path):
 @pytest.fixture(scope="module")
 def reference_run(tmp_path_factory):
     """One job through the reference: server + 1 worker + 1 requester, 2 chunks of 16 frames of 128x96 video."""
+    import time
     for port, kind in ((9999, socket.SOCK_DGRAM), (5555, socket.SOCK_STREAM)):
-        s = socket.socket(socket.AF_INET, kind)
-        try:
-            s.bind(("", port))
-        except OSError:
+        for attempt in range(20):                      # a reference server killed by an earlier test may still be dying
+            s = socket.socket(socket.AF_INET, kind)
+            s.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+            try:
+                s.bind(("", port))
+                break
+            except OSError:
+                time.sleep(0.25)
+            finally:
+                s.close()
+        else:
             pytest.skip(f"port {port} (fixed in the reference, server.py:11,18) is busy")
-        finally:
-            s.close()
     env = dict(os.environ, DVC_REF_KEEP="1", DVC_REF_TIMEOUT="120", PYTHONPATH=ROOT)
     p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "2",
                         "--warmup", "0", "--batch", "16", "--frame-h", "96", "--frame-w", "128"],
