@@ -55,9 +55,9 @@ if os.path.exists(so):
         m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_]*)", ln)
         if m and cur:
             table[cur][m.group(1)] += 1
-    keys = ["UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "FHFMA", "HMMA", "FFMA", "LDS", "STS", "LDG", "STG", "ST", "LD", "BAR"]
+    keys = ["UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "ACQBULK", "PREEXIT", "FHFMA", "HMMA", "FFMA", "LDS", "STS", "LDG", "STG", "ST", "LD", "BAR"]
     lines = ["# SASS mnemonic counts per kernel (cuobjdump -sass of ops/libdvc_b200.so, sm_100a)", "",
-             "UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG/UTMASTG = TMA load/store, SYNCS = mbarrier ops, FHFMA = fp16xfp16+fp32 FMA.", "",
+             "UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG/UTMASTG = TMA load/store, SYNCS = mbarrier ops, ACQBULK / PREEXIT = griddepcontrol.wait / launch_dependents (programmatic dependent launch), FHFMA = fp16xfp16+fp32 FMA.", "",
              "| kernel | instrs | " + " | ".join(keys) + " |", "|---|---|" + "---|" * len(keys)]
     for fn, cnt in table.items():
         short = subprocess.run(["c++filt", fn], capture_output=True, text=True).stdout.strip().split("(")[0]
