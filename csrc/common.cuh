@@ -50,6 +50,9 @@ int make_tmap_nhwc_f16(CUtensorMap* out, const void* base, uint64_t n, uint64_t 
 // Because every kernel of the chain waits, "predecessor complete" is transitive back to the start of the stream.
 bool pdl_enabled();
 
+int make_tmap_nhwc_f16_sw128(CUtensorMap* out, const void* base, uint64_t n, uint64_t h, uint64_t w, uint64_t c,
+                             uint32_t box_c, uint32_t box_w, uint32_t box_h);
+
 // ---------------------------------------------------------------------------------- PTX
 #ifdef __CUDACC__
 template <typename... KArgs, typename... Args>

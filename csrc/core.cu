@@ -91,6 +91,34 @@ int make_tmap_nhwc_f16(CUtensorMap* out, const void* base, uint64_t n, uint64_t 
   return DVC_OK;
 }
 
+// Same 4-D NHWC view with 128-byte swizzle: for TMA *stores* of epilogue tiles staged as 128-byte rows
+// (box_c must be 64 fp16 = 128 bytes); coordinates outside the tensor are clipped by the hardware.
+int make_tmap_nhwc_f16_sw128(CUtensorMap* out, const void* base, uint64_t n, uint64_t h, uint64_t w, uint64_t c,
+                             uint32_t box_c, uint32_t box_w, uint32_t box_h) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
+    return DVC_ERR_CUDA;
+  }
+  if (box_c * 2 != 128) {
+    set_error("make_tmap_nhwc_f16_sw128: box_c=%u must be 64 (128-byte swizzle rows)", box_c);
+    return DVC_ERR_ARG;
+  }
+  cuuint64_t dims[4] = {c, w, h, n};
+  cuuint64_t strides[3] = {c * 2, w * c * 2, h * w * c * 2};
+  cuuint32_t box[4] = {box_c, box_w, box_h, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(4d, sw128) failed: CUresult %d (n=%llu h=%llu w=%llu c=%llu box=%ux%ux%u)", (int)r,
+              (unsigned long long)n, (unsigned long long)h, (unsigned long long)w, (unsigned long long)c, box_c, box_w, box_h);
+    return DVC_ERR_CUDA;
+  }
+  return DVC_OK;
+}
+
 }  // namespace dvc
 
 extern "C" int dvc_version(void) { return 100; }

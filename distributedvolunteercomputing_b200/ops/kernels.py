@@ -161,6 +161,21 @@ def gemm_head(a: torch.Tensor, wt: torch.Tensor, bias: torch.Tensor, loc: torch.
                                   block_n, L.stream_ptr(stream)), "gemm_head")
 
 
+def dwpw_fused_s1(x: torch.Tensor, wdw_9c: torch.Tensor, bdw: torch.Tensor, wpw: torch.Tensor, bpw: torch.Tensor,
+                  out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
+    """EXPERIMENTAL (csrc/dwpw_fused.cu: compiles, not yet validated on hardware, unused by the engine): depthwise 3x3
+    stride 1 + ReLU fused into the pointwise 1x1 + ReLU of the same block.  x [B,H,W,C_in] fp16 -> [B,H,W,C_out] fp16."""
+    assert x.dtype == torch.float16 and x.is_cuda and x.dim() == 4 and x.is_contiguous()
+    assert wpw.dtype == torch.float16 and wpw.is_contiguous() and wpw.shape[1] == x.shape[3]
+    B, H, W, C_in = x.shape
+    C_out = wpw.shape[0]
+    if out is None:
+        out = torch.empty((B, H, W, C_out), dtype=torch.float16, device=x.device)
+    L.check(L.load().dvc_dwpw_fused_s1(L.ptr(x), B, H, W, C_in, L.ptr(wdw_9c), L.ptr(bdw), L.ptr(wpw), L.ptr(bpw), C_out,
+                                       L.ptr(out), L.stream_ptr(stream)), "dwpw_fused_s1")
+    return out
+
+
 # ------------------------------------------------------------------------------------ K6..K10
 def priorbox(specs, img_hw: Tuple[int, int], device) -> Tuple[torch.Tensor, torch.Tensor]:
     total = sum(s.count for s in specs)

@@ -211,6 +211,14 @@ int dvc_plan_set_timestamps(dvc_plan*, unsigned long long* t_ingest, unsigned lo
 int dvc_plan_set_epoch_gate(dvc_plan*, const uint32_t* epoch_now, const uint32_t* epoch_expect, uint32_t* stale_count);
 int dvc_plan_run(dvc_plan*, void* stream);
 
+/* EXPERIMENTAL - compiles, not yet validated on hardware, not used by the plan executor (csrc/dwpw_fused.cu).
+ * Fused depthwise 3x3 stride 1 (+bias+ReLU) -> pointwise 1x1 (+bias+ReLU) of one MobileNet block; the intermediate
+ * stays in shared memory as the A operand of tcgen05.mma.  No reference counterpart (the reference runs cv2.dnn).
+ * in [B,H,W,C_in] fp16, wdw [9][C_in] fp32, bdw [C_in], wpw [C_out][C_in] fp16, bpw [C_out], out [B,H,W,C_out] fp16;
+ * C_in = 32 or a multiple of 64, C_out in {64,128,192,256}. */
+int dvc_dwpw_fused_s1(const void* in_f16, int B, int H, int W, int C_in, const float* wdw, const float* bdw,
+                      const void* wpw_f16, const float* bpw, int C_out, void* out_f16, void* stream);
+
 /* ---- P2P substrate (csrc/p2p.cu).  These DO allocate / map device memory (set-up time only).
  * A buffer is owned by one GPU process, exported as a 64-byte CUDA IPC handle and mapped by the
  * other per-GPU processes of the box; kernels then load/store it directly over NVLink.  This
