@@ -54,6 +54,7 @@ class Config:
     batch: int = 64                     # frames per GPU batch (BASELINE.json config 2)
     sub_batch: int = 0                  # 0 = whole batch per launch; >0 runs conv0..conv6 in sub-batches of this size
     use_cuda_graph: bool = True
+    max_cached_states: int = 64         # per-(batch, frame size, requester) device states kept by one engine (LRU)
     metrics_jsonl: Optional[str] = None
     metrics_port: int = -1              # >= 0: serve /metrics (Prometheus text) and /summary on this port (0 = any free port)
 

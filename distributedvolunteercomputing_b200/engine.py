@@ -119,7 +119,11 @@ class NativeEngine:
         self.device = torch.device(device)
         self.requester_id = requester_id
         self.max_batch = max_batch or self.cfg.batch
-        self._states: Dict[Tuple[int, int, int, str], _ShapeState] = {}
+        # LRU: a long-lived worker sees many (frame size, requester) pairs; states held by streams / lanes (slot > 0)
+        # belong to their caller and are never evicted
+        from .utils.lru import LruCache
+        self._states: "LruCache[_ShapeState]" = LruCache(max(1, self.cfg.max_cached_states), on_evict=self._release_state,
+                                                         can_evict=lambda st: getattr(st, "evictable", False))
         with torch.cuda.device(self.device):
             L.set_device(self.device)
             self._pack_weights()
@@ -185,8 +189,19 @@ class NativeEngine:
             with torch.cuda.device(self.device):
                 self.L.set_device(self.device)
                 st = self._make_state(B, H, W, rid)
-            self._states[key] = st
+            st.evictable = slot == 0
+            self._states.put(key, st)
         return st
+
+    def _release_state(self, key, st: _ShapeState):
+        """LRU eviction: the state is idle (process() is synchronous), but make sure before its buffers are recycled."""
+        torch.cuda.synchronize(self.device)
+        for name in ("graph_ann", "graph_noann"):
+            if hasattr(st, name):
+                delattr(st, name)
+        if getattr(st, "plan", None):
+            self.lib.dvc_plan_destroy(st.plan)
+            st.plan = None
 
     def _make_state(self, B: int, H: int, W: int, rid: str) -> _ShapeState:
         K, L, g, dev, cfg = self.K, self.L, self.graph, self.device, self.cfg

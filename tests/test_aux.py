@@ -203,6 +203,22 @@ def test_worker_declared_dead_can_rejoin_cleanly():
         srv.exit_threads()
 
 
+def test_lru_cache_evicts_oldest_unpinned_and_calls_hook():
+    from distributedvolunteercomputing_b200.utils.lru import LruCache
+    gone = []
+    c = LruCache(3, on_evict=lambda k, v: gone.append(k), can_evict=lambda v: not v.get("pinned"))
+    c.put("a", {}); c.put("p", {"pinned": True}); c.put("b", {})
+    assert c.get("a") is not None                 # refreshes a: order is now p, b, a
+    c.put("c", {})                                # over capacity: p is pinned, so b goes
+    assert gone == ["b"] and "a" in c and "p" in c and "c" in c and len(c) == 3
+    c.put("d", {}); c.put("e", {})
+    assert gone == ["b", "a", "c"] and "p" in c and c.evictions == 3
+    for k in "xyz":                               # everything else pinned: the cache may exceed its capacity, never drops the newcomer
+        c.put(k, {"pinned": True})
+    assert "z" in c and "p" in c and len(c) >= 4
+    c.clear(); assert len(c) == 0
+
+
 def test_logger_is_gated_by_verbose(capsys):
     Logger(False, "[x] ").log("hidden")
     Logger(True, "[x] ").log("shown")
