@@ -4,6 +4,8 @@
   --config live          single synthetic 1080p stream at --fps 30|60: p50/p99 per-frame latency
   --config elastic       8 -> 4 -> 8 workers (or N -> N/2 -> N) mid-stream, no dropped frames
   --config multi_client  32 concurrent synthetic 720p streams, whole-box frames/s
+  --config cpu_localhost server + 1 worker + requester on localhost, CPU engine, synthetic 64-frame video (no GPU):
+                         this framework's network stack and, with the same video and caffemodel, the unmodified reference
 
 Prints one JSON line per run.  Latencies are host wall-clock from "frame handed to the cluster" to
 "result delivered in order" (they include H2D, all kernels, D2H and scheduling).
@@ -29,7 +31,65 @@ def synth(n, h, w, seed=0):
     return np.ascontiguousarray(np.repeat(np.repeat(small, 16, axis=1), 16, axis=2)[:, :h, :w])
 
 
+def cpu_localhost(frames: int, chunk: int, h: int, w: int):
+    """BASELINE.json config 1: everything over the loopback UDP / ZeroMQ wire, model on the CPU."""
+    import re
+    import socket
+    import subprocess
+    import tempfile
+    from distributedvolunteercomputing_b200 import caffe_io
+    from distributedvolunteercomputing_b200.client import client
+    from distributedvolunteercomputing_b200.config import Config
+    from distributedvolunteercomputing_b200.coordinator import coordinator
+    from distributedvolunteercomputing_b200.engine import CpuEngine
+    from distributedvolunteercomputing_b200.models.mobilenet_ssd import SSDGraph
+    from distributedvolunteercomputing_b200.session import write_synthetic_video
+    work = tempfile.mkdtemp(prefix="dvc_cpu_")
+    proto_path, model_path = os.path.join(work, "MobileNetSSD_deploy.prototxt.txt"), os.path.join(work, "MobileNetSSD_deploy.caffemodel")
+    open(proto_path, "w").write(caffe_io.mobilenet_ssd_prototxt())
+    net = caffe_io.load_netdef(proto_path)
+    caffe_io.write_caffemodel(model_path, caffe_io.random_init_weights(net, seed=1, conf_gain=2.5))
+    video = write_synthetic_video(os.path.join(work, "in.mp4"), frames, h, w)
+    graph = SSDGraph.from_files(proto_path, model_path)
+    s = socket.socket(socket.AF_INET, socket.SOCK_DGRAM); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    cfg = lambda: Config(control_port=port, my_port=0, number_of_frames_in_chunk=chunk, control_retry_s=1.0, data_port_lo=0,
+                         data_port_hi=-1, worker_timeout_s=120.0, device="cpu")
+    srv = coordinator("127.0.0.1", cfg())
+    try:
+        wrk = client("127.0.0.1", "127.0.0.1", cfg(), engine=CpuEngine(graph, cfg()), out_dir=work)
+        req = client("127.0.0.1", "127.0.0.1", cfg(), engine=CpuEngine(graph, cfg()), out_dir=work)
+        wrk.ready.wait(5); req.ready.wait(5)
+        req.become_requester(video)
+        secs = req.wait_job(600)
+        wrk.exit_threads(); req.exit_threads()
+    finally:
+        srv.exit_threads()
+    out = {"config": "cpu_localhost", "impl": "native-cpu", "frames": frames, "chunk": chunk, "frame_hw": [h, w],
+           "job_seconds": secs, "frames_per_s": round(frames / secs, 2) if secs else None,
+           "note": "coordinator + worker + requester threads over loopback UDP/ZeroMQ, CpuEngine (torch fp32 CPU), all frames kept"}
+    print(json.dumps(out), flush=True)
+    ref = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "1", "--warmup", "0",
+                          "--batch", str(frames), "--frame-h", str(h), "--frame-w", str(w)], capture_output=True, text=True, timeout=900, cwd=ROOT)
+    line = (ref.stdout.strip().splitlines() or ["{}"])[-1]
+    try:
+        r = json.loads(line)
+        print(json.dumps({"config": "cpu_localhost", "impl": "reference", "frames": r.get("config", {}).get("frames"),
+                          "frames_per_s": r.get("value"), "job_seconds": r.get("config", {}).get("job_seconds"),
+                          "unavailable": r.get("unavailable")}), flush=True)
+    except Exception:
+        print(json.dumps({"config": "cpu_localhost", "impl": "reference", "unavailable": line[-200:]}), flush=True)
+
+
 def main():
+    if "cpu_localhost" in sys.argv:
+        ap = argparse.ArgumentParser()
+        ap.add_argument("--config", required=True)
+        ap.add_argument("--frames", type=int, default=64)
+        ap.add_argument("--chunk", type=int, default=64)
+        ap.add_argument("--frame-h", type=int, default=300)
+        ap.add_argument("--frame-w", type=int, default=300)
+        a = ap.parse_args()
+        return cpu_localhost(a.frames, a.chunk, a.frame_h, a.frame_w)
     import torch
     from distributedvolunteercomputing_b200.config import Config
     from distributedvolunteercomputing_b200.engine import NativeEngine
