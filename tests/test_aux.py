@@ -219,6 +219,43 @@ def test_lru_cache_evicts_oldest_unpinned_and_calls_hook():
     c.clear(); assert len(c) == 0
 
 
+def test_engine_state_cache_eviction_and_close(monkeypatch):
+    """NativeEngine.state() bookkeeping without a GPU (device work stubbed out): same key -> same state, the oldest
+    unpinned state is evicted and its native plan destroyed, stream / lane states (slot > 0) survive, close() frees all."""
+    import contextlib
+    import types
+    import torch
+    from distributedvolunteercomputing_b200.config import Config
+    from distributedvolunteercomputing_b200.engine import NativeEngine, _ShapeState
+    from distributedvolunteercomputing_b200.utils.lru import LruCache
+    monkeypatch.setattr(torch.cuda, "device", lambda d: contextlib.nullcontext())
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda d=None: None)
+    e = NativeEngine.__new__(NativeEngine)
+    e.cfg, e.device, e.requester_id = Config(max_cached_states=3), torch.device("cpu"), ""
+    destroyed = []
+    e.lib = types.SimpleNamespace(dvc_plan_destroy=lambda p: destroyed.append(p))
+    e.L = types.SimpleNamespace(set_device=lambda d: None)
+    e._states = LruCache(3, on_evict=e._release_state, can_evict=lambda st: getattr(st, "evictable", False))
+
+    def make(B, H, W, rid):
+        st = _ShapeState()
+        st.plan, st.graph_ann = ("plan", B, rid), object()
+        return st
+
+    e._make_state = make
+    a = e.state(1, 2, 3)
+    assert e.state(1, 2, 3) is a and e.state(1, 2, 3, requester_id="other") is not a
+    lane = e.state(4, 2, 3, slot=5)                       # pinned: belongs to a stream / lane
+    e.state(2, 2, 3)
+    assert len(e._states) == 3 and destroyed == [("plan", 1, "")] and not hasattr(a, "graph_ann") and a.plan is None
+    e.state(3, 2, 3); e.state(5, 2, 3)
+    assert (4, 2, 3, "", 5) in e._states and lane.plan is not None and len(e._states) == 3
+    n = len(destroyed)
+    e.close()
+    assert len(e._states) == 0 and len(destroyed) == n + 3
+    e.close()                                             # idempotent (also what __del__ calls)
+
+
 def test_logger_is_gated_by_verbose(capsys):
     Logger(False, "[x] ").log("hidden")
     Logger(True, "[x] ").log("shown")
