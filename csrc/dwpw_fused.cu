@@ -1,5 +1,7 @@
-// EXPERIMENTAL - compiled, NOT yet run on hardware (written after this round's GPU budget was spent).
-// Nothing in the plan executor calls it; scripts/check_dwpw_fused.py is the numerics / timing harness for it.
+// EXPERIMENTAL - written after this round's GPU budget was all but spent.  Its one hardware run (the last
+// seconds of the budget, profiles/dwpw_fused_first_run.log) was bit-identical to the dwconv3x3 -> gemm_f16 path on five
+// small shapes (overhanging tiles, C_in = 32, C_out = 192, several K chunks); it has NOT been timed at the flagship shapes
+// and nothing in the plan executor calls it yet.  scripts/check_dwpw_fused.py is the numerics / timing harness.
 //
 // K3 as the producer stage of K2: depthwise 3x3 (stride 1, pad 1) + bias + ReLU feeding the
 // pointwise 1x1 + bias + ReLU of the same MobileNet block without the intermediate ever leaving the SM.

@@ -163,7 +163,8 @@ def gemm_head(a: torch.Tensor, wt: torch.Tensor, bias: torch.Tensor, loc: torch.
 
 def dwpw_fused_s1(x: torch.Tensor, wdw_9c: torch.Tensor, bdw: torch.Tensor, wpw: torch.Tensor, bpw: torch.Tensor,
                   out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
-    """EXPERIMENTAL (csrc/dwpw_fused.cu: compiles, not yet validated on hardware, unused by the engine): depthwise 3x3
+    """EXPERIMENTAL (csrc/dwpw_fused.cu: bit-identical to dwconv3x3 + gemm_f16 on small shapes in its one hardware run, not
+    yet timed, unused by the engine): depthwise 3x3
     stride 1 + ReLU fused into the pointwise 1x1 + ReLU of the same block.  x [B,H,W,C_in] fp16 -> [B,H,W,C_out] fp16."""
     assert x.dtype == torch.float16 and x.is_cuda and x.dim() == 4 and x.is_contiguous()
     assert wpw.dtype == torch.float16 and wpw.is_contiguous() and wpw.shape[1] == x.shape[3]

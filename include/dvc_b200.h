@@ -211,7 +211,8 @@ int dvc_plan_set_timestamps(dvc_plan*, unsigned long long* t_ingest, unsigned lo
 int dvc_plan_set_epoch_gate(dvc_plan*, const uint32_t* epoch_now, const uint32_t* epoch_expect, uint32_t* stale_count);
 int dvc_plan_run(dvc_plan*, void* stream);
 
-/* EXPERIMENTAL - compiles, not yet validated on hardware, not used by the plan executor (csrc/dwpw_fused.cu).
+/* EXPERIMENTAL - bit-identical to dvc_dwconv3x3 + dvc_gemm_f16 on small shapes in its one hardware run, not yet timed
+ * at the flagship shapes, not used by the plan executor (csrc/dwpw_fused.cu).
  * Fused depthwise 3x3 stride 1 (+bias+ReLU) -> pointwise 1x1 (+bias+ReLU) of one MobileNet block; the intermediate
  * stays in shared memory as the A operand of tcgen05.mma.  No reference counterpart (the reference runs cv2.dnn).
  * in [B,H,W,C_in] fp16, wdw [9][C_in] fp32, bdw [C_in], wpw [C_out][C_in] fp16, bpw [C_out], out [B,H,W,C_out] fp16;
