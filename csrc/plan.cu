@@ -47,8 +47,10 @@ int dw_launch(const DwLaunch* L, cudaStream_t st);
 DwLaunch* dw_alloc();
 void dw_free(DwLaunch*);
 int im2col_launch(const void* in, int B, int H, int W, int C, void* out, cudaStream_t st);
+int dwpw_fused_s1_launch(const void* in, int B, int H, int W, int C_in, const float* wdw, const float* bdw, const void* wpw,
+                         const float* bpw, int C_out, void* out, cudaStream_t st);
 
-enum OpKind { OP_PREPROC, OP_DW, OP_GEMM, OP_IM2COL, OP_DET };
+enum OpKind { OP_PREPROC, OP_DW, OP_GEMM, OP_IM2COL, OP_DET, OP_DWPW };
 
 struct Op {
   OpKind kind;
@@ -59,6 +61,8 @@ struct Op {
   // im2col
   const void* in = nullptr; void* out = nullptr; const float* w = nullptr; const float* b = nullptr;
   int B = 0, H = 0, W = 0, C = 0, stride = 1, relu = 0;
+  // fused depthwise -> pointwise (experimental): w / b above are the depthwise ones
+  const void* wpw = nullptr; const float* bpw = nullptr; int C_out = 0;
 };
 
 }  // namespace dvc
@@ -121,6 +125,18 @@ extern "C" int dvc_plan_add_im2col(dvc_plan* p, const void* in_f16, int B, int H
   DVC_REQUIRE(p, "plan is null");
   DVC_REQUIRE(C % 8 == 0, "im2col: C=%d unsupported", C);
   Op op; op.kind = OP_IM2COL; op.in = in_f16; op.out = out_f16; op.B = B; op.H = H; op.W = W; op.C = C;
+  p->ops.push_back(op);
+  return DVC_OK;
+}
+
+/* EXPERIMENTAL (csrc/dwpw_fused.cu): one op for a stride-1 depthwise 3x3 + its pointwise 1x1, both with ReLU. */
+extern "C" int dvc_plan_add_dwpw_fused(dvc_plan* p, const void* in_f16, int B, int H, int W, int C_in, const float* wdw,
+                                       const float* bdw, const void* wpw_f16, const float* bpw, int C_out, void* out_f16) {
+  DVC_REQUIRE(p, "plan is null");
+  DVC_REQUIRE((C_in == 32 || C_in % 64 == 0) && C_out % 64 == 0 && C_out >= 64 && C_out <= 256,
+              "dwpw_fused: C_in=%d / C_out=%d unsupported", C_in, C_out);
+  Op op; op.kind = OP_DWPW; op.in = in_f16; op.out = out_f16; op.B = B; op.H = H; op.W = W; op.C = C_in;
+  op.w = wdw; op.b = bdw; op.wpw = wpw_f16; op.bpw = bpw; op.C_out = C_out;
   p->ops.push_back(op);
   return DVC_OK;
 }
@@ -191,6 +207,7 @@ extern "C" int dvc_plan_run(dvc_plan* p, void* stream) {
       case OP_GEMM: rc = gemm_launch(op.gemm, st); break;
       case OP_IM2COL: rc = im2col_launch(op.in, op.B, op.H, op.W, op.C, op.out, st); break;
       case OP_DET: rc = det_launch(op.det, st); break;
+      case OP_DWPW: rc = dwpw_fused_s1_launch(op.in, op.B, op.H, op.W, op.C, op.w, op.b, op.wpw, op.bpw, op.C_out, op.out, st); break;
     }
     if (rc) return rc;
   }

@@ -83,6 +83,8 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
             pass
         self.continue_requesting = False
         self.running = False
+        if self.sender:
+            self.sender.abort.set()            # a send still waiting for the server's reply gives up now
         for t in self.threads:
             t.join(timeout=3.0)
         if self.tracker and self.tracker.sink:

@@ -80,6 +80,8 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
     def exit_threads(self):
         """`quit` (server.py:160-163) - and the threads really stop."""
         self.running = False
+        for snd in list(self.senders.values()):
+            snd.abort.set()                    # sender threads blocked on a reply give up within 250 ms
         if getattr(self, "metrics_http", None) is not None:
             self.metrics_http.shutdown()
             self.metrics_http.server_close()

@@ -14,6 +14,7 @@ Two implementations behind one interface:
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Dict, Optional, Sequence, Tuple
 
@@ -285,6 +286,11 @@ class NativeEngine:
                                           w.shape[1], w.shape[1], 1, None, 0, 0, C.byref(head), 0), h.tap + "_mbox")
 
         assert body[0].name == "conv0" and body[0].k == 3 and body[0].cout == 32, "first layer must be the 3x3/s2 stem"
+        fuse = os.environ.get("DVC_FUSE_DWPW", "0") == "1"       # experimental fused dw -> pw launches (csrc/dwpw_fused.cu)
+
+        def fusable(dw, pw):
+            return (dw.depthwise and dw.stride == 1 and dw.relu and pw.k == 1 and not pw.depthwise and pw.relu
+                    and pw.cin == dw.cout and pw.cout % 64 == 0 and 64 <= pw.cout <= 256 and (dw.cin == 32 or dw.cin % 64 == 0))
         # ---- early layers, per sub-batch, in the small (L2-resident) ping-pong buffers
         for b0 in range(0, B, sub):
             nb = min(sub, B - b0)
@@ -293,8 +299,21 @@ class NativeEngine:
                 plan, L.ptr(st.frames400_flat), st.stride400, None, nb, st.h4, st.w4,
                 L.ptr(st.t_lin.xs), L.ptr(st.t_lin.xq), L.ptr(st.t_lin.ys), L.ptr(st.t_lin.yq), L.ptr(self.w["conv0"]),
                 L.ptr(self.b["conv0"]), C.cast(st.mean, C.c_void_p), float(self.cfg.scale), L.ptr(cur), b0), "conv0")
-            for li in range(1, split_idx + 1):
+            li = 1
+            while li <= split_idx:
                 c = body[li]
+                nxt = body[li + 1] if li + 1 <= split_idx else None
+                if fuse and nxt is not None and fusable(c, nxt):
+                    # EXPERIMENTAL (DVC_FUSE_DWPW=1): depthwise + pointwise of one block as a single launch
+                    dst = L.ptr(st.fA) + b0 * per_frame[li + 1] * esz if li + 1 == split_idx else L.ptr(other)
+                    L.check(lib.dvc_plan_add_dwpw_fused(plan, L.ptr(cur), nb, c.in_hw[0], c.in_hw[1], c.cin, L.ptr(self.w[c.name]),
+                                                        L.ptr(self.b[c.name]), L.ptr(self.w[nxt.name]), L.ptr(self.b[nxt.name]),
+                                                        nxt.cout, dst), c.name + "+" + nxt.name)
+                    cur, other = other, cur
+                    if nxt.top in heads and li + 1 != split_idx:
+                        add_head(heads[nxt.top], dst, nb, b0)
+                    li += 2
+                    continue
                 if li == split_idx:
                     dst = L.ptr(st.fA) + b0 * per_frame[li] * esz
                 else:
@@ -303,6 +322,7 @@ class NativeEngine:
                 cur, other = other, cur
                 if c.top in heads and li != split_idx:
                     add_head(heads[c.top], dst, nb, b0)
+                li += 1
         # ---- late layers on the full batch
         cur, other = st.fA, st.fB
         if body[split_idx].top in heads:

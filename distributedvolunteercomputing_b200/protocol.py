@@ -15,6 +15,7 @@ timeout (the reference hangs forever on a dead peer and on quit), and ports are 
 from __future__ import annotations
 
 import socket
+import threading
 from dataclasses import dataclass
 from typing import List, Optional, Sequence, Tuple
 
@@ -104,6 +105,7 @@ class ImageSender:
         self.ctx = zmq.Context.instance()
         self.connect_to = connect_to
         self.timeout_s = timeout_s
+        self.abort = threading.Event()      # set by another thread (quit): a pending reply wait gives up within 250 ms
         self._open()
 
     def _open(self):
@@ -119,8 +121,12 @@ class ImageSender:
         self.sock.send_json(md, zmq.SNDMORE)
         self.sock.send(image, copy=False)
         t = self.timeout_s if timeout_s is None else timeout_s
-        if self.sock.poll(int(t * 1000), zmq.POLLIN):
-            return self.sock.recv()
+        left_ms = int(t * 1000)
+        while left_ms > 0 and not self.abort.is_set():      # sliced so `quit` never waits for the whole timeout
+            step = min(250, left_ms)
+            if self.sock.poll(step, zmq.POLLIN):
+                return self.sock.recv()
+            left_ms -= step
         # a REQ socket that missed its reply is wedged: rebuild it so the caller can retry elsewhere
         self.sock.close(0)
         self._open()

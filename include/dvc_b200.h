@@ -191,6 +191,9 @@ int dvc_plan_add_dwconv(dvc_plan*, const void* in_f16, int B, int H, int W, int 
 int dvc_plan_add_gemm(dvc_plan*, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
                       int out_mode, void* out_f16, int ldc, int relu, const dvc_head_out* head, int block_n);
 int dvc_plan_add_im2col(dvc_plan*, const void* in_f16, int B, int H, int W, int C, void* out_f16);
+/* EXPERIMENTAL: dvc_dwpw_fused_s1 as a plan op (the engine adds it only when DVC_FUSE_DWPW=1). */
+int dvc_plan_add_dwpw_fused(dvc_plan*, const void* in_f16, int B, int H, int W, int C_in, const float* wdw, const float* bdw,
+                            const void* wpw_f16, const float* bpw, int C_out, void* out_f16);
 int dvc_plan_add_detection(dvc_plan*, const float* loc, const float* conf, const float* priors, const float* variances,
                            int B, const dvc_det_params* p, const int* slot_index, float* det, int* det_count,
                            int* boxes_i, int* box_count, uint32_t* flags, uint32_t flag_value,
