@@ -256,6 +256,64 @@ def test_engine_state_cache_eviction_and_close(monkeypatch):
     e.close()                                             # idempotent (also what __del__ calls)
 
 
+def _recorded_plan(monkeypatch, fuse):
+    """NativeEngine._build_plan against a recording stand-in for the native library (no GPU needed)."""
+    import ctypes as C
+    import types
+    import torch
+    from distributedvolunteercomputing_b200.config import Config
+    from distributedvolunteercomputing_b200.engine import NativeEngine, _ShapeState
+    from distributedvolunteercomputing_b200.models.mobilenet_ssd import SSDGraph
+    from distributedvolunteercomputing_b200.ops import lib as Lmod
+    monkeypatch.setenv("DVC_FUSE_DWPW", "1" if fuse else "0")
+    e = NativeEngine.__new__(NativeEngine)
+    e.graph, e.cfg, e.device = SSDGraph.random(seed=1), Config(), torch.device("cpu")
+    calls = []
+
+    class FakeLib:
+        def __getattr__(self, name):
+            def f(*a):
+                if name == "dvc_plan_create":
+                    return 1234
+                if name == "dvc_plan_num_ops":
+                    return len(calls)
+                calls.append((name.replace("dvc_plan_add_", ""),) + tuple(x for x in a[1:] if isinstance(x, int) and x < 10 ** 6))
+                return 0
+            return f
+
+    e.lib = FakeLib()
+    e.L = types.SimpleNamespace(ptr=lambda t: 0 if t is None else t.data_ptr(), check=lambda rc, what="": None, HeadOut=Lmod.HeadOut)
+    e._pack_weights()
+    e.priors, e.variances = torch.zeros(4), torch.zeros(4)
+    st = _ShapeState()
+    st.B, st.h4, st.w4, st.stride400 = 64, 400, 400, 480000
+    st.frames400_flat = torch.zeros(16)
+    st.t_lin = types.SimpleNamespace(xs=torch.zeros(1), xq=torch.zeros(1), ys=torch.zeros(1), yq=torch.zeros(1))
+    st.mean = (C.c_float * 3)(127.5, 0, 0)
+    st.loc, st.conf = torch.zeros((64, 1917 * 4)), torch.zeros((64, 1917 * 21))
+    st.det = st.det_count = st.boxes_i = st.box_count = st.det_scratch = torch.zeros(1)
+    st.det_params = Lmod.DetParams()
+    e._build_plan(st)
+    return calls, st.n_ops
+
+
+def test_plan_construction_default_and_fused(monkeypatch):
+    """The launch sequence the engine asks the native executor for: 46 ops by default (stem, 13 dw + 13 pw, 4 x (1x1,
+    im2col, 3x3) extras, 6 heads, detection); with the experimental switch the three stride-1 pairs whose pointwise
+    has <= 256 outputs (conv1, conv3, conv5) become one fused op each and nothing else moves."""
+    calls, n = _recorded_plan(monkeypatch, fuse=False)
+    kinds = [c[0] for c in calls]
+    assert n == 46 and kinds[0] == "preproc_conv0" and kinds[-1] == "detection"
+    assert kinds.count("dwconv") == 13 and kinds.count("im2col") == 4 and kinds.count("gemm") == 13 + 8 + 6 and "dwpw_fused" not in kinds
+    fused, nf = _recorded_plan(monkeypatch, fuse=True)
+    fk = [c[0] for c in fused]
+    assert nf == 43 and fk.count("dwpw_fused") == 3 and fk.count("dwconv") == 10 and fk.count("gemm") == 13 + 8 + 6 - 3
+    assert [c[1:] for c in fused if c[0] == "dwpw_fused"] == [(64, 150, 150, 32, 64), (64, 75, 75, 128, 128), (64, 38, 38, 256, 256)]
+    assert [k for k in fk if k != "dwpw_fused"] == [k for i, k in enumerate(kinds) if not (
+        (k == "dwconv" and calls[i][1:] in {(64, 150, 150, 32, 1, 1), (64, 75, 75, 128, 1, 1), (64, 38, 38, 256, 1, 1)})
+        or (k == "gemm" and i > 0 and kinds[i - 1] == "dwconv" and calls[i - 1][1:] in {(64, 150, 150, 32, 1, 1), (64, 75, 75, 128, 1, 1), (64, 38, 38, 256, 1, 1)}))]
+
+
 def test_logger_is_gated_by_verbose(capsys):
     Logger(False, "[x] ").log("hidden")
     Logger(True, "[x] ").log("shown")
