@@ -31,7 +31,7 @@ from .utils.metrics import Logger, Metrics
 class client:  # noqa: N801  (name kept from the reference's public surface)
     def __init__(self, server_ip: str = "localhost", own_ip: str = "localhost", cfg: Optional[Config] = None,
                  engine=None, out_dir: str = ".", start: bool = True):
-        self.cfg = cfg or Config.from_env()
+        self.cfg = (cfg or Config.from_env()).validate()
         self.cfg.server_ip, self.cfg.own_ip = server_ip, own_ip
         if int(self.cfg.my_port) == 0:
             self.cfg.my_port = proto.free_tcp_port()

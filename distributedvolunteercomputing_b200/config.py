@@ -58,6 +58,18 @@ class Config:
     metrics_jsonl: Optional[str] = None
     metrics_port: int = -1              # >= 0: serve /metrics (Prometheus text) and /summary on this port (0 = any free port)
 
+    def validate(self) -> "Config":
+        """Reject settings that would silently do something else than asked."""
+        if self.transport != "req_rep":
+            # the reference's REQ_REP=False branch connects to tcp://*:port, which ZeroMQ refuses (server.py:44-46,117-123;
+            # worker.py:65-67,165-167): it never worked there, so there is no behaviour to be compatible with
+            raise ValueError(f"transport={self.transport!r}: only 'req_rep' exists (the reference's PUB/SUB branch is dead code)")
+        if self.dispatch_policy not in ("least_loaded", "round_robin"):
+            raise ValueError(f"dispatch_policy={self.dispatch_policy!r}: use 'least_loaded' or 'round_robin'")
+        if self.number_of_frames_in_chunk < 1 or self.batch < 1:
+            raise ValueError("number_of_frames_in_chunk and batch must be positive")
+        return self
+
     @staticmethod
     def from_env(**overrides) -> "Config":
         cfg = Config()

@@ -30,7 +30,7 @@ from .utils.metrics import Logger, Metrics
 
 class coordinator:  # noqa: N801  (name kept from the reference's public surface)
     def __init__(self, ip: str = "localhost", cfg: Optional[Config] = None, start: bool = True):
-        self.cfg = cfg or Config.from_env()
+        self.cfg = (cfg or Config.from_env()).validate()
         self.my_ip = f"{ip}:{self.cfg.control_port}"
         self.logger = Logger(self.cfg.verbose, "[server] ")
         self.log = self.logger.log

@@ -71,3 +71,15 @@ def test_config_defaults_env_and_argv(monkeypatch):
     assert (c.server_ip, c.own_ip, c.my_port, c.number_of_frames_in_chunk, c.verbose) == ("10.0.0.1", "10.0.0.2", 6001, 16, True)
     assert c.mean == (127.5, 127.5, 127.5) and c.addr == "10.0.0.2:6001"
     assert Config.from_argv([], ("server_ip",)).server_ip == "localhost"      # positional-only invocation keeps working
+
+
+def test_config_rejects_settings_that_would_be_silently_ignored():
+    import pytest
+    from distributedvolunteercomputing_b200.config import Config
+    assert Config().validate().transport == "req_rep"
+    with pytest.raises(ValueError, match="PUB/SUB"):
+        Config(transport="pub_sub").validate()
+    with pytest.raises(ValueError, match="dispatch_policy"):
+        Config(dispatch_policy="random").validate()
+    with pytest.raises(ValueError):
+        Config(number_of_frames_in_chunk=0).validate()
