@@ -45,7 +45,7 @@ struct GemmArgs {
   const float* bias;
   int out_mode;        // 0: fp16 [M, ldc]   1: SSD head split store (fp32)
   int tma_store;       // out_mode 0 only: epilogue goes through smem + TMA store
-  int cluster;         // CTAs per cluster along M sharing one multicast weight tile (1, 2 or 4)
+  int cluster;         // CTAs per cluster (2 only in CTA-pair mode, else 1)
   int two_cta;         // cta_group::2: a CTA pair multiplies one 256 x block_n tile (cluster == 2, no multicast)
   int m_tiles, num_ctiles;
   int b_resident;      // whole weight matrix stays in smem (one N tile, few K blocks): loaded once per CTA
@@ -134,7 +134,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
       pdl_wait();               // A is the previous kernel's output; the (constant) resident weights are already in flight
       int it = 0;
-      const int slice_rows = g.block_n / g.cluster, slice_bytes = b_stage_bytes / g.cluster;
+      const int slice_rows = g.block_n / g.cluster;
       for (int ct = cluster_id; ct < g.num_ctiles; ct += num_clusters) {
         const int n_tile = ct % g.n_tiles, m_tile = (ct / g.n_tiles) * g.cluster + crank;
         for (int kb = 0; kb < g.num_kb; ++kb, ++it) {
@@ -152,11 +152,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           }
           mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
           tma_load_2d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], kb * BK, m_tile * BM);
-          if (g.cluster > 1) {
-            // this CTA fetches 1/cluster of the weight tile and multicasts it to every CTA of the cluster
-            tma_load_2d_mcast(sB + s * b_stage_bytes + crank * slice_bytes, &tmB, &full_bar[s], kb * BK,
-                              n_tile * g.block_n + crank * slice_rows, cmask);
-          } else if (!g.b_resident) {
+          if (!g.b_resident) {
             tma_load_2d(sB + s * b_stage_bytes, &tmB, &full_bar[s], kb * BK, n_tile * g.block_n);
           }
         }
@@ -379,15 +375,10 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
   const int b_tile_bytes = block_n * BK * 2;
   g.m_tiles = ceil_div(M, BM);
   g.b_resident = (g.n_tiles == 1 && g.num_kb * b_tile_bytes <= 64 * 1024 && g.num_tiles > 1) ? 1 : 0;
-  // Optional clusters along M sharing one multicast weight tile (DVC_GEMM_CLUSTER=2|4).  Measured on B200:
-  // no gain for these shapes (conv7: 24.5 us with 1, 2 or 4 CTAs per cluster) - the main loop is limited by
-  // how many K blocks fit in shared memory (3 stages of 48 KB at block_n=256 cover ~1500 cycles of MMA, less
-  // than the TMA round trip), not by L2 bandwidth, and multicast does not shrink the per-CTA tile.  Off by default.
+  // The weight pointer is caller-supplied, so weight tiles are fetched per CTA: TMA multicast loads here read only
+  // this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.  (The multicast
+  // variant measured no gain on these shapes anyway: conv7 24.5 us with 1, 2 or 4 CTAs per cluster.)
   int cluster = 1;
-  if (const char* env = getenv("DVC_GEMM_CLUSTER")) {
-    const int c = atoi(env);
-    if ((c == 1 || c == 2 || c == 4) && !(g.b_resident && c > 1) && (block_n / c) % 8 == 0 && g.m_tiles >= c) cluster = c;
-  }
   // CTA pairs (tcgen05 cta_group::2, DVC_GEMM_2CTA=<min K blocks>): one 256 x block_n tile per pair, each CTA stages
   // its 128 rows of A and half of the weight tile, so a stage is 16 + block_n/8 KB instead of 16 + block_n/4 KB, more
   // K blocks fit in flight and each SM reads 8 KB instead of 12 KB of operands per MMA.  Measured on B200

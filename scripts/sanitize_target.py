@@ -24,7 +24,6 @@ for (B, H, W, C, s) in [(2, 19, 19, 64, 1), (2, 20, 21, 32, 2), (1, 7, 5, 8, 1)]
 K.im2col3x3s2(rnd(2, 5, 5, 64))
 for (M, N, Kd, bn) in [(300, 128, 64, 0), (700, 64, 32, 64), (513, 48, 96, 48), (260, 256, 320, 128), (1000, 512, 256, 256)]:
     K.gemm_f16(rnd(M, Kd), rnd(N, Kd), torch.randn((N,), device=dev), True, block_n=bn)
-os.environ["DVC_GEMM_CLUSTER"] = "2"; K.gemm_f16(rnd(1100, 256), rnd(256, 256), torch.randn((256,), device=dev), True, block_n=128); os.environ.pop("DVC_GEMM_CLUSTER")
 loc = torch.zeros((2, 1917 * 4), device=dev); conf = torch.zeros((2, 1917 * 21), device=dev)
 K.gemm_head(rnd(2 * 361, 512), rnd(80, 512) * 0.05, torch.randn((80,), device=dev), loc, conf, 361, 12, 63, 0, 21)
 K.priorbox(g.priors_spec, g.input_hw, dev)
