@@ -61,6 +61,9 @@ struct DetArgs {
   // batch was dispatched under; otherwise count the frame in *stale_count and leave the sinks untouched
   const uint32_t* epoch_now; const uint32_t* epoch_expect; uint32_t* stale_count;
   unsigned long long* t_done;      // optional [B]: %globaltimer when a frame's rows have been delivered
+  // mailbox binding (csrc/mailbox.cu, optional): the flag value comes from the lane's control block, and the last CTA
+  // of the batch publishes it in *done_word (a word on the client GPU) once every frame's rows are system-visible
+  const uint32_t* flag_value_ptr; uint32_t* done_word; uint32_t* done_counter;
   // global scratch (per frame): prob [C][P], kept_n [C], kept_score [C][K], kept_idx [C][K], kept_box [C][K][4]
   float* prob; int* kept_n; float* kept_score; int* kept_idx; float* kept_box;
 };
@@ -247,12 +250,24 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
   if (threadIdx.x == 0) {
     // a dispatch made under an older membership epoch must not land in rings that may have been re-assigned
     int stale = 0;
-    if (a.epoch_now && a.epoch_expect) stale = ld_acquire_sys_u32(a.epoch_now) != ld_acquire_sys_u32(a.epoch_expect);
-    if (stale && a.stale_count) atomicAdd(a.stale_count, 1u);
+    if (a.epoch_now && a.epoch_expect) {
+      const uint32_t expect = ld_acquire_sys_u32(a.epoch_expect);
+      stale = ld_acquire_sys_u32(a.epoch_now) != expect;
+      // expect == ~0: the lane's wait saw no dispatch at all (csrc/mailbox.cu) - nothing to deliver, nothing to count
+      if (stale && a.stale_count && expect != 0xFFFFFFFFu) atomicAdd(a.stale_count, 1u);
+    }
     s_stale = stale;
   }
   __syncthreads();
-  if (s_stale) return;
+  if (s_stale) {
+    // mailbox: a batch with a rejected frame never publishes its done word (the client times out and re-dispatches);
+    // the arrival is still counted so the counter is back at zero for the lane's next batch
+    if (threadIdx.x == 0 && a.done_counter) {
+      const uint32_t prev = atomicAdd(a.done_counter, 0x10001u);
+      if ((prev & 0xFFFFu) == (uint32_t)a.B - 1u) atomicExch(a.done_counter, 0u);
+    }
+    return;
+  }
   unsigned long long* keys = reinterpret_cast<unsigned long long*>(msm);   // survivors of all classes, one sort key each
   const int f = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int slot = a.slot_index ? a.slot_index[f] : f;
@@ -340,8 +355,21 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
   // delivery: make the rows visible system-wide, then publish the slot flag
   __threadfence_system();
   __syncthreads();
-  if (tid == 0 && a.flags) st_release_sys_u32(a.flags + slot, a.flag_value);
-  if (tid == 0 && a.t_done) a.t_done[f] = globaltimer_ns();
+  if (tid == 0) {
+    const uint32_t fv = a.flag_value_ptr ? *reinterpret_cast<const volatile uint32_t*>(a.flag_value_ptr) : a.flag_value;
+    if (a.flags) st_release_sys_u32(a.flags + slot, fv);
+    if (a.done_counter) {
+      // batch-level completion: every CTA's rows were fenced to system scope above; the device-scope atomic chains
+      // them (cumulativity) to the last arriver, whose release.sys store is what the client's ld.acquire.sys observes
+      const uint32_t prev = atomicAdd(a.done_counter, 1u);
+      if ((prev & 0xFFFFu) == (uint32_t)a.B - 1u) {
+        atomicExch(a.done_counter, 0u);
+        __threadfence_system();
+        if ((prev >> 16) == 0u && a.done_word) st_release_sys_u32(a.done_word, fv);
+      }
+    }
+    if (a.t_done) a.t_done[f] = globaltimer_ns();
+  }
 }
 
 // one 8-byte sort key per per-class survivor slot, padded to a power of two for the bitonic network
@@ -385,6 +413,7 @@ int det_prepare(DetLaunch* L, const float* loc, const float* conf, const float* 
   a.det = det; a.det_count = det_count; a.boxes_i = boxes_i; a.box_count = box_count; a.flags = flags; a.flag_value = flag_value;
   a.epoch_now = nullptr; a.epoch_expect = nullptr; a.stale_count = nullptr;      // gate off until det_set_epoch_gate
   a.t_done = nullptr;
+  a.flag_value_ptr = nullptr; a.done_word = nullptr; a.done_counter = nullptr;
   const int C = p->num_classes, P = p->num_priors;
   uint8_t* s = reinterpret_cast<uint8_t*>(scratch);
   a.prob = reinterpret_cast<float*>(s);
@@ -424,6 +453,9 @@ void det_set_flag_value(DetLaunch* L, uint32_t v) { L->args.flag_value = v; }
 void det_set_timestamps(DetLaunch* L, unsigned long long* t_done) { L->args.t_done = t_done; }
 void det_set_epoch_gate(DetLaunch* L, const uint32_t* now, const uint32_t* expect, uint32_t* stale_count) {
   L->args.epoch_now = now; L->args.epoch_expect = expect; L->args.stale_count = stale_count;
+}
+void det_set_mailbox(DetLaunch* L, const uint32_t* flag_value_ptr, uint32_t* done_word, uint32_t* done_counter) {
+  L->args.flag_value_ptr = flag_value_ptr; L->args.done_word = done_word; L->args.done_counter = done_counter;
 }
 void det_set_sinks(DetLaunch* L, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index) {
   L->args.det = det; L->args.det_count = det_count; L->args.boxes_i = boxes_i; L->args.box_count = box_count;

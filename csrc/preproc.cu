@@ -28,6 +28,7 @@ struct ResizeArgs {
   int tab_off;    // byte offset of the x-tap table inside the dynamic shared memory
   const uint32_t* epoch_now;      // K14 gate (optional): skip the pull when the membership epoch has moved on
   const uint32_t* epoch_expect;
+  const uint8_t* const* src_indirect;   // optional: the source base is read from this device word (mailbox lanes)
 };
 
 // CTA-uniform "is this dispatch stale?" (thread 0 reads the two words, everyone gets the same answer).
@@ -59,7 +60,8 @@ __global__ void __launch_bounds__(256) resize_u8_kernel(const ResizeArgs a) {
   else if (a.mode == 1) { r_lo = dy0 * a.iy; r_hi = dy1 * a.iy + a.iy - 1; }
   else { r_lo = a.ys[dy0]; r_hi = min(a.ys[dy1] + 1, a.sh - 1); }
   r_hi = min(r_hi, a.sh - 1);
-  const uint8_t* frame = a.src + (size_t)b * a.src_stride;
+  const uint8_t* src_base = a.src_indirect ? *a.src_indirect : a.src;
+  const uint8_t* frame = src_base + (size_t)b * a.src_stride;
   const long long start = (long long)r_lo * row_bytes, end = (long long)(r_hi + 1) * row_bytes;
   int skew = 0;
   if (a.aligned) {
@@ -601,7 +603,7 @@ static int resize_u8_impl(const uint8_t* src, long long src_frame_stride, int B,
                           long long dst_frame_stride, int dh, int dw, int mode, const int* xs, const int* xc,
                           const float* xa, int x_taps, const int* ys, const int* yc, const float* ya, int y_taps,
                           const int* xq, const int* yq, int ix, int iy, const uint32_t* epoch_now,
-                          const uint32_t* epoch_expect, void* stream) {
+                          const uint32_t* epoch_expect, void* stream, const uint8_t* const* src_indirect = nullptr) {
   using namespace dvc;
   DVC_REQUIRE((epoch_now == nullptr) == (epoch_expect == nullptr), "resize: give both epoch words or neither");
   DVC_REQUIRE(B > 0 && sh > 0 && sw > 0 && dh > 0 && dw > 0 && mode >= 0 && mode <= 2, "resize: bad arguments");
@@ -609,8 +611,9 @@ static int resize_u8_impl(const uint8_t* src, long long src_frame_stride, int B,
   if (mode == 1) DVC_REQUIRE(ix > 0 && iy > 0 && dw * ix <= sw && dh * iy <= sh, "resize: bad integer ratio");
   if (mode == 2) DVC_REQUIRE(xs && ys && xq && yq, "resize: bilinear tables missing");
   ResizeArgs a{src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps,
-               ys, yc, ya, y_taps, xq, yq, ix, iy, 1, 0, 0, epoch_now, epoch_expect};
-  a.aligned = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && src_frame_stride % 16 == 0) ? 1 : 0;
+               ys, yc, ya, y_taps, xq, yq, ix, iy, 1, 0, 0, epoch_now, epoch_expect, src_indirect};
+  // an indirect source is promised to be 16-byte aligned by its owner (arena slots and engine buffers are)
+  a.aligned = ((src_indirect || (reinterpret_cast<uintptr_t>(src) & 15) == 0) && src_frame_stride % 16 == 0) ? 1 : 0;
   // band height: as many output rows as keep the staged source rows within ~64 KB of shared memory
   const long long row_bytes = (long long)sw * 3;
   const double sy = mode == 1 ? (double)iy : (double)sh / (double)dh;
@@ -652,6 +655,16 @@ extern "C" int dvc_resize_u8_gated(const uint8_t* src, long long src_frame_strid
                                    const uint32_t* epoch_expect, void* stream) {
   return resize_u8_impl(src, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps, ys, yc, ya,
                         y_taps, xq, yq, ix, iy, epoch_now, epoch_expect, stream);
+}
+
+extern "C" int dvc_resize_u8_indirect(const uint8_t* const* src_indirect, long long src_frame_stride, int B, int sh, int sw,
+                                      uint8_t* dst, long long dst_frame_stride, int dh, int dw, int mode, const int* xs,
+                                      const int* xc, const float* xa, int x_taps, const int* ys, const int* yc,
+                                      const float* ya, int y_taps, const int* xq, const int* yq, int ix, int iy,
+                                      const uint32_t* epoch_now, const uint32_t* epoch_expect, void* stream) {
+  DVC_REQUIRE(src_indirect != nullptr, "resize (indirect): the source word is null");
+  return resize_u8_impl(nullptr, src_frame_stride, B, sh, sw, dst, dst_frame_stride, dh, dw, mode, xs, xc, xa, x_taps, ys, yc,
+                        ya, y_taps, xq, yq, ix, iy, epoch_now, epoch_expect, stream, src_indirect);
 }
 
 extern "C" int dvc_preproc_conv0(const uint8_t* src400, long long src_frame_stride, const int* frame_index, int B, int sh,

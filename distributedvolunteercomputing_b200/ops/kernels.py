@@ -76,6 +76,17 @@ def make_linear_tables(sh: int, sw: int, dh: int, dw: int, device, area_mode: bo
                         xq=_dev_i32(xq, device), yq=_dev_i32(yq, device))
 
 
+def resize_u8_indirect(src_word: int, src_frame_stride: int, B: int, t: ResizeTables, dst: torch.Tensor,
+                       dst_frame_stride: int, gate_now: int, gate_expect: int, stream=None) -> None:
+    """K1a for a mailbox lane: the source base pointer is read by the kernel from the device word at ``src_word``
+    (``&lane_ctl.src``) and the pull is skipped unless the two gate words (device addresses) are equal."""
+    lib = L.load()
+    L.check(lib.dvc_resize_u8_indirect(src_word, src_frame_stride, B, t.sh, t.sw, L.ptr(dst), dst_frame_stride, t.dh, t.dw,
+                                       t.mode, L.ptr(t.xs), L.ptr(t.xc), L.ptr(t.xa), t.x_taps, L.ptr(t.ys), L.ptr(t.yc),
+                                       L.ptr(t.ya), t.y_taps, L.ptr(t.xq), L.ptr(t.yq), t.ix, t.iy, gate_now, gate_expect,
+                                       L.stream_ptr(stream)), "resize_u8_indirect")
+
+
 def resize_u8(src: torch.Tensor, t: ResizeTables, dst: Optional[torch.Tensor] = None, dst_frame_stride: int = 0,
               stream=None, epoch_gate=None) -> torch.Tensor:
     """cv2 INTER_AREA on the device.  ``epoch_gate=(epoch_now, epoch_expect)`` (two int32 device words) makes the

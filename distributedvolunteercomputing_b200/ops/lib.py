@@ -33,6 +33,27 @@ class DetParams(C.Structure):
                 ("app_conf", C.c_float), ("consider_mask", C.c_uint32), ("out_w", C.c_int), ("out_h", C.c_int)]
 
 
+class MbxDesc(C.Structure):
+    """dvc_mbx_desc (include/dvc_b200.h): one dispatch, written by the client, polled by the worker lane."""
+    _fields_ = [("seq", C.c_uint32), ("epoch", C.c_uint32), ("n_valid", C.c_uint32), ("kind", C.c_uint32),
+                ("src_off", C.c_uint64), ("batch_id", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class MbxLaneCtl(C.Structure):
+    """dvc_mbx_lane_ctl: worker-local control block of one lane (device memory)."""
+    _fields_ = [("src", C.c_void_p), ("gate_now", C.c_uint32), ("gate_expect", C.c_uint32), ("flag_value", C.c_uint32),
+                ("status", C.c_uint32), ("batch_id", C.c_uint32), ("n_valid", C.c_uint32), ("next_seq", C.c_uint32),
+                ("reserved", C.c_uint32)]
+
+
+class MbxHostStatus(C.Structure):
+    """dvc_mbx_host_status: what a wait kernel saw, in pinned host memory."""
+    _fields_ = [("status", C.c_uint32), ("seq", C.c_uint32), ("batch_id", C.c_uint32), ("n_valid", C.c_uint32),
+                ("wait_ns", C.c_uint64)]
+
+
+MBX_NOTHING, MBX_GO, MBX_STOP, MBX_SEQ_STOP, MBX_MAX_GROUP = 0, 1, 2, 0xFFFFFFFF, 16
+
 _P, _I, _LL, _F, _U32, _SZ = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint32, C.c_size_t
 
 _SIGS = {
@@ -77,6 +98,13 @@ _SIGS = {
     "dvc_epoch_broadcast": ([_P, _I, _U32, _P], _I),
     "dvc_push_multicast": ([_P, _P, _I, _SZ, _P], _I),
     "dvc_peer_read": ([_P, _SZ, _P, _P], _I),
+    "dvc_mbx_post": ([_P, _P, _I, _P], _I),
+    "dvc_mbx_wait_desc": ([_P, _U32, _P, _P, _P, _P, C.c_ulonglong, _P], _I),
+    "dvc_mbx_wait_done": ([_P, _P, _I, _P, C.c_ulonglong, _P], _I),
+    "dvc_mbx_dispatch": ([_P, _P, _SZ, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _SZ, _P, _P], _I),
+    "dvc_mbx_signal": ([_P, _U32, _P], _I),
+    "dvc_plan_set_mailbox": ([_P, _P, _P, _P, _P, _P], _I),
+    "dvc_resize_u8_indirect": ([_P, _LL, _I, _I, _I, _P, _LL, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _P, _P, _P], _I),
 }
 
 

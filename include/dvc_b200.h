@@ -240,6 +240,98 @@ int dvc_push_multicast(const void* src, void** d_dst_ptrs, int n, size_t bytes, 
 /* NVLink read-bandwidth probe (16-byte loads of a possibly remote buffer). */
 int dvc_peer_read(const void* src, size_t bytes, void* d_sink, void* stream);
 
+
+/* ---- Mailboxes: device-side flow control for the in-box data plane (csrc/mailbox.cu). --------------------------
+ * The reference's flow control is one blocking REQ/REP round trip per chunk through the server (`b'OK'`,
+ * server.py:62, worker.py:180) and its dispatch is server.py:77-91.  Here the requesting client's GPU owns, per
+ * (worker, lane), one 32-byte descriptor and one completion word; everything is written and polled by kernels
+ * with system-scope release / acquire, so no collective and no host round trip orders a step:
+ *
+ *   client  dvc_mbx_post       fills the descriptor, then st.release.sys(desc.seq)              (client-local memory)
+ *   worker  dvc_mbx_wait_desc  polls ld.acquire.sys(desc.seq) over NVLink until it equals the lane's next sequence
+ *                              number (bounded wait), then copies source pointer / epoch / sequence into the lane's
+ *                              local control block, which K1a, K1b and K9 of that lane read
+ *   worker  K1a                pulls the frames from the client's arena with peer loads (the scatter)
+ *   worker  K9                 pushes rows with peer stores; the last CTA of the batch does
+ *                              st.release.sys(done word = seq)                                    (the gather)
+ *   client  dvc_mbx_wait_done  polls ld.acquire.sys(done word) (client-local memory, bounded), then the stream goes
+ *                              on to the device->host copy of the rows; a time-out is reported, never a hang
+ *
+ * Reuse of a lane's arena slot and result slot needs no separate credit word: the next descriptor of the lane is
+ * posted only after the client has consumed the previous result, in stream order on the client.
+ * Every wait is bounded by a time-out measured with %globaltimer, so a dead peer cannot wedge a GPU. */
+typedef struct dvc_mbx_desc {
+  uint32_t seq;        /* written last with release.sys; 0xFFFFFFFF = stop serving this lane */
+  uint32_t epoch;      /* membership epoch of the worker slot the batch was dispatched under (K14) */
+  uint32_t n_valid;    /* frames of the batch that carry data (<= B) */
+  uint32_t kind;       /* 0: frames are in the client's arena at src_off (NVLink pull); 1: worker-local frames */
+  uint64_t src_off;    /* byte offset of the batch's first frame inside the arena */
+  uint32_t batch_id;
+  uint32_t reserved;
+} dvc_mbx_desc;
+
+/* Worker-local, per lane, device memory: written by dvc_mbx_wait_desc, read by that lane's kernels. */
+typedef struct dvc_mbx_lane_ctl {
+  const uint8_t* src;  /* where K1a reads this batch's raw frames */
+  uint32_t gate_now;   /* K1a / K1b run only when gate_now == gate_expect (nothing arrived: they differ) */
+  uint32_t gate_expect;/* K9 delivers only when the client's live epoch word still equals this */
+  uint32_t flag_value; /* the sequence number K9 publishes in the done word */
+  uint32_t status;     /* DVC_MBX_* below */
+  uint32_t batch_id;
+  uint32_t n_valid;
+  uint32_t next_seq;   /* the lane's position: the sequence number its next wait expects (advanced on every GO) */
+  uint32_t reserved;
+} dvc_mbx_lane_ctl;
+
+/* Host-visible (pinned, mapped) mirror of what a wait saw; `wait_ns` is how long the kernel polled. */
+typedef struct dvc_mbx_host_status {
+  uint32_t status, seq, batch_id, n_valid;
+  unsigned long long wait_ns;
+} dvc_mbx_host_status;
+
+#define DVC_MBX_NOTHING 0u   /* the wait timed out */
+#define DVC_MBX_GO 1u
+#define DVC_MBX_STOP 2u
+#define DVC_MBX_SEQ_STOP 0xFFFFFFFFu
+#define DVC_MBX_MAX_GROUP 16
+
+/* Client: publish n descriptors (n <= DVC_MBX_MAX_GROUP).  h_desc_ptrs[i] is the device address of descriptor i
+ * (client-local); h_descs[i] its new contents (seq included).  Host arrays, copied into the launch. */
+int dvc_mbx_post(void* const* h_desc_ptrs, const dvc_mbx_desc* h_descs, int n, void* stream);
+/* Worker: wait (at most timeout_ns) until desc->seq == expect_seq (0: use and advance ctl->next_seq, so several
+ * waits can be queued ahead of their batches) or == DVC_MBX_SEQ_STOP, then fill *ctl and
+ * *h_status.  `desc` usually is a peer address on the client GPU; `arena_base` is the worker's
+ * mapping of the arena, `local_src` the worker's own frame buffer (kind 1).  h_status is pinned mapped host memory
+ * (device-accessible address) or NULL. */
+int dvc_mbx_wait_desc(const dvc_mbx_desc* desc, uint32_t expect_seq, const uint8_t* arena_base, const uint8_t* local_src,
+                      dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* h_status, unsigned long long timeout_ns, void* stream);
+/* Client: wait (at most timeout_ns) until *done_ptrs[i] == seqs[i] for every i < n; h_status[i].status = GO or
+ * NOTHING (timed out).  h_status is pinned mapped host memory, one entry per waited word. */
+int dvc_mbx_wait_done(void* const* h_done_ptrs, const uint32_t* h_seqs, int n, dvc_mbx_host_status* h_status,
+                      unsigned long long timeout_ns, void* stream);
+/* Client, one call per dispatch to a remote worker, all on `stream`: optional host->device copy of the frames into
+ * the arena, dvc_mbx_post of one descriptor, dvc_mbx_wait_done on its done word, optional device->host copy of the
+ * result slot, optional cudaEventRecord(event).  Pointers that are NULL switch their step off. */
+int dvc_mbx_dispatch(const void* h_src, void* d_dst, size_t src_bytes, void* desc_ptr, const dvc_mbx_desc* h_desc,
+                     void* done_ptr, dvc_mbx_host_status* h_status, unsigned long long timeout_ns,
+                     const void* d_result, void* h_result, size_t result_bytes, void* event, void* stream);
+/* st.release.sys of one word (epoch bump, hand-rolled completion after an extra copy). */
+int dvc_mbx_signal(uint32_t* word, uint32_t value, void* stream);
+/* Bind a plan to a lane: K1b's gate reads ctl->gate_now / gate_expect, K9 takes its flag value from ctl->flag_value,
+ * compares *live_epoch (the client's word for this worker, a peer address) with ctl->gate_expect, counts rejected
+ * frames in *stale_count and lets the last CTA of the batch publish *done_word = flag value.  `done_counter` is one
+ * zero-initialised device word owned by the lane. */
+int dvc_plan_set_mailbox(dvc_plan*, const dvc_mbx_lane_ctl* ctl, const uint32_t* live_epoch, uint32_t* done_word,
+                         uint32_t* done_counter, uint32_t* stale_count);
+/* K1a whose source base pointer is read from device memory at run time (`*src_indirect`, e.g. &ctl->src) and which is
+ * gated like dvc_resize_u8_gated. */
+int dvc_resize_u8_indirect(const uint8_t* const* src_indirect, long long src_frame_stride, int B, int sh, int sw,
+                           uint8_t* dst, long long dst_frame_stride, int dh, int dw, int mode,
+                           const int* xs, const int* xc, const float* xa, int x_taps,
+                           const int* ys, const int* yc, const float* ya, int y_taps,
+                           const int* xq, const int* yq, int ix, int iy,
+                           const uint32_t* epoch_now, const uint32_t* epoch_expect, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
