@@ -152,7 +152,11 @@ class Scheduler:
         self._ids = itertools.count(1)
         self.queues: "collections.OrderedDict[str, Deque[Batch]]" = collections.OrderedDict()
         self.inflight: Dict[int, InFlight] = {}
-        self.done: Dict[str, set] = collections.defaultdict(set)      # requester -> completed batch ids
+        # requester -> number of completed batches (a counter, not a set of ids: `request live` never ends)
+        self.done: Dict[str, int] = collections.defaultdict(int)
+        # batches given up after max_attempts; `on_drop(batch)` (optional) lets the owner fail the job or deliver a gap
+        self.dropped: "collections.deque[Batch]" = collections.deque(maxlen=1024)
+        self.on_drop: Optional[Callable[[Batch], None]] = None
         self._rr = 0            # the reference's single global round-robin counter (server.py:78,89-90)
         self._last_req = None   # requester rotation for fair share
         self.stats = collections.Counter()
@@ -283,7 +287,7 @@ class Scheduler:
                     for b in q:
                         if b.batch_id == batch_id:
                             q.remove(b)
-                            self.done[b.requester].add(batch_id)
+                            self.done[b.requester] += 1
                             self.stats["completed"] += 1
                             self.stats["late_results"] += 1
                             self.cv.notify_all()
@@ -300,10 +304,29 @@ class Scheduler:
                 w.inflight = max(0, w.inflight - 1)
                 w.completed += 1
                 w.last_seen = self.clock()
-            self.done[f.batch.requester].add(batch_id)
+            self.done[f.batch.requester] += 1
             self.stats["completed"] += 1
             self.cv.notify_all()
             return f.batch
+
+    def undo_dispatch(self, batch_id: int) -> Optional[Batch]:
+        """The dispatcher could not hand the batch over after all (no free lane / buffer yet): back to the FRONT of its
+        queue, the worker's credit is returned and the attempt is not counted."""
+        with self.cv:
+            f = self.inflight.pop(batch_id, None)
+            if f is None:
+                return None
+            w = self.members.workers.get(f.worker)
+            if w is not None:
+                w.inflight = max(0, w.inflight - 1)
+            f.batch.attempts = max(0, f.batch.attempts - 1)
+            self.queues.setdefault(f.batch.requester, collections.deque()).appendleft(f.batch)
+            self.stats["undone"] += 1
+            return f.batch
+
+    def touch(self, addr: str):
+        """The worker has just shown a sign of life (e.g. acknowledged a dispatch)."""
+        self.members.touch(addr, now=self.clock())
 
     def fail(self, batch_id: int, reason: str = "error") -> Optional[Batch]:
         """Explicit failure report (e.g. a send timed out): re-queue at the front."""
@@ -332,6 +355,7 @@ class Scheduler:
             hit = [f for f in self.inflight.values() if pred(f)]
             hit.sort(key=lambda f: f.batch.batch_id, reverse=True)   # appendleft in reverse keeps FIFO order
             out = []
+            dropped: List[Batch] = []
             for f in hit:
                 del self.inflight[f.batch.batch_id]
                 w = self.members.workers.get(f.worker)
@@ -339,6 +363,7 @@ class Scheduler:
                     w.inflight = max(0, w.inflight - 1)
                 if f.batch.attempts >= self.max_attempts:
                     self.stats["dropped_after_max_attempts"] += 1
+                    dropped.append(f.batch)
                     continue
                 self.queues.setdefault(f.batch.requester, collections.deque()).appendleft(f.batch)
                 self.stats["redispatched"] += 1
@@ -346,7 +371,14 @@ class Scheduler:
                 out.append(f.batch)
             if out:
                 self.cv.notify_all()
-            return list(reversed(out))
+        for b in dropped:                     # outside the lock: the callback may call back into the scheduler
+            self.dropped.append(b)
+            if self.on_drop is not None:
+                try:
+                    self.on_drop(b)
+                except Exception:
+                    self.stats["on_drop_errors"] += 1
+        return list(reversed(out))
 
     def drop_requester(self, requester: str):
         with self.lock:
