@@ -153,6 +153,7 @@ class WorkerLanes:
             torch.cuda.synchronize(self.dev)
         self.served = 0
         self.idle_polls = 0
+        self.busy_ms = 0.0
 
     # ------------------------------------------------------------------ addresses
     def ctl_ptr(self, l: int) -> int:
@@ -230,6 +231,7 @@ class WorkerLanes:
         stopping = False
         fed = 0
         served0 = self.served
+        self._first_ev = self._last_ev = None
 
         def push(l: int, kind: str):
             nonlocal fed
@@ -243,9 +245,12 @@ class WorkerLanes:
                             src.reshape(lay.B, -1), non_blocking=True)
                     self.hs[idx]["status"] = 0xFFFF
                     self.enqueue_wait(l, idx, 0, stream_timeout_s if kind == "full" else probe_timeout_s)
+                if kind == "body" and self._first_ev is None:
+                    self._first_ev = torch.cuda.Event(enable_timing=True)      # the first real batch of this serve() starts here
+                    self._first_ev.record()
                 if kind != "probe":
                     self.enqueue_body(l)
-                ev = torch.cuda.Event()
+                ev = torch.cuda.Event(enable_timing=True)
                 ev.record()
             queues[l].append((kind, idx, ev))
 
@@ -262,10 +267,11 @@ class WorkerLanes:
                 for l in range(nl):
                     q = queues[l]
                     while q and q[0][2].query():
-                        kind, idx, _ = q.popleft()
+                        kind, idx, ev_done = q.popleft()
                         progressed = True
                         if kind == "body":
                             self.served += 1
+                            self._last_ev = ev_done
                             continue
                         status = int(self.hs[idx]["status"])
                         free_hs[l].append(idx)
@@ -277,6 +283,7 @@ class WorkerLanes:
                                 need_body[l] = True          # the probe consumed the descriptor: run its batch now
                             else:
                                 self.served += 1
+                                self._last_ev = ev_done
                         else:
                             mode[l] = "idle"
                             self.idle_polls += 1
@@ -297,6 +304,8 @@ class WorkerLanes:
                 if not progressed:
                     time.sleep(idle_sleep_s if all(m == "idle" for m in mode) else 0.00002)
             torch.cuda.synchronize(dev)
+            # device time from the start of the first batch served to the end of the last one (CUDA events on this GPU)
+            self.busy_ms = self._first_ev.elapsed_time(self._last_ev) if self._first_ev is not None and self._last_ev is not None else 0.0
         return self.served - served0
 
 
@@ -416,6 +425,8 @@ class ClientBox:
         with torch.cuda.device(self.dev):
             L.set_device(self.dev)
             if loc is None:
+                if kind == 1:
+                    host_src = None           # the worker uploads its own shard
                 src_ptr, src_bytes = (host_src.data_ptr(), host_src.numel()) if host_src is not None else (None, 0)
                 if host_src is not None:
                     assert lay.raw_stride == lay.H * lay.W * 3, "host upload needs a dense frame pitch"
@@ -427,7 +438,10 @@ class ClientBox:
                 # the client's own GPU works too: same kernels, same words, queued inline on the same stream (a wait
                 # never spins on something a later launch of this GPU has to produce)
                 with torch.cuda.stream(stream):
-                    if host_src is not None:
+                    if host_src is not None and kind == 1:
+                        loc.local_raw[lane].view(lay.B, lay.raw_stride)[:, : lay.H * lay.W * 3].copy_(
+                            host_src.reshape(lay.B, -1), non_blocking=True)
+                    elif host_src is not None:
                         self.slot_tensor(slot).copy_(host_src, non_blocking=True)
                     ptrs = (C.c_void_p * 1)(lay.desc_addr(cp, worker, lane))
                     L.check(self.lib.dvc_mbx_post(ptrs, C.byref(desc), 1, stream.cuda_stream), "mbx_post")
@@ -588,6 +602,12 @@ class ElasticBox:
         """Frames already resident in arena slot `slot` (decoded or produced on the client GPU)."""
         return self.sched.submit(requester or self.requester, frame_ids, payload={"slot": slot, "host": None, "keep": keep_slot})
 
+    def submit_local(self, frame_ids: Sequence[int], host: Optional[torch.Tensor] = None, requester: Optional[str] = None) -> Batch:
+        """Sharded ingest: the frames are (or will be) in the WORKER's own memory - every worker process uploads its
+        own shard over its own PCIe link (`WorkerLanes.serve(local_feed=...)`); the descriptor (kind 1) only carries
+        the permission to deliver.  `host` is what the client's own GPU uploads when the batch lands on it."""
+        return self.sched.submit(requester or self.requester, frame_ids, payload={"slot": 0, "host": host, "keep": True, "kind": 1})
+
     def submit_host(self, frames: torch.Tensor, frame_ids: Sequence[int], requester: Optional[str] = None) -> Batch:
         """A pinned host batch [B, H, W, 3]; it is uploaded into an arena slot on the stream of the lane it goes to."""
         return self.sched.submit(requester or self.requester, frame_ids, payload={"slot": None, "host": frames, "keep": False})
@@ -643,7 +663,8 @@ class ElasticBox:
                         break
                 # a re-dispatched batch is uploaded again on ITS lane's stream: the first upload was ordered on another
                 host = pl["host"]
-            self.client.dispatch(w, lane, pl["slot"], len(batch.frame_ids), batch.batch_id, host_src=host, fetch=self.fetch)
+            self.client.dispatch(w, lane, pl["slot"], len(batch.frame_ids), batch.batch_id, kind=pl.get("kind", 0),
+                                 host_src=host, fetch=self.fetch)
             self.flights[(w, lane)] = _Flight(batch, w, lane, pl["slot"], time.monotonic())
             self.stats["dispatched"] += 1
         return done
