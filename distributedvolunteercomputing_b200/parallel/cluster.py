@@ -75,7 +75,7 @@ class BoxCluster:
         with torch.cuda.device(self.dev):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            n = self.lanes.serve(local_feed=local_feed)
+            n = self.lanes.serve(local_feed=local_feed, expect_work=True)
             b.record()
             b.synchronize()
             self.serve_ms = a.elapsed_time(b)

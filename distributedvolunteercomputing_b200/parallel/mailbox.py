@@ -212,21 +212,22 @@ class WorkerLanes:
 
     def serve(self, should_stop: Callable[[], bool] = lambda: False, max_batches: Optional[int] = None,
               stream_timeout_s: float = 0.003, probe_timeout_s: float = 0.0005, idle_sleep_s: float = 0.0002,
-              local_feed: Optional[Callable[[int], torch.Tensor]] = None) -> int:
+              local_feed: Optional[Callable[[int], torch.Tensor]] = None, expect_work: bool = False) -> int:
         """Serve dispatches until the client posts stop, `should_stop()` turns true or `max_batches` were served.
 
         While batches keep arriving every lane has `depth` (wait + network) pairs queued on its stream, so the GPU never
         waits for this loop; the sequence position lives in the lane's control block on the device.  When a wait times
         out the lane falls back to short probes (a wait kernel alone) so an idle worker does no useless work.
         `local_feed(i)` (optional, sharded ingest) returns the pinned host batch this worker uploads itself before the
-        i-th queued batch; the client's descriptor (kind 1) is then only the permission to deliver."""
+        i-th queued batch; the client's descriptor (kind 1) is then only the permission to deliver.
+        `expect_work` starts the lanes in streaming mode (a phase the client opens with a full queue)."""
         if not self.sync_position():
             return 0
         lay, dev = self.layout, self.dev
         nl = lay.lanes
         queues: List[Deque[Tuple[str, int, torch.cuda.Event]]] = [collections.deque() for _ in range(nl)]
         free_hs: List[List[int]] = [list(range(l * 4, l * 4 + 4)) for l in range(nl)]
-        mode = ["idle"] * nl
+        mode = ["stream" if expect_work else "idle"] * nl      # expect_work: the client dispatches at once, skip the probes
         need_body = [False] * nl
         stopping = False
         fed = 0
@@ -245,7 +246,7 @@ class WorkerLanes:
                             src.reshape(lay.B, -1), non_blocking=True)
                     self.hs[idx]["status"] = 0xFFFF
                     self.enqueue_wait(l, idx, 0, stream_timeout_s if kind == "full" else probe_timeout_s)
-                if kind == "body" and self._first_ev is None:
+                if kind != "probe" and self._first_ev is None:      # after the wait, before the batch's first kernel
                     self._first_ev = torch.cuda.Event(enable_timing=True)      # the first real batch of this serve() starts here
                     self._first_ev.record()
                 if kind != "probe":
@@ -287,6 +288,8 @@ class WorkerLanes:
                         else:
                             mode[l] = "idle"
                             self.idle_polls += 1
+                            if self._last_ev is None:
+                                self._first_ev = None        # nothing served yet: the busy span has not started
                     if need_body[l]:
                         push(l, "body")
                         need_body[l] = False

@@ -46,6 +46,24 @@ def main():
     pool = [torch.from_numpy(rng.integers(0, 256, (B, H, W, 3), dtype=np.uint8)).pin_memory() for _ in range(6)]
     refs = [eng.process(f).numpy() for f in pool]
 
+    def retire(w):
+        """Reap worker process w (it may already have returned from serve() and be gone): its last message, if any."""
+        p, conn = box.procs.pop(w)
+        try:
+            conn.send("stop")
+        except (BrokenPipeError, OSError):
+            pass
+        msg = None
+        try:
+            while conn.poll(20.0 if msg is None else 0.0):
+                msg = conn.recv()
+        except (EOFError, OSError):
+            pass
+        p.join(30.0)
+        if p.is_alive():
+            p.kill()
+        return msg
+
     def check(ids, what):
         per = {}
         for k, bid in enumerate(ids):
@@ -75,10 +93,7 @@ def main():
         box.remove_worker(victim, reason="leave", stop=True)
         assert box.drain(60.0), box.stats
         check(ids, "leave")
-        p, conn = box.procs.pop(victim)
-        conn.send("stop")
-        msg = conn.recv() if conn.poll(30.0) else None
-        p.join(30.0)
+        msg = retire(victim)
         stale_seen = msg[2] if msg else -1
         box.spawn_worker(victim, victim, graph, cfg)
         if stale_seen > 0:
@@ -88,9 +103,8 @@ def main():
 
     # ---- 3. silent worker (stalls after 3 batches): bounded wait -> time-out -> re-dispatch
     victim = 1
-    p, conn = box.procs.pop(victim)
     box.remove_worker(victim)
-    conn.send("stop"); p.join(30.0)
+    retire(victim)
     box.spawn_worker(victim, victim, graph, cfg, stall_after=3)
     f0 = len(box.failed_workers)
     ids = [box.submit_host(pool[k % len(pool)], range(B)).batch_id for k in range(16 * n)]
@@ -100,8 +114,7 @@ def main():
     assert box.failed_workers[f0:] == [victim], box.failed_workers
     print(f"mailbox check ok: silent worker gpu{victim} found by the device-side time-out after {time.monotonic() - t0:.2f} s, "
           f"{box.stats['redispatched']} batches re-dispatched so far", flush=True)
-    p, conn = box.procs.pop(victim)
-    conn.send("stop"); p.join(30.0)
+    retire(victim)
     box.spawn_worker(victim, victim, graph, cfg)
 
     # ---- 4. SIGKILL mid-stream
