@@ -100,11 +100,19 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
         self.ready.set()
         try:
             while self.running:
-                got = hub.recv_image(timeout_s=0.25)
-                if got is None:
+                # a message that cannot be decoded is answered and skipped; it must not end this thread (the server
+                # blocks on the reply, and every later chunk would be lost)
+                try:
+                    got = hub.recv_image(timeout_s=0.25)
+                    if got is None:
+                        continue
+                    info, frame = got
+                    hdr = proto.parse_header(info)
+                except ValueError as e:           # proto.BadMessage included
+                    self.metrics.inc("bad_messages")
+                    self.log(f"undecodable message skipped: {e}")
+                    hub.send_reply(b"OK")
                     continue
-                info, frame = got
-                hdr = proto.parse_header(info)
                 item = (hdr, np.array(frame, copy=True))
                 hub.send_reply(b"OK")
                 while self.running:
@@ -152,6 +160,13 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
             try:
                 hdr, img = self.recv_q.get(timeout=0.25)
             except queue.Empty:
+                continue
+            if hdr.cmd == "dropped":
+                # the server gave these frames up (no worker could finish them): the writer must not wait for them
+                if hdr.requester == self.my_ip and self.tracker is not None:
+                    print(f"[WARN] {len(hdr.frames)} frame(s) lost by the pool: {hdr.frames[:5]}...", flush=True)
+                    for n in hdr.frames:
+                        self.tracker.skip(n)
                 continue
             frames = proto.unpack_chunk(img, len(hdr.frames), hdr.height, hdr.width)
             if hdr.cmd == "processed":
@@ -226,12 +241,19 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
             if not self.continue_requesting:
                 break
             if not started:
-                sink = VideoSink(self.cfg, frame.shape[0], frame.shape[1], self.out_dir, self.path_out_num)
-                jpath = sink.path + ".journal"
-                skip_to = JobJournal.load(jpath) if getattr(self, "_resume", False) else 0
+                # resume: only a journal of an UNFINISHED job on the SAME source counts; the tail then goes to a new
+                # segment file (video<N>.part<k>.mp4) so the frames written before the interruption are kept
+                jpath = os.path.join(self.out_dir, f"video{self.path_out_num}.mp4.journal")
+                source = os.path.abspath(path) if os.path.exists(path) else path
+                state = JobJournal.load_state(jpath) if getattr(self, "_resume", False) else {}
+                if state.get("finished") or state.get("source") != source:
+                    state = {}
+                skip_to = int(state.get("last_contiguous_frame", 0))
+                segment = int(state.get("segment", 0)) + 1 if skip_to > 0 else 0
+                sink = VideoSink(self.cfg, frame.shape[0], frame.shape[1], self.out_dir, self.path_out_num, segment=segment)
                 self.path_out_num += 1
                 self.tracker = JobTracker(sink, first_frame=skip_to + 1, out=lambda m: print(m, flush=True),
-                                          journal=JobJournal(jpath))
+                                          journal=JobJournal(jpath, source=source, segment=segment))
                 started = True
             frame_number += 1
             if frame_number <= skip_to:          # already written by the interrupted run (journal)

@@ -37,6 +37,7 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
         self.metrics = Metrics(self.cfg.metrics_jsonl)
         self.sched = Scheduler(policy=self.cfg.dispatch_policy, requester_works=False,
                                worker_timeout_s=self.cfg.worker_timeout_s)
+        self.sched.on_drop = self._on_drop          # a chunk given up after max_attempts is reported, not lost silently
         self.lock = threading.RLock()
         self.running = False
         self.free_ports: List[int] = list(range(self.cfg.data_port_lo, self.cfg.data_port_hi + 1))
@@ -190,14 +191,38 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
             if ev:
                 ev.set()
             s = self.senders.pop(address, None)
-            if s:
-                s.close()
-            self.sender_locks.pop(address, None)
+            slock = self.sender_locks.pop(address, None)
             self.outbox.pop(address, None)
             self.results.pop(address, None)
+        if s is not None:
+            # ZeroMQ sockets are not thread-safe: worker_sender / send_reply may be inside send_image on this one, so it
+            # is closed under the same lock they hold (outside self.lock: a send may take its full time-out)
+            if slock is not None:
+                with slock:
+                    s.close()
+            else:
+                s.close()
         if address in self.frame_owner:
             self.sched.drop_requester(address)
-            self.frame_owner.pop(address, None)
+            with self.lock:
+                owner = self.frame_owner.pop(address, None) or {}
+                for bid in set(owner.values()):
+                    self.missing.pop(bid, None)
+
+    def _on_drop(self, batch):
+        """The scheduler gave a chunk up (max_attempts): tell the requester which frames will never come, so its
+        in-order writer can move on instead of waiting for ever, and forget the chunk."""
+        self.metrics.inc("dropped_chunks")
+        self.log(f"chunk {batch.batch_id} of {batch.requester} dropped after {batch.attempts} attempts: frames {batch.frame_ids[:3]}...")
+        with self.lock:
+            self.missing.pop(batch.batch_id, None)
+            owner = self.frame_owner.get(batch.requester, {})
+            for n in batch.frame_ids:
+                owner.pop(n, None)
+            q = self.results.get(batch.requester)
+        if q is not None:
+            gap = proto.Header(batch.requester, "dropped", tuple(batch.frame_ids), 1, 1)
+            q.put((gap.encode(), np.zeros((1, len(batch.frame_ids), 3), np.uint8)))
 
     # ------------------------------------------------------------------ data plane: ingest
     def server(self, ip: str, port: int, address: str, stop: threading.Event):
@@ -205,13 +230,24 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
         hub = proto.ImageHub("tcp://*:" + str(port))
         try:
             while self.running and not stop.is_set():
-                got = hub.recv_image(timeout_s=0.25)
+                # one bad message (undecodable JSON / shape, malformed header) must not end this client's ingest thread:
+                # log it, count it, answer it (the peer blocks on the reply) and keep serving
+                try:
+                    got = hub.recv_image(timeout_s=0.25)
+                except proto.BadMessage as e:
+                    self.metrics.inc("bad_messages")
+                    self.log(f"{address}: {e}")
+                    hub.send_reply(b"OK")
+                    continue
                 if got is None:
                     continue
                 info, frame = got
                 self.log(info)
                 try:
                     self._on_chunk(info, frame, address)
+                except Exception as e:
+                    self.metrics.inc("bad_messages")
+                    self.log(f"{address}: chunk {info[:80]!r} rejected: {e!r}")
                 finally:
                     hub.send_reply(b"OK")
         finally:
@@ -250,6 +286,8 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
                         if not miss:
                             finished.append(bid)
                             del self.missing[bid]
+                    if miss is None or n not in miss:
+                        owner.pop(n, None)          # delivered: the table holds in-flight frames only (`request live`)
                 q = self.results.get(hdr.requester)
             for bid in finished:
                 self.sched.complete(bid, sender_addr)

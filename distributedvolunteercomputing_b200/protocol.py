@@ -23,7 +23,7 @@ import numpy as np
 
 SEP = "||"
 CONTROL_COMMANDS = ("join", "request", "stop", "end")   # matched by substring, in this order (server.py:104-141)
-DATA_COMMANDS = ("request", "processed")
+DATA_COMMANDS = ("request", "processed", "dropped")   # "dropped": gap marker, server -> requester (not in the reference)
 
 
 # ------------------------------------------------------------------------------ control plane
@@ -139,6 +139,10 @@ class ImageSender:
             pass
 
 
+class BadMessage(ValueError):
+    """A message that cannot be decoded (bad JSON, dtype, shape or header).  The hub may - and must - still reply."""
+
+
 class ImageHub:
     """imagezmq.ImageHub(open_port, REQ_REP=True) equivalent; recv_image takes a timeout."""
 
@@ -155,10 +159,16 @@ class ImageHub:
         zmq = self._zmq
         if timeout_s is not None and not self.sock.poll(int(timeout_s * 1000), zmq.POLLIN):
             return None
-        md = self.sock.recv_json()
-        data = self.sock.recv(copy=False)
-        img = np.frombuffer(data, dtype=md["dtype"]).reshape(md["shape"])
-        return md["msg"], img
+        # take the whole message off the socket first: a REP socket that has received must reply before it can receive
+        # again, so a malformed message has to leave us in the "may reply" state, not half-read
+        parts = self.sock.recv_multipart(copy=False)
+        try:
+            import json
+            md = json.loads(bytes(parts[0].buffer))
+            img = np.frombuffer(parts[1].buffer, dtype=md["dtype"]).reshape(md["shape"])
+            return md["msg"], img
+        except Exception as e:
+            raise BadMessage(f"malformed imagezmq message ({len(parts)} part(s)): {e!r}") from e
 
     def send_reply(self, reply: bytes = b"OK"):
         self.sock.send(reply)

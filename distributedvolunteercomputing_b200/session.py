@@ -101,11 +101,13 @@ class VideoSink:
 
     _counter = 0
 
-    def __init__(self, cfg: Config, src_h: int, src_w: int, directory: str = ".", index: Optional[int] = None):
+    def __init__(self, cfg: Config, src_h: int, src_w: int, directory: str = ".", index: Optional[int] = None,
+                 segment: int = 0):
         if index is None:
             index = VideoSink._counter
             VideoSink._counter += 1
-        self.path = os.path.join(directory, f"video{index}.mp4")
+        # segment > 0: the tail of a resumed job; earlier segments (video<N>.mp4, .part1.mp4, ...) are left alone
+        self.path = os.path.join(directory, f"video{index}.mp4" if segment == 0 else f"video{index}.part{segment}.mp4")
         self.h, self.w = out_size_400(src_h, src_w, cfg.out_width)
         self.writer = cv2.VideoWriter(self.path, cv2.VideoWriter_fourcc(*"mp4v"), cfg.writer_fps, (self.w, self.h))
         self.frames_written = 0
@@ -125,21 +127,30 @@ class JobJournal:
     with the last frame number that has been written contiguously.  A restarted requester skips those
     frames (`client.become_requester(path, resume=True)`), so only the unwritten tail is re-sent."""
 
-    def __init__(self, path: str, every: int = 32):
+    def __init__(self, path: str, every: int = 32, source: Optional[str] = None, segment: int = 0):
         self.path = path
         self.every = max(1, every)
+        self.source = source          # what was being processed: a journal is only good for resuming the same source
+        self.segment = segment        # which output segment the job is writing (0 = video<N>.mp4)
         self._since = 0
 
     @staticmethod
-    def load(path: str) -> int:
+    def load_state(path: str) -> dict:
         try:
             with open(path) as f:
                 import json
-                return int(json.loads(f.read().strip() or "{}").get("last_contiguous_frame", 0))
+                d = json.loads(f.read().strip() or "{}")
+                return d if isinstance(d, dict) else {}
         except (OSError, ValueError):
-            return 0
+            return {}
 
-    def record(self, last_frame: int, force: bool = False):
+    @staticmethod
+    def load(path: str) -> int:
+        """Last contiguous frame of an unfinished job, 0 otherwise."""
+        d = JobJournal.load_state(path)
+        return 0 if d.get("finished") else int(d.get("last_contiguous_frame", 0))
+
+    def record(self, last_frame: int, force: bool = False, finished: bool = False):
         self._since += 1
         if not force and self._since < self.every:
             return
@@ -147,7 +158,8 @@ class JobJournal:
         import json
         tmp = self.path + ".tmp"
         with open(tmp, "w") as f:
-            f.write(json.dumps({"last_contiguous_frame": int(last_frame), "t": time.time()}))
+            f.write(json.dumps({"last_contiguous_frame": int(last_frame), "t": time.time(), "source": self.source,
+                                "segment": self.segment, "finished": bool(finished)}))
         os.replace(tmp, self.path)
 
 
@@ -165,14 +177,21 @@ class JobTracker:
         self.job_seconds: Optional[float] = None
         self.out = out
         self.counts: List[int] = []
+        self.lost = 0
+        self._finishing = False
 
     def set_final(self, n: int):
         self.final_sent_frame = n
         self._maybe_finish()
 
-    def push(self, n: int, frame: np.ndarray, count: Optional[int] = None):
+    def skip(self, n: int):
+        """Frame n will never arrive (the pool gave it up): let the in-order writer pass over it."""
+        self.lost += 1
+        self.push(n, None)
+
+    def push(self, n: int, frame: Optional[np.ndarray], count: Optional[int] = None):
         for k, item in self.reorder.push(n, (frame, count)):
-            if self.sink is not None:
+            if self.sink is not None and item[0] is not None:
                 self.sink.write(item[0])
             if item[1] is not None:
                 self.counts.append(item[1])
@@ -183,11 +202,12 @@ class JobTracker:
     def _maybe_finish(self):
         if self.finished or self.final_sent_frame is None:
             return
-        if self.reorder.next - 1 >= self.final_sent_frame:
-            self.finished = True
+        if self.reorder.next - 1 >= self.final_sent_frame and not self._finishing:
+            self._finishing = True
             self.job_seconds = time.time() - self.start_time
             self.out("final frame time taken for the job = " + str(self.job_seconds))
-            if self.journal is not None:
-                self.journal.record(self.reorder.next - 1, force=True)
             if self.sink is not None:
                 self.sink.release()
+            if self.journal is not None:
+                self.journal.record(self.reorder.next - 1, force=True, finished=True)
+            self.finished = True          # last: whoever waits on it finds the output file closed and the journal final

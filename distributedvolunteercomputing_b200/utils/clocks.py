@@ -110,8 +110,15 @@ class ClockSampler:
         self._t.start()
         return self
 
+    def mark(self) -> "ClockSampler":
+        """Samples taken before this call are ignored by stop(): start the sampler early (its start-up cost stays out
+        of the timed region), mark right before the region."""
+        self._mark = len(self._nvml_samples) if self.backend == "nvml" else len(self.lines)
+        return self
+
     def stop(self) -> Dict:
         if self.backend == "nvml":
+            self._nvml_samples = self._nvml_samples[getattr(self, "_mark", 0):] if not self._stop.is_set() else self._nvml_samples
             return self._stop_nvml()
         if self.proc is not None:
             self.proc.terminate()
@@ -124,7 +131,7 @@ class ClockSampler:
         sm, mx = [], []
         reasons = set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in self.lines[getattr(self, "_mark", 0):]:
             parts = [p.strip() for p in ln.split(",")]
             if len(parts) < 9:
                 continue

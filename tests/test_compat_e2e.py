@@ -199,11 +199,86 @@ def test_job_journal_and_resume(tmp_path):
     for n in (2, 1, 3, 4, 5):
         tr.push(n, np.zeros((2, 2, 3), np.uint8))
     assert JobJournal.load(j.path) in (4, 5)          # flushed every 4 contiguous frames
-    tr.set_final(5)
-    assert tr.finished and JobJournal.load(j.path) == 5
     tr2 = JobTracker(None, first_frame=JobJournal.load(j.path) + 1, out=lambda m: None)
-    assert tr2.reorder.next == 6
+    assert tr2.reorder.next in (5, 6)
+    tr.set_final(5)
+    st = JobJournal.load_state(j.path)
+    assert tr.finished and st["finished"] and st["last_contiguous_frame"] == 5
+    assert JobJournal.load(j.path) == 0, "the journal of a finished job must not make a later job skip frames"
     assert JobJournal.load(str(tmp_path / "missing.journal")) == 0
+    # a frame the pool gave up is passed over by the in-order writer
+    tr3 = JobTracker(None, first_frame=1, out=lambda m: None)
+    tr3.push(1, np.zeros((2, 2, 3), np.uint8)); tr3.push(3, np.zeros((2, 2, 3), np.uint8)); tr3.skip(2)
+    tr3.set_final(3)
+    assert tr3.finished and tr3.lost == 1
+
+
+def test_resume_keeps_the_head_and_writes_the_tail_to_a_new_segment(tmp_path):
+    """become_requester(resume=True) end to end with a real sink: the frames written before the interruption stay in
+    video0.mp4, the tail goes to video0.part1.mp4; a journal of a finished job or of another source is ignored."""
+    import json
+    port = _udp_port()
+    srv = coordinator("127.0.0.1", _cfg(port))
+    try:
+        video = write_synthetic_video(str(tmp_path / "in.mp4"), 20, 96, 128)
+        w = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        r = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        assert w.ready.wait(5) and r.ready.wait(5)
+        r.become_requester(video)
+        assert r.wait_job(30) is not None and _count_frames(str(tmp_path / "video0.mp4")) == 20
+        r.exit_threads()
+        jpath = str(tmp_path / "video0.mp4.journal")
+        assert json.load(open(jpath))["finished"] is True
+        # (a) finished journal: a resume of the same source starts over (nothing skipped)
+        r2 = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        assert r2.ready.wait(5)
+        r2.become_requester(video, resume=True)
+        assert r2.wait_job(30) is not None and _count_frames(str(tmp_path / "video0.mp4")) == 20
+        assert not (tmp_path / "video0.part1.mp4").exists()
+        r2.exit_threads()
+        # (b) interrupted after frame 8 of this source: the tail (12 frames) goes to a new segment, the head file is kept
+        json.dump({"last_contiguous_frame": 8, "source": str(tmp_path / "in.mp4"), "segment": 0, "finished": False}, open(jpath, "w"))
+        r3 = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        assert r3.ready.wait(5)
+        r3.become_requester(video, resume=True)
+        assert r3.wait_job(30) is not None
+        assert _count_frames(str(tmp_path / "video0.part1.mp4")) == 12 and _count_frames(str(tmp_path / "video0.mp4")) == 20
+        r3.exit_threads()
+        # (c) journal of another source: ignored
+        json.dump({"last_contiguous_frame": 8, "source": "/somewhere/else.mp4", "segment": 0, "finished": False}, open(jpath, "w"))
+        r4 = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        assert r4.ready.wait(5)
+        r4.become_requester(video, resume=True)
+        assert r4.wait_job(30) is not None and _count_frames(str(tmp_path / "video0.mp4")) == 20
+        r4.exit_threads(); w.exit_threads()
+    finally:
+        srv.exit_threads()
+
+
+def test_malformed_chunk_does_not_kill_the_ingest_thread(tmp_path):
+    """A bad header / undecodable message on a client's data port is answered and skipped; the next good job completes."""
+    port = _udp_port()
+    srv = coordinator("127.0.0.1", _cfg(port))
+    try:
+        video = write_synthetic_video(str(tmp_path / "in.mp4"), 12, 96, 128)
+        w = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        r = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        assert w.ready.wait(5) and r.ready.wait(5)
+        junk = np.zeros((2, 2, 3), np.uint8)
+        r.sender.send_image("not-a-header", junk)                       # malformed header -> coordinator ingest thread
+        r.sender.send_image("a||request||x-y||2||2", junk)              # unparsable frame numbers
+        r.sender.sock.send_multipart([b"{this is not json", b"\x00"])     # undecodable imagezmq message
+        assert r.sender.sock.recv() == b"OK"
+        # straight at the worker's own hub as well (client.recv_image_thread)
+        direct = proto.ImageSender("tcp://127.0.0.1:" + w.my_ip.split(":")[1])
+        direct.send_image("garbage", junk)
+        direct.close()
+        r.become_requester(video)
+        assert r.wait_job(30) is not None and _count_frames(str(tmp_path / "video0.mp4")) == 12
+        assert srv.metrics.counters["bad_messages"] >= 3 and w.metrics.counters["bad_messages"] >= 1
+        w.exit_threads(); r.exit_threads()
+    finally:
+        srv.exit_threads()
 
 
 def test_trace_span_records_metrics():
