@@ -150,34 +150,83 @@ class client:  # noqa: N801  (name kept from the reference's public surface)
         self.engine = create_engine(graph, self.cfg)
         print("[INFO] detecting: {}...".format(", ".join(self.cfg.consider)), flush=True)
 
+    def _handle_results_chunk(self, hdr, img) -> bool:
+        """`processed` / `dropped` chunks addressed to this client as a requester.  True if the chunk was one of those."""
+        if hdr.cmd == "dropped":
+            # the server gave these frames up (no worker could finish them): the writer must not wait for them
+            if hdr.requester == self.my_ip and self.tracker is not None:
+                print(f"[WARN] {len(hdr.frames)} frame(s) lost by the pool: {hdr.frames[:5]}...", flush=True)
+                for n in hdr.frames:
+                    self.tracker.skip(n)
+            return True
+        if hdr.cmd == "processed":
+            if hdr.requester != self.my_ip:
+                print("frame not mine.", flush=True)
+                return True
+            if self.tracker is not None:
+                for n, f in zip(hdr.frames, proto.unpack_chunk(img, len(hdr.frames), hdr.height, hdr.width)):
+                    self.tracker.push(n, f)
+                    self.log("processed frame : " + str(n))
+            return True
+        return False
+
+    def _worker_pipelined(self):
+        """GPU volunteers: chunks go through `NativeEngine.process_stream`, so the upload of chunk i+1, the kernels of
+        chunk i and the read-back of chunk i-1 overlap (the reference does one blocking net.forward() per frame,
+        worker.py:241-249).  An idle queue flushes the pipeline, so a stream's last chunk is answered at once."""
+        hdrs: List[proto.Header] = []
+        t_in: List[float] = []
+
+        def batches():
+            while self.running:
+                try:
+                    hdr, img = self.recv_q.get(timeout=0.02 if hdrs else 0.25)
+                except queue.Empty:
+                    yield None
+                    continue
+                if self._handle_results_chunk(hdr, img) or hdr.cmd != "request":
+                    continue
+                self.chunks_taken += 1
+                if self.cfg.inject_leave_after and self.chunks_taken > self.cfg.inject_leave_after:
+                    self._vanish()
+                    return
+                if self.cfg.inject_stall_after and self.chunks_taken > self.cfg.inject_stall_after:
+                    self.log("fault injection: chunk swallowed")
+                    continue
+                frames = proto.unpack_chunk(img, len(hdr.frames), hdr.height, hdr.width)
+                hdrs.append(hdr)
+                t_in.append(time.time())
+                yield (np.stack(frames), hdr.requester)
+
+        for res in self.engine.process_stream(batches(), depth=2, fetch_frames=True):
+            hdr = hdrs.pop(0)
+            self.metrics.observe("batch_ms", (time.time() - t_in.pop(0)) * 1e3)
+            self.metrics.inc("frames_processed", len(hdr.frames))
+            fr = res.frames400.numpy() if hasattr(res.frames400, "numpy") else res.frames400
+            out = [fr[i] for i in range(len(hdr.frames))]
+            h, w = out[0].shape[:2]
+            reply = proto.Header(hdr.requester, "processed", hdr.frames, h, w)
+            self._enqueue_send(reply.encode(), proto.pack_chunk(out))        # pack_chunk copies out of the pinned slot
+
     def worker(self):
         try:
             self._ensure_engine()
         except Exception as e:
             print(f"[ERROR] cannot load model: {e!r}", flush=True)
             self.engine = None
+        if self.engine is not None and hasattr(self.engine, "process_stream") and self.cfg.pipelined_worker:
+            self._worker_pipelined()
+            print("worker terminated.", flush=True)
+            return
         while self.running:
             try:
                 hdr, img = self.recv_q.get(timeout=0.25)
             except queue.Empty:
                 continue
-            if hdr.cmd == "dropped":
-                # the server gave these frames up (no worker could finish them): the writer must not wait for them
-                if hdr.requester == self.my_ip and self.tracker is not None:
-                    print(f"[WARN] {len(hdr.frames)} frame(s) lost by the pool: {hdr.frames[:5]}...", flush=True)
-                    for n in hdr.frames:
-                        self.tracker.skip(n)
+            if self._handle_results_chunk(hdr, img):
                 continue
             frames = proto.unpack_chunk(img, len(hdr.frames), hdr.height, hdr.width)
-            if hdr.cmd == "processed":
-                if hdr.requester != self.my_ip:
-                    print("frame not mine.", flush=True)
-                    continue
-                if self.tracker is not None:
-                    for n, f in zip(hdr.frames, frames):
-                        self.tracker.push(n, f)
-                        self.log("processed frame : " + str(n))
-            elif hdr.cmd == "request":
+            if hdr.cmd == "request":
                 if self.engine is None:
                     continue
                 self.chunks_taken += 1

@@ -47,6 +47,7 @@ class Config:
     worker_timeout_s: float = 10.0      # in-flight batches older than this are re-dispatched
     verbose: bool = False
     # ---- fault injection (the reference has none)
+    pipelined_worker: bool = True       # GPU volunteers overlap upload / kernels / read-back of consecutive chunks (process_stream)
     inject_stall_after: int = 0         # worker: after this many chunks, keep accepting chunks but never answer
     inject_leave_after: int = 0         # worker: after this many chunks, vanish without sending `end` (process death)
     # ---- B200 engine

@@ -333,6 +333,7 @@ class coordinator:  # noqa: N801  (name kept from the reference's public surface
             try:
                 with lock:
                     sender.send_image(info, frame)
+                self.sched.touch(address)          # the worker acknowledged the chunk: it is alive as of now
                 self.metrics.inc("chunks_dispatched")
             except TimeoutError:
                 self.log(f"worker {address} did not acknowledge a chunk: presuming it dead")

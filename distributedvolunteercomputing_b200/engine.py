@@ -515,7 +515,15 @@ class NativeEngine:
         host-side ``BatchResult`` per batch, in order.  ``depth`` independent slots (own buffers, plan, CUDA
         graph and compute stream each) plus a copy-in and a copy-out stream overlap the host->device copy of
         batch i+1, the kernels of batches i and i-1 (which share the SMs) and the device->host read of batch i-2.
-        ``fetch_frames`` also brings the annotated 400-wide frames back (large); detections always come back."""
+        ``fetch_frames`` also brings the annotated 400-wide frames back (large); detections always come back.
+
+        Lifetime: a yielded ``BatchResult`` is a view of its slot's pinned host buffers.  It is valid until the consumer
+        asks for the NEXT item - the slot is then re-used and an asynchronous copy overwrites it - so copy what must
+        outlive the iteration (``list(engine.process_stream(...))`` keeps aliases, not results).
+
+        Live sources: an item may be ``None`` ("nothing more for now"): everything in flight is then finished and
+        yielded before the generator is asked again, so the tail of a stream is not held back waiting for a batch that
+        may never come.  An item may also be ``(frames, requester_id)`` to overlay a per-batch requester id."""
         dev = self.device
         with torch.cuda.device(dev):
             s_in, s_out = (torch.cuda.Stream(device=dev) for _ in range(2))
@@ -528,14 +536,23 @@ class NativeEngine:
                 return BatchResult(rec["h_det"], rec["h_cnt"], rec["h_boxes"], rec["h_bcnt"],
                                    rec["h_frames"] if fetch_frames else None)
 
-            for i, batch in enumerate(batches):
+            i = -1
+            for batch in batches:
+                if batch is None:                       # live source has nothing right now: flush what is in flight
+                    while pending:
+                        yield finish(*pending.pop(0))
+                    continue
+                i += 1
+                rid = requester_id
+                if isinstance(batch, tuple):
+                    batch, rid = batch
                 t = batch if isinstance(batch, torch.Tensor) else torch.as_tensor(batch)
                 B, H, W, _ = t.shape
                 k = i % depth
-                key = (k, B, H, W)
+                key = (k, B, H, W, rid)
                 rec = slots.get(key)
                 if rec is None:
-                    st = self.state(B, H, W, requester_id, slot=1 + k)
+                    st = self.state(B, H, W, rid, slot=1 + k)
                     rec = {"st": st, "free": None,
                            "h_det": torch.empty((B, 100, 7), dtype=torch.float32).pin_memory(),
                            "h_cnt": torch.empty((B,), dtype=torch.int32).pin_memory(),

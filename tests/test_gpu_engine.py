@@ -133,6 +133,62 @@ def test_process_stream_matches_sync(engines):
             assert np.array_equal(a[2][k, : a[3][k]], b[2][k, : b[3][k]])
 
 
+def test_process_stream_flushes_on_none_and_takes_per_batch_ids(engines):
+    """A live source yields None when it has nothing: everything in flight must come out before the generator is asked
+    again (otherwise the last chunk of a stream would wait for a chunk that never comes)."""
+    nat, _ = engines
+    batches = [torch.from_numpy(_frames(4, 300, 300, seed=60 + i)).pin_memory() for i in range(3)]
+    seen = []
+
+    def live():
+        yield (batches[0], "10.0.0.1:5554")
+        yield None
+        assert len(seen) == 1, "the first batch was not flushed by None"
+        yield (batches[1], "10.0.0.2:5554")
+        yield (batches[2], "10.0.0.1:5554")
+        yield None
+        assert len(seen) == 3
+
+    for r in nat.process_stream(live(), depth=3, fetch_frames=True):
+        seen.append((r.det_count.numpy().copy(), r.frames400.numpy().copy()))
+    assert len(seen) == 3
+    ref = nat.process(batches[1], requester_id="10.0.0.2:5554").numpy()
+    assert np.array_equal(seen[1][0], ref.det_count) and np.array_equal(seen[1][1], ref.frames400)
+
+
+def test_network_volunteer_uses_the_pipelined_path(graph, tmp_path):
+    """server + a GPU volunteer (NativeEngine through process_stream) + a requester over loopback: every frame comes back."""
+    cv2 = pytest.importorskip("cv2")
+    pytest.importorskip("zmq")
+    import socket
+    from distributedvolunteercomputing_b200.client import client
+    from distributedvolunteercomputing_b200.coordinator import coordinator
+    from distributedvolunteercomputing_b200.session import write_synthetic_video
+    s = socket.socket(socket.AF_INET, socket.SOCK_DGRAM); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    cfg = lambda: Config(control_port=port, my_port=0, number_of_frames_in_chunk=8, control_retry_s=1.0, data_port_lo=0,
+                         data_port_hi=-1, worker_timeout_s=30.0, data_timeout_s=10.0)
+    srv = coordinator("127.0.0.1", cfg())
+    try:
+        video = write_synthetic_video(str(tmp_path / "in.mp4"), 28, 120, 160)
+        eng = NativeEngine(graph, "cuda:0", cfg())
+        used = []
+        orig = eng.process_stream
+        eng.process_stream = lambda *a, **k: (used.append(1), orig(*a, **k))[1]
+        w = client("127.0.0.1", "127.0.0.1", cfg(), engine=eng, out_dir=str(tmp_path))
+        r = client("127.0.0.1", "127.0.0.1", cfg(), engine=CpuEngine(graph, cfg()), out_dir=str(tmp_path))
+        assert w.ready.wait(10) and r.ready.wait(10)
+        r.become_requester(video)
+        assert r.wait_job(120) is not None
+        cap = cv2.VideoCapture(str(tmp_path / "video0.mp4"))
+        n = 0
+        while cap.read()[0]:
+            n += 1
+        assert n == 28 and used, (n, used)
+        w.exit_threads(); r.exit_threads()
+    finally:
+        srv.exit_threads()
+
+
 def test_programmatic_dependent_launch_equals_serialized(graph, monkeypatch):
     """Every hot kernel is launched with programmatic stream serialization (next kernel resident while this one
     drains, griddepcontrol.wait before it touches produced data).  Results must be bit-identical to fully
