@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""The other BASELINE.json configs, on the in-process elastic cluster (one NativeEngine per GPU):
+"""The other BASELINE.json configs, on the elastic mailbox data plane (client + scheduler on GPU 0, one worker process per
+other GPU, parallel/mailbox.py):
 
   --config live          single synthetic 1080p stream at --fps 30|60: p50/p99 per-frame latency
   --config elastic       8 -> 4 -> 8 workers (or N -> N/2 -> N) mid-stream, no dropped frames
@@ -94,118 +95,175 @@ def main():
     from distributedvolunteercomputing_b200.config import Config
     from distributedvolunteercomputing_b200.engine import NativeEngine
     from distributedvolunteercomputing_b200.models.mobilenet_ssd import SSDGraph
-    from distributedvolunteercomputing_b200.parallel.local_cluster import LocalCluster
+    from distributedvolunteercomputing_b200.parallel.mailbox import ClientBox, ElasticBox, WorkerLanes
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", required=True, choices=["live", "elastic", "multi_client"])
     ap.add_argument("--gpus", type=int, default=torch.cuda.device_count())
     ap.add_argument("--fps", type=int, default=30)
     ap.add_argument("--frames", type=int, default=0)
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--seconds", type=float, default=2.0, help="elastic: length of each membership window")
+    ap.add_argument("--ingest", default="both", choices=["client", "sharded", "both"], help="multi_client: where frames enter")
     args = ap.parse_args()
     n_gpu = min(args.gpus, torch.cuda.device_count())
     graph = SSDGraph.random(seed=1, conf_gain=2.5)
+    torch.cuda.set_device(0)
 
-    def engine(i, batch, sub, hw=None):
-        e = NativeEngine(graph, f"cuda:{i}", Config(batch=batch, sub_batch=sub, use_cuda_graph=True), requester_id="client")
-        if hw is not None:      # build the plan and capture the CUDA graph up front, one engine at a time
-            e.process(np.zeros((batch, hw[0], hw[1], 3), np.uint8))
-        return e
+    def make_box(B, H, W, lanes, slots, on_result=None, fetch=True, done_timeout_s=2.0, feed_spec=None):
+        """Client + scheduler on GPU 0 (which also works), one spawned worker process per other GPU."""
+        cfg = Config(batch=B, use_cuda_graph=True)
+        eng = NativeEngine(graph, "cuda:0", cfg, requester_id="client")
+        client = ClientBox("cuda:0", B, H, W, max_workers=n_gpu, lanes=lanes, arena_slots=slots, engine=eng,
+                           done_timeout_s=done_timeout_s)
+        client.attach_local(0, WorkerLanes(eng, client.layout, *client.bases(), worker=0))
+        box = ElasticBox(client, on_result=on_result, fetch=fetch)
+        box.add_worker(0)
+        if n_gpu > 1:
+            box.spawn_workers([(w, w) for w in range(1, n_gpu)], graph, cfg, local_feed_spec=feed_spec)
+        return eng, client, box
+
+    def run_until(box, pred, timeout_s=120.0):
+        t0 = time.monotonic()
+        while not pred():
+            if box.pump() == 0:
+                if time.monotonic() - t0 > timeout_s:
+                    return False
+                time.sleep(0.00002)
+        return True
 
     if args.config == "live":
-        B = args.batch or 1
-        H, W = 1080, 1920
+        # one 1080p camera at --fps: each frame is a batch of one, handed to the least-loaded GPU the moment it arrives
+        B, H, W = 1, 1080, 1920
         n = args.frames or 300
-        cfg = Config(batch=B, worker_timeout_s=5.0)
-        lat = []
-        cl = LocalCluster(cfg, annotate=True, on_frame=lambda r, fr: lat.append(fr.latency_s * 1e3))
-        for i in range(n_gpu):
-            cl.join(f"gpu{i}", engine(i, B, 1, (H, W)), capacity=2)
-        frames = [torch.from_numpy(f).pin_memory() for f in synth(8, H, W)]
-        for i in range(2 * n_gpu * 3):                                        # warm-up (plans, graphs)
-            cl.submit("warm", frames[i % 8][None], i + 1)
-        cl.wait("warm", 2 * n_gpu * 3, 60)
+        t_sub, lat = {}, []
+        eng, client, box = make_box(B, H, W, lanes=2, slots=4 * n_gpu + 8,
+                                    on_result=lambda b, v, w: lat.append((time.perf_counter() - t_sub[b.batch_id]) * 1e3))
+        frames = [torch.from_numpy(f[None]).pin_memory() for f in synth(8, H, W)]
+        for i in range(6 * n_gpu):                                        # warm-up
+            b = box.submit_host(frames[i % 8], [i]); t_sub[b.batch_id] = time.perf_counter()
+        assert box.drain(60.0)
         lat.clear()
         period = 1.0 / args.fps
-        t0 = time.monotonic()
+        t0 = time.perf_counter()
         for i in range(n):
             target = t0 + i * period
-            while time.monotonic() < target:
-                time.sleep(0.0002)
-            cl.submit("cam", frames[i % 8][None], i + 1)
-        ok = cl.wait("cam", n, 60)
-        lat_s = sorted(lat)
-        out = {"config": "live 1080p", "fps": args.fps, "n_gpus": n_gpu, "frames": n, "complete": ok,
-               "p50_ms": round(lat_s[len(lat_s) // 2], 3), "p99_ms": round(lat_s[int(len(lat_s) * 0.99) - 1], 3),
-               "max_ms": round(lat_s[-1], 3), "batch": B}
-        out["error"] = cl.last_error
-        print(json.dumps(out), flush=True)
-        cl.close()
+            while time.perf_counter() < target:
+                box.pump()
+            b = box.submit_host(frames[i % 8], [i])
+            t_sub[b.batch_id] = time.perf_counter()
+            box.pump()
+        ok = box.drain(30.0)
+        ls = sorted(lat)
+        print(json.dumps({"config": "live 1080p", "fps": args.fps, "n_gpus": n_gpu, "frames": n, "complete": bool(ok and len(ls) == n),
+                          "p50_ms": round(ls[len(ls) // 2], 3), "p99_ms": round(ls[int(len(ls) * 0.99) - 1], 3), "max_ms": round(ls[-1], 3),
+                          "batch": B, "path": "ElasticBox.submit_host: pinned host frame -> arena (H2D) -> NVLink pull in K1a -> rows pushed "
+                          "back in K9 -> D2H; latency = host wall clock from submit to result callback", "stats": dict(box.stats)}), flush=True)
+        box.shutdown(); client.close()
     elif args.config == "elastic":
-        B = args.batch or 64
-        H, W = 300, 300
-        n_batches = 60 * n_gpu
-        cfg = Config(batch=B, worker_timeout_s=10.0)
-        seen = []
-        cl = LocalCluster(cfg, annotate=True, on_frame=lambda r, fr: seen.append(fr.frame_id))
-        engines = [engine(i, B, 0, (H, W)) for i in range(n_gpu)]
-        for i, e in enumerate(engines):
-            cl.join(f"gpu{i}", e)
-        pool = torch.from_numpy(synth(B * 4, H, W)).pin_memory()
-        for i in range(n_gpu * 2):
-            cl.submit("warm", pool[:B], i * B + 1)
-        cl.wait("warm", n_gpu * 2 * B, 60)
-        N = n_batches * B
-        t0 = time.monotonic()
-        for b in range(n_batches):
-            cl.submit("client", pool[(b % 4) * B:(b % 4 + 1) * B], b * B + 1)
-        time.sleep(0.05)
-        half = list(range(n_gpu // 2, n_gpu)) if n_gpu > 1 else []
-        t_leave = time.monotonic() - t0
-        lost = sum(cl.leave(f"gpu{i}") for i in half)                         # N -> N/2 with batches in flight
-        time.sleep(0.15)
-        for i in half:
-            cl.join(f"gpu{i}", engines[i])                                    # N/2 -> N
-        t_join = time.monotonic() - t0
-        ok = cl.wait("client", N, 90)
-        dt = time.monotonic() - t0
-        in_order = seen[-N:] == list(range(1, N + 1))
-        out = {"config": f"elastic {n_gpu}->{n_gpu - len(half)}->{n_gpu}", "n_gpus": n_gpu, "frames": N, "complete": ok,
-               "in_order_no_drop_no_dup": bool(in_order), "redispatched_batches": int(cl.sched.stats["redispatched"]),
-               "batches_in_flight_at_leave": int(lost), "t_leave_s": round(t_leave, 3), "t_rejoin_s": round(t_join, 3),
-               "frames_per_s": round(N / dt, 1), "seconds": round(dt, 3), "error": cl.last_error}
-        print(json.dumps(out), flush=True)
-        cl.close()
+        # N -> N/2 -> N on the fused NVLink path: half of the workers leave with batches in flight, later join again
+        B, H, W = args.batch or 64, 300, 300
+        lanes, pool_n = 4, 8 * n_gpu
+        done_at, per_batch = [], {}
+
+        def on_result(b, v, w):
+            per_batch[b.batch_id] = per_batch.get(b.batch_id, 0) + 1
+            done_at.append(time.perf_counter())
+
+        eng, client, box = make_box(B, H, W, lanes=lanes, slots=pool_n + 8, on_result=on_result, fetch=True, done_timeout_s=1.0)
+        pool = torch.from_numpy(synth(B * 8, H, W)).view(8, B, H, W, 3)
+        slots = [client.alloc_slot() for _ in range(pool_n)]
+        for k, sl in enumerate(slots):
+            client.slot_tensor(sl).copy_(pool[k % 8])
+        torch.cuda.synchronize()
+        submitted = []
+
+        def top_up():
+            while box.sched.pending() < 2 * n_gpu * lanes:
+                submitted.append(box.submit_slot(slots[len(submitted) % pool_n], range(B)).batch_id)
+
+        def window(seconds):
+            t_end = time.perf_counter() + seconds
+            while time.perf_counter() < t_end:
+                top_up()
+                box.pump()
+
+        window(0.5)                                                       # warm-up
+        half = list(range(n_gpu - n_gpu // 2, n_gpu)) if n_gpu > 1 else []
+        marks = [time.perf_counter()]
+        window(args.seconds)
+        marks.append(time.perf_counter())
+        inflight_at_leave = sum(box.remove_worker(w, reason="leave", stop=True) for w in half)
+        marks.append(time.perf_counter())
+        window(args.seconds)
+        marks.append(time.perf_counter())
+        for w in half:
+            box.rejoin_worker(w)
+        marks.append(time.perf_counter())
+        window(args.seconds)
+        marks.append(time.perf_counter())
+        ok = box.drain(30.0)
+
+        def rate(a, b, guard=0.2):
+            n = sum(1 for t in done_at if a + guard <= t < b)
+            return round(n * B / max(1e-9, b - a - guard), 1)
+
+        exactly_once = sorted(per_batch) == sorted(submitted) and all(c == 1 for c in per_batch.values())
+        print(json.dumps({"config": f"elastic {n_gpu}->{n_gpu - len(half)}->{n_gpu}", "n_gpus": n_gpu, "batch": B,
+                          "frames": len(submitted) * B, "complete": bool(ok), "every_batch_delivered_exactly_once": bool(exactly_once),
+                          "batches_in_flight_at_leave_redispatched": int(inflight_at_leave),
+                          "frames_per_s_all": rate(marks[0], marks[1]), "frames_per_s_half": rate(marks[2], marks[3]),
+                          "frames_per_s_rejoined": rate(marks[4], marks[5]), "leave_ms": round((marks[2] - marks[1]) * 1e3, 2),
+                          "rejoin_ms": round((marks[4] - marks[3]) * 1e3, 2), "window_s": args.seconds,
+                          "path": "ElasticBox on the mailbox data plane: frames resident in the client GPU's arena, NVLink pull in K1a, "
+                                  "rows pushed back in K9, results read to the host; worker processes leave (stop) and re-join",
+                          "stats": dict(box.stats), "sched": dict(box.sched.stats)}), flush=True)
+        box.shutdown(); client.close()
     else:
-        B = args.batch or 16
-        H, W = 720, 1280
-        streams, per = 32, (args.frames or 128)
-        cfg = Config(batch=B, worker_timeout_s=10.0)
-        counts = {}
-        lk = threading.Lock()
+        # 32 concurrent 720p streams, fair share between them (one scheduler queue per stream), batches of B frames
+        B, H, W = args.batch or 16, 720, 1280
+        streams, per = 32, (args.frames or 512)
+        lanes = 3
+        n_batches = streams * per // B
+        for ingest in (["client", "sharded"] if args.ingest == "both" else [args.ingest]):
+            counts, lat, t_sub = {}, [], {}
 
-        def on_frame(r, fr):
-            with lk:
-                counts[r] = counts.get(r, 0) + 1
+            def on_result(b, v, w):
+                counts[b.requester] = counts.get(b.requester, 0) + len(b.frame_ids)
+                lat.append((time.perf_counter() - t_sub[b.batch_id]) * 1e3)
 
-        cl = LocalCluster(cfg, annotate=True, on_frame=on_frame)
-        for i in range(n_gpu):
-            cl.join(f"gpu{i}", engine(i, B, 4, (H, W)))
-        pool = torch.from_numpy(synth(B * 2, H, W)).pin_memory()
-        for i in range(n_gpu * 2):
-            cl.submit("warm", pool[:B], i * B + 1)
-        cl.wait("warm", n_gpu * 2 * B, 60)
-        t0 = time.monotonic()
-        for s in range(streams):
-            for k in range(0, per, B):
-                cl.submit(f"cam{s}", pool[(k // B % 2) * B:(k // B % 2 + 1) * B], k + 1)
-        deadline = time.monotonic() + 90
-        ok = all(cl.wait(f"cam{s}", per, max(0.1, deadline - time.monotonic())) for s in range(streams))
-        dt = time.monotonic() - t0
-        out = {"config": "32 concurrent 720p streams", "n_gpus": n_gpu, "streams": streams, "frames": streams * per, "complete": ok,
-               "frames_per_s": round(streams * per / dt, 1), "seconds": round(dt, 3), "batch": B,
-               "batch_latency_p50_ms": cl.metrics.percentile("batch_latency_ms", 50), "batch_latency_p99_ms": cl.metrics.percentile("batch_latency_ms", 99)}
-        print(json.dumps(out), flush=True)
-        cl.close()
+            eng, client, box = make_box(B, H, W, lanes=lanes, slots=n_gpu * lanes + 8, on_result=on_result, done_timeout_s=5.0,
+                                        feed_spec=("synthetic", 4, 11) if ingest == "sharded" else None)
+            pool = torch.from_numpy(synth(B * 4, H, W)).view(4, B, H, W, 3).pin_memory()
+            for i in range(4 * n_gpu):
+                b = box.submit_local(range(B), host=pool[i % 4], requester="warm") if ingest == "sharded" else \
+                    box.submit_host(pool[i % 4], range(B), requester="warm")
+                t_sub[b.batch_id] = time.perf_counter()
+            assert box.drain(60.0)
+            box.sched.drop_requester("warm")
+            counts.clear(); lat.clear()
+            sent = 0
+            t0 = time.perf_counter()
+            while sent < n_batches or box.outstanding() or box.flights:
+                while sent < n_batches and box.sched.pending() < 4 * n_gpu * lanes:
+                    s_id = sent % streams
+                    b = box.submit_local(range(B), host=pool[sent % 4], requester=f"cam{s_id}") if ingest == "sharded" else \
+                        box.submit_host(pool[sent % 4], range(B), requester=f"cam{s_id}")
+                    t_sub[b.batch_id] = time.perf_counter()
+                    sent += 1
+                box.pump()
+            dt = time.perf_counter() - t0
+            ls = sorted(lat)
+            total = sum(counts.values())
+            print(json.dumps({"config": "32 concurrent 720p streams", "ingest": ingest, "n_gpus": n_gpu, "streams": streams,
+                              "frames": total, "complete": total == n_batches * B and len(counts) == streams,
+                              "frames_per_s": round(total / dt, 1), "seconds": round(dt, 3), "batch": B,
+                              "batch_latency_p50_ms": round(ls[len(ls) // 2], 3), "batch_latency_p99_ms": round(ls[int(len(ls) * 0.99) - 1], 3),
+                              "h2d_MB_per_s": round(total * H * W * 3 / dt / 1e6, 1),
+                              "note": "client: every frame enters over the client GPU's PCIe link, then NVLink; "
+                                      "sharded: each GPU's process uploads its share over its own PCIe link" , "stats": dict(box.stats)}), flush=True)
+            box.shutdown(); client.close()
+            del eng, client, box
+            torch.cuda.empty_cache()
 
 
 if __name__ == "__main__":

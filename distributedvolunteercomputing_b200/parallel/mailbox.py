@@ -582,23 +582,47 @@ class ElasticBox:
     def workers_alive(self) -> List[int]:
         return [w for w, a in self.alive.items() if a]
 
-    def spawn_worker(self, w: int, device_index: int, graph, cfg, stall_after: Optional[int] = None, ready_timeout_s: float = 180.0):
-        """Start a worker PROCESS on GPU `device_index` and add it once its lanes are built.  Returns the process."""
+    def spawn_workers(self, workers: Sequence[Tuple[int, int]], graph, cfg, stall_after: Optional[int] = None,
+                      ready_timeout_s: float = 300.0, local_feed_spec: Optional[Tuple] = None) -> None:
+        """Start one worker PROCESS per (worker index, device index) pair - all at once, they build their engines in
+        parallel - and add each to the pool once its lanes are built."""
         import multiprocessing as mp
         ctx = mp.get_context("spawn")
-        self.client.reset_worker(w)            # clears an earlier stop before the newcomer reads its position
-        parent, child = ctx.Pipe()
-        p = ctx.Process(target=worker_process_main, args=(self.client.export(), w, device_index, graph, cfg, child, stall_after),
-                        daemon=True)
-        p.start()
-        if not parent.poll(ready_timeout_s):
-            p.kill()
-            raise RuntimeError(f"worker gpu{w} did not come up within {ready_timeout_s} s")
-        msg = parent.recv()
+        started = []
+        for w, dev_index in workers:
+            self.client.reset_worker(w)            # clears an earlier stop before the newcomer reads its position
+            parent, child = ctx.Pipe()
+            p = ctx.Process(target=worker_process_main,
+                            args=(self.client.export(), w, dev_index, graph, cfg, child, stall_after, local_feed_spec), daemon=True)
+            p.start()
+            started.append((w, p, parent))
+        deadline = time.monotonic() + ready_timeout_s
+        for w, p, parent in started:
+            if not parent.poll(max(0.0, deadline - time.monotonic())):
+                p.kill()
+                raise RuntimeError(f"worker gpu{w} did not come up within {ready_timeout_s} s")
+            msg = parent.recv()
+            assert msg[0] == "ready", msg
+            self.procs[w] = (p, parent)
+            self.add_worker(w)
+
+    def spawn_worker(self, w: int, device_index: int, graph, cfg, stall_after: Optional[int] = None, ready_timeout_s: float = 300.0):
+        """Start a worker PROCESS on GPU `device_index` and add it once its lanes are built.  Returns the process."""
+        self.spawn_workers([(w, device_index)], graph, cfg, stall_after, ready_timeout_s)
+        return self.procs[w][0]
+
+    def rejoin_worker(self, w: int, ready_timeout_s: float = 60.0):
+        """A worker process that left (its serving loop returned on stop) joins again: no new process, no new engine."""
+        p, conn = self.procs[w]
+        while conn.poll(0.0):
+            conn.recv()                            # its "served" report of the previous membership
+        self.client.reset_worker(w)
+        conn.send("rejoin")
+        if not conn.poll(ready_timeout_s):
+            raise RuntimeError(f"worker gpu{w} did not answer the re-join")
+        msg = conn.recv()
         assert msg[0] == "ready", msg
-        self.procs[w] = (p, parent)
         self.add_worker(w)
-        return p
 
     # ------------------------------------------------------------------ work intake
     def submit_slot(self, slot: int, frame_ids: Sequence[int], keep_slot: bool = True, requester: Optional[str] = None) -> Batch:
@@ -701,28 +725,48 @@ class ElasticBox:
 
 # ====================================================================================== process / thread front-ends
 def worker_process_main(export: Dict[str, Any], worker: int, device_index: int, graph, cfg, conn=None,
-                        stall_after: Optional[int] = None):
+                        stall_after: Optional[int] = None, local_feed_spec: Optional[Tuple] = None):
     """Entry point of a spawned worker process (multiprocessing 'spawn'): map the client's box, adopt its weights,
-    serve until told to stop.  `conn` is a multiprocessing connection: "ready" goes out once the lanes are built,
-    anything coming in means stop.  `stall_after` (fault injection) makes the worker go silent after that many batches."""
+    serve until told to stop; then wait on the pipe: "rejoin" serves again (workers leave and join at will,
+    server.py:104-154), anything else ends the process.  "ready" goes out whenever the lanes are about to serve,
+    ("served", batches, stale frames) whenever a membership ends.  `stall_after` (fault injection) makes the worker go
+    silent after that many batches.  `local_feed_spec` = ("synthetic", pool, seed): sharded ingest, the worker uploads
+    its own synthetic frames (a pinned pool of `pool` batches) instead of pulling them from the client."""
     from ..engine import NativeEngine
     torch.cuda.set_device(device_index)
     dev = f"cuda:{device_index}"
     eng = NativeEngine(graph, dev, cfg, requester_id=getattr(cfg, "requester_id", "") or "client")
     lay, cb, rb, ab = open_box(export, dev)
     lanes = WorkerLanes(eng, lay, cb, rb, ab, worker, adopt_weights=True)
-    if conn is not None:
-        conn.send(("ready", worker))
-    stop = (lambda: conn.poll()) if conn is not None else (lambda: False)
-    n = lanes.serve(should_stop=stop, max_batches=stall_after)
-    if stall_after is not None:
-        while not stop():          # injected stall: alive, mapped, silent
-            time.sleep(0.01)
-    if conn is not None:
+    feed = None
+    if local_feed_spec is not None and local_feed_spec[0] == "synthetic":
+        _, pool, seed = local_feed_spec
+        rng = np.random.default_rng(seed + worker)
+        small = rng.integers(0, 256, (pool, lay.B, lay.H // 8 + 1, lay.W // 8 + 1, 3), dtype=np.uint8)
+        frames = np.repeat(np.repeat(small, 8, axis=2), 8, axis=3)[:, :, :lay.H, :lay.W]
+        host = torch.from_numpy(np.ascontiguousarray(frames)).pin_memory()
+        feed = lambda i: host[i % pool]
+    stop_seen = [False]
+
+    def stop() -> bool:
+        return conn is not None and conn.poll()
+
+    while True:
+        if conn is not None:
+            conn.send(("ready", worker))
+        n = lanes.serve(should_stop=stop, max_batches=stall_after, local_feed=feed)
+        if stall_after is not None:
+            while not stop():          # injected stall: alive, mapped, silent
+                time.sleep(0.01)
+        if conn is None:
+            return
         try:
             conn.send(("served", n, lanes.stale_count()))
-        except Exception:
-            pass
+            msg = conn.recv()          # blocks: "rejoin" or anything else / EOF = exit
+        except (EOFError, OSError):
+            return
+        if msg != "rejoin":
+            return
 
 
 class ThreadWorker:
