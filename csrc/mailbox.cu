@@ -196,6 +196,13 @@ extern "C" int dvc_mbx_dispatch(const void* h_src, void* d_dst, size_t src_bytes
   return DVC_OK;
 }
 
+extern "C" int dvc_mbx_copy_out(const void* d_result, void* h_result, size_t bytes, void* event, void* stream) {
+  DVC_REQUIRE(d_result && h_result && bytes, "mbx_copy_out: bad arguments");
+  DVC_CHECK_CUDA(cudaMemcpyAsync(h_result, d_result, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  if (event) DVC_CHECK_CUDA(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
+  return DVC_OK;
+}
+
 extern "C" int dvc_mbx_signal(uint32_t* word, uint32_t value, void* stream) {
   DVC_REQUIRE(word, "mbx_signal: null word");
   mbx_signal_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(word, value);

@@ -65,7 +65,10 @@ class BoxCluster:
             for w in range(self.world):
                 if w == self.rank and not self.client_works:
                     continue
-                self.box.add_worker(w)
+                self.box.add_worker(w)          # descriptors show the client's position, fresh epoch words
+        self.dist.barrier()
+        if not self.is_client:
+            self._synced = self.lanes.sync_position()      # read BEFORE the client may post the phase's first descriptor
         self.dist.barrier()
 
     def serve(self, local_feed=None) -> int:
@@ -75,7 +78,7 @@ class BoxCluster:
         with torch.cuda.device(self.dev):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            n = self.lanes.serve(local_feed=local_feed, expect_work=True)
+            n = self.lanes.serve(local_feed=local_feed, expect_work=True, synced=True) if self._synced else 0
             b.record()
             b.synchronize()
             self.serve_ms = a.elapsed_time(b)

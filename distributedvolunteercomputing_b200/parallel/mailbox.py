@@ -133,6 +133,7 @@ class WorkerLanes:
             self.depth = 2
             self._hs_keep, self.hs, self.hs_addr = pinned_status(nl * 4)
             self.states = []
+            self.graphs: Dict[int, Any] = {}
             self.my_boxes, self.my_box_count = [], []
             for l in range(nl):
                 st = engine.state(lay.B, lay.H, lay.W, slot=300 + worker * 16 + l)
@@ -176,11 +177,28 @@ class WorkerLanes:
 
     def enqueue_body(self, l: int):
         """K1a (peer pull of the batch named by the lane's control block) -> network -> K9 (peer push + done word) ->
-        K10 overlay of this GPU's own 400-wide frames."""
+        K10 overlay of this GPU's own 400-wide frames.  With CUDA graphs the whole chain is ONE replay: every pointer in
+        it is fixed (the source of K1a is read from the lane's control block at run time)."""
+        if not self.engine.cfg.use_cuda_graph:
+            return self._enqueue_body_eager(l)
+        g = self.graphs.get(l)
+        if g is None:
+            from ..engine import _CAPTURE_LOCK
+            with _CAPTURE_LOCK:
+                self._enqueue_body_eager(l)                  # warm-up outside capture (first-launch attribute set-up)
+                torch.cuda.synchronize(self.dev)
+                g = torch.cuda.CUDAGraph()
+                cap = torch.cuda.Stream(device=self.dev)
+                with torch.cuda.graph(g, stream=cap, capture_error_mode="thread_local"):
+                    self._enqueue_body_eager(l)
+            self.graphs[l] = g
+        g.replay()
+
+    def _enqueue_body_eager(self, l: int):
         from ..ops import kernels as K
         st, lay, cp = self.states[l], self.layout, self.ctl_ptr(l)
         K.resize_u8_indirect(cp, lay.raw_stride, lay.B, st.t_area, st.frames400_flat, st.stride400, cp + 8, cp + 12)
-        self.engine.run(st, annotate=False, resize=False)
+        self.engine.run(st, annotate=False, resize=False, use_graph=False)
         if self.annotate:
             m = st.masks
             nl_, lh, lw = m.label_masks.shape
@@ -212,7 +230,8 @@ class WorkerLanes:
 
     def serve(self, should_stop: Callable[[], bool] = lambda: False, max_batches: Optional[int] = None,
               stream_timeout_s: float = 0.003, probe_timeout_s: float = 0.0005, idle_sleep_s: float = 0.0002,
-              local_feed: Optional[Callable[[int], torch.Tensor]] = None, expect_work: bool = False) -> int:
+              local_feed: Optional[Callable[[int], torch.Tensor]] = None, expect_work: bool = False,
+              on_ready: Optional[Callable[[], None]] = None, synced: bool = False) -> int:
         """Serve dispatches until the client posts stop, `should_stop()` turns true or `max_batches` were served.
 
         While batches keep arriving every lane has `depth` (wait + network) pairs queued on its stream, so the GPU never
@@ -220,9 +239,15 @@ class WorkerLanes:
         out the lane falls back to short probes (a wait kernel alone) so an idle worker does no useless work.
         `local_feed(i)` (optional, sharded ingest) returns the pinned host batch this worker uploads itself before the
         i-th queued batch; the client's descriptor (kind 1) is then only the permission to deliver.
-        `expect_work` starts the lanes in streaming mode (a phase the client opens with a full queue)."""
-        if not self.sync_position():
+        `expect_work` starts the lanes in streaming mode (a phase the client opens with a full queue).
+        `on_ready()` is called once the lanes' sequence position has been read: only then may the client add this worker."""
+        # the lanes' position must be read BEFORE the client may dispatch to this worker (`on_ready` tells it so, or the
+        # caller did sync_position() itself ahead of a barrier): a descriptor posted in between would be taken for the
+        # baseline and its batch never served
+        if not synced and not self.sync_position():
             return 0
+        if on_ready is not None:
+            on_ready()
         lay, dev = self.layout, self.dev
         nl = lay.lanes
         queues: List[Deque[Tuple[str, int, torch.cuda.Event]]] = [collections.deque() for _ in range(nl)]
@@ -347,6 +372,21 @@ class ClientBox:
         self.epoch = [0] * max_workers
         self.busy = [[False] * lanes for _ in range(max_workers)]
         self.free_slots = list(range(slots - 1, -1, -1))
+        self._hs_status = self.hs["status"]
+        self._cache = []
+        for k in range(max_workers * lanes):
+            w, l = divmod(k, lanes)
+            d = L.MbxDesc()
+            self._cache.append({"desc": d, "desc_ref": C.byref(d), "desc_addr": lay.desc_addr(self.ctl.ptr, w, l),
+                                "done_addr": lay.done_addr(self.ctl.ptr, w, l), "hs": self.hs_addr + k * HS_DTYPE.itemsize,
+                                "res": lay.res_addr(self.res.ptr, w, l), "h_res": self.h_res[k].data_ptr(),
+                                "event": self.events[k].cuda_event, "stream": self.streams[k].cuda_stream,
+                                "desc_addr_arr": (C.c_void_p * 1)(lay.desc_addr(self.ctl.ptr, w, l)),
+                                "done_addr_arr": (C.c_void_p * 1)(lay.done_addr(self.ctl.ptr, w, l)),
+                                "seq_arr": (C.c_uint32 * 1)(0)})
+        # one process driving several GPUs from several threads must re-select the device in the library's own CUDA
+        # runtime on every call; a process that only ever uses the client's GPU (torchrun, spawned workers) need not
+        self._set_device_each_call = False
         self.local: Dict[int, WorkerLanes] = {}        # workers living on the client's own GPU (same process)
         self._views: Dict[int, Dict[str, np.ndarray]] = {}
         self.dispatches = 0
@@ -417,46 +457,52 @@ class ClientBox:
         if self.seq[worker][lane] >= L.MBX_SEQ_STOP:
             self.seq[worker][lane] = 1
         seq = self.seq[worker][lane]
-        desc = L.MbxDesc(seq, self.epoch[worker], n_valid, kind, lay.arena_off(slot), batch_id & 0xFFFFFFFF, 0)
+        c = self._cache[k]                 # per (worker, lane): addresses and handles resolved once
+        desc = c["desc"]
+        desc.seq, desc.epoch, desc.n_valid, desc.kind = seq, self.epoch[worker], n_valid, kind
+        desc.src_off, desc.batch_id = lay.arena_off(slot), batch_id & 0xFFFFFFFF
         stream = self.streams[k]
-        hs = self.hs_addr + k * HS_DTYPE.itemsize
-        self.hs[k]["status"] = 0xFFFF
-        cp = self.ctl.ptr
-        res = lay.res_addr(self.res.ptr, worker, lane)
+        hs = c["hs"]
+        self._hs_status[k] = 0xFFFF
+        res = c["res"]
         tmo = int(self.done_timeout_s * 1e9)
         loc = self.local.get(worker)
-        with torch.cuda.device(self.dev):
+        if loc is None:
+            # hot path (7 of 8 dispatches on a full box): one native call, no Python context managers
+            if kind == 1:
+                host_src = None           # the worker uploads its own shard
+            src_ptr, src_bytes = (host_src.data_ptr(), host_src.numel()) if host_src is not None else (None, 0)
+            if host_src is not None:
+                assert lay.raw_stride == lay.H * lay.W * 3, "host upload needs a dense frame pitch"
+            if self._set_device_each_call:
+                L.set_device(self.dev)
+            rc = self.lib.dvc_mbx_dispatch(src_ptr, self.arena.ptr + desc.src_off, src_bytes, c["desc_addr"], c["desc_ref"],
+                                           c["done_addr"], hs, tmo, res, c["h_res"] if fetch else None, lay.copy_bytes,
+                                           c["event"], c["stream"])
+            if rc:
+                L.check(rc, "mbx_dispatch")
+            self.busy[worker][lane] = True
+            self.dispatches += 1
+            return
+        # the client's own GPU works too: same kernels, same words, queued inline on the same stream (a wait never spins
+        # on something a later launch of this GPU has to produce)
+        with torch.cuda.device(self.dev), torch.cuda.stream(stream):
             L.set_device(self.dev)
-            if loc is None:
-                if kind == 1:
-                    host_src = None           # the worker uploads its own shard
-                src_ptr, src_bytes = (host_src.data_ptr(), host_src.numel()) if host_src is not None else (None, 0)
-                if host_src is not None:
-                    assert lay.raw_stride == lay.H * lay.W * 3, "host upload needs a dense frame pitch"
-                L.check(self.lib.dvc_mbx_dispatch(src_ptr, self.arena.ptr + lay.arena_off(slot), src_bytes,
-                                                  lay.desc_addr(cp, worker, lane), C.byref(desc), lay.done_addr(cp, worker, lane),
-                                                  hs, tmo, res, self.h_res[k].data_ptr() if fetch else None, lay.copy_bytes,
-                                                  self.events[k].cuda_event, stream.cuda_stream), "mbx_dispatch")
+            if host_src is not None and kind == 1:
+                loc.local_raw[lane].view(lay.B, lay.raw_stride)[:, : lay.H * lay.W * 3].copy_(
+                    host_src.reshape(lay.B, -1), non_blocking=True)
+            elif host_src is not None:
+                self.slot_tensor(slot).copy_(host_src, non_blocking=True)
+            sp = c["stream"]
+            L.check(self.lib.dvc_mbx_post(c["desc_addr_arr"], c["desc_ref"], 1, sp), "mbx_post")
+            loc.enqueue_wait(lane, None, seq, 0.001)
+            loc.enqueue_body(lane)
+            c["seq_arr"][0] = seq
+            L.check(self.lib.dvc_mbx_wait_done(c["done_addr_arr"], c["seq_arr"], 1, hs, tmo, sp), "mbx_wait_done")
+            if fetch:
+                L.check(self.lib.dvc_mbx_copy_out(res, c["h_res"], lay.copy_bytes, c["event"], sp), "mbx_copy_out")
             else:
-                # the client's own GPU works too: same kernels, same words, queued inline on the same stream (a wait
-                # never spins on something a later launch of this GPU has to produce)
-                with torch.cuda.stream(stream):
-                    if host_src is not None and kind == 1:
-                        loc.local_raw[lane].view(lay.B, lay.raw_stride)[:, : lay.H * lay.W * 3].copy_(
-                            host_src.reshape(lay.B, -1), non_blocking=True)
-                    elif host_src is not None:
-                        self.slot_tensor(slot).copy_(host_src, non_blocking=True)
-                    ptrs = (C.c_void_p * 1)(lay.desc_addr(cp, worker, lane))
-                    L.check(self.lib.dvc_mbx_post(ptrs, C.byref(desc), 1, stream.cuda_stream), "mbx_post")
-                    loc.enqueue_wait(lane, None, seq, 0.001)
-                    loc.enqueue_body(lane)
-                    dptr = (C.c_void_p * 1)(lay.done_addr(cp, worker, lane))
-                    sq = (C.c_uint32 * 1)(seq)
-                    L.check(self.lib.dvc_mbx_wait_done(dptr, sq, 1, hs, tmo, stream.cuda_stream), "mbx_wait_done")
-                    if fetch:
-                        self.h_res[k].copy_(self.res.tensor(torch.uint8, (lay.copy_bytes,), offset_bytes=res - self.res.ptr),
-                                            non_blocking=True)
-                    self.events[k].record(stream)
+                self.events[k].record(stream)
         self.busy[worker][lane] = True
         self.dispatches += 1
 
@@ -752,9 +798,8 @@ def worker_process_main(export: Dict[str, Any], worker: int, device_index: int, 
         return conn is not None and conn.poll()
 
     while True:
-        if conn is not None:
-            conn.send(("ready", worker))
-        n = lanes.serve(should_stop=stop, max_batches=stall_after, local_feed=feed)
+        ready = (lambda: conn.send(("ready", worker))) if conn is not None else None
+        n = lanes.serve(should_stop=stop, max_batches=stall_after, local_feed=feed, on_ready=ready)
         if stall_after is not None:
             while not stop():          # injected stall: alive, mapped, silent
                 time.sleep(0.01)
@@ -780,6 +825,7 @@ class ThreadWorker:
                 L.check(client.lib.dvc_p2p_enable_peer(client.dev.index or 0), "enable_peer")
             self.lanes = WorkerLanes(engine, client.layout, *client.bases(), worker)
         self._stop = threading.Event()
+        self.ready = threading.Event()          # set once the lanes' position is read: add the worker after this
         self.thread = threading.Thread(target=self._run, daemon=True, name=f"mbx-worker-{worker}")
         self.hang = False
 
@@ -788,7 +834,7 @@ class ThreadWorker:
         return self
 
     def _run(self):
-        self.lanes.serve(should_stop=self._stop.is_set)
+        self.lanes.serve(should_stop=self._stop.is_set, on_ready=self.ready.set)
 
     def stop(self, join_s: float = 10.0):
         self._stop.set()

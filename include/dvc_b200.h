@@ -315,6 +315,8 @@ int dvc_mbx_wait_done(void* const* h_done_ptrs, const uint32_t* h_seqs, int n, d
 int dvc_mbx_dispatch(const void* h_src, void* d_dst, size_t src_bytes, void* desc_ptr, const dvc_mbx_desc* h_desc,
                      void* done_ptr, dvc_mbx_host_status* h_status, unsigned long long timeout_ns,
                      const void* d_result, void* h_result, size_t result_bytes, void* event, void* stream);
+/* Device->host copy of a result slot into pinned memory, then cudaEventRecord(event) (event may be NULL). */
+int dvc_mbx_copy_out(const void* d_result, void* h_result, size_t bytes, void* event, void* stream);
 /* st.release.sys of one word (epoch bump, hand-rolled completion after an extra copy). */
 int dvc_mbx_signal(uint32_t* word, uint32_t value, void* stream);
 /* Bind a plan to a lane: K1b's gate reads ctl->gate_now / gate_expect, K9 takes its flag value from ctl->flag_value,
