@@ -436,6 +436,16 @@ class ClientBox:
             L.check(self.lib.dvc_mbx_post(ptrs, descs, n, self.ctrl_stream.cuda_stream), "mbx_post")
             self.ctrl_stream.synchronize()
 
+    def cancel(self, worker: int, lane: int):
+        """Release the lane's pending done-wait now (the worker is gone, nobody will publish the word): the client writes
+        the awaited sequence number itself.  The caller ignores what the lane's poll then reports."""
+        if not self.busy[worker][lane]:
+            return
+        with torch.cuda.device(self.dev):
+            L.set_device(self.dev)
+            L.check(self.lib.dvc_mbx_signal(self.layout.done_addr(self.ctl.ptr, worker, lane), self.seq[worker][lane],
+                                            self.ctrl_stream.cuda_stream), "mbx_signal")
+
     def stop_worker(self, worker: int):
         """Tell the worker's serving loop to return (every lane's descriptor gets the stop sequence number)."""
         self._post_all_lanes(worker, [L.MBX_SEQ_STOP] * self.layout.lanes)
@@ -566,6 +576,7 @@ class _Flight:
     lane: int
     slot: int
     t0: float
+    cancelled: bool = False
 
 
 class ElasticBox:
@@ -619,6 +630,10 @@ class ElasticBox:
         self.epoch_counter += 1
         self.client.set_epoch(w, self.epoch_counter)          # K14: whatever it still delivers is stale from here on
         requeued = self.sched.leave(self.name(w), reason)
+        for (fw, fl), flight in self.flights.items():
+            if fw == w and not flight.cancelled:
+                flight.cancelled = True            # re-queued above; its done word will not come, do not wait for it
+                self.client.cancel(fw, fl)
         if stop:
             self.client.stop_worker(w)
         self.stats["leaves" if reason == "leave" else "failures"] += 1
@@ -696,6 +711,8 @@ class ElasticBox:
             if r is None:
                 continue
             del self.flights[key]
+            if fl.cancelled:
+                continue
             if r == "ok":
                 first = self.sched.complete(fl.batch.batch_id, self.name(fl.worker))
                 if first is not None:

@@ -33,6 +33,9 @@ class FakeClient:
         if f is None:
             return None
         f[0] += 1
+        if f[0] >= 10 ** 9:
+            del self.flight[(w, lane)]
+            return "ok"
         if w in self.dead:
             if f[0] >= self.timeout_polls:
                 del self.flight[(w, lane)]
@@ -46,6 +49,11 @@ class FakeClient:
 
     def result(self, w, lane):
         return {"batch_id": self.last[1]}
+
+    def cancel(self, w, lane):
+        f = self.flight.get((w, lane))
+        if f is not None:
+            f[0] = 10 ** 9                # the client released the wait itself: the poll returns at once
 
     def set_epoch(self, w, e):
         self.epochs[w].append(e)
@@ -140,8 +148,19 @@ def test_waiting_for_a_lane_does_not_burn_attempts():
     box.add_worker(0)
     for _ in range(40):
         box.pump()
-    assert box.sched.stats["dropped_after_max_attempts"] == 0 and box.sched.stats["undone"] > 3
+    assert box.sched.stats["dropped_after_max_attempts"] == 0
     assert run(box) and box.stats["completed"] == 1
+
+
+def test_undo_dispatch_returns_credit_and_attempt():
+    s = Scheduler(max_attempts=2, requester_works=True)
+    s.join("a", capacity=1)
+    b = s.submit("r", [1])
+    for _ in range(10):                       # far more hand-over failures than max_attempts
+        d = s.next_dispatch()
+        assert d is not None and d[0] is b
+        assert s.undo_dispatch(b.batch_id) is b and b.attempts == 0
+    assert s.stats["dropped_after_max_attempts"] == 0 and s.members.workers["a"].inflight == 0
 
 
 def test_dropped_batches_are_reported():
