@@ -203,6 +203,53 @@ extern "C" int dvc_mbx_copy_out(const void* d_result, void* h_result, size_t byt
   return DVC_OK;
 }
 
+extern "C" int dvc_mbx_poll(void* const* h_events, const unsigned char* h_busy, int n, unsigned char* h_done) {
+  DVC_REQUIRE(h_events && h_busy && h_done && n >= 0, "mbx_poll: bad arguments");
+  int found = 0;
+  for (int i = 0; i < n; ++i) {
+    h_done[i] = 0;
+    if (!h_busy[i]) continue;
+    cudaError_t e = cudaEventQuery((cudaEvent_t)h_events[i]);
+    if (e == cudaSuccess) { h_done[i] = 1; ++found; }
+    else if (e != cudaErrorNotReady) { DVC_CHECK_CUDA(e); }
+  }
+  cudaGetLastError();      // cudaErrorNotReady is not sticky, but keep the thread's last-error slot clean
+  return found;
+}
+
+extern "C" int dvc_mbx_worker_enqueue(const dvc_mbx_desc* desc, uint32_t expect_seq, const uint8_t* arena_base,
+                                      const uint8_t* local_src, dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* h_status,
+                                      unsigned long long timeout_ns, void* graph_exec, void* event, void* stream) {
+  if (desc) {
+    int rc = dvc_mbx_wait_desc(desc, expect_seq, arena_base, local_src, ctl, h_status, timeout_ns, stream);
+    if (rc) return rc;
+  }
+  if (graph_exec) DVC_CHECK_CUDA(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream));
+  if (event) DVC_CHECK_CUDA(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
+  return DVC_OK;
+}
+
+extern "C" int dvc_mbx_local_dispatch(void* desc_ptr, const dvc_mbx_desc* h_desc, const uint8_t* arena_base,
+                                      const uint8_t* local_src, dvc_mbx_lane_ctl* ctl, void* graph_exec, void* done_ptr,
+                                      dvc_mbx_host_status* h_status, unsigned long long timeout_ns, const void* d_result,
+                                      void* h_result, size_t result_bytes, void* event, void* stream) {
+  DVC_REQUIRE(desc_ptr && h_desc && ctl && graph_exec && done_ptr, "mbx_local_dispatch: missing argument");
+  void* dp[1] = {desc_ptr};
+  int rc = dvc_mbx_post(dp, h_desc, 1, stream);
+  if (rc) return rc;
+  rc = dvc_mbx_wait_desc(reinterpret_cast<const dvc_mbx_desc*>(desc_ptr), h_desc->seq, arena_base, local_src, ctl, nullptr,
+                         1000000ull, stream);
+  if (rc) return rc;
+  DVC_CHECK_CUDA(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream));
+  void* wp[1] = {done_ptr};
+  const uint32_t sq[1] = {h_desc->seq};
+  rc = dvc_mbx_wait_done(wp, sq, 1, h_status, timeout_ns, stream);
+  if (rc) return rc;
+  if (h_result && result_bytes) DVC_CHECK_CUDA(cudaMemcpyAsync(h_result, d_result, result_bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  if (event) DVC_CHECK_CUDA(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
+  return DVC_OK;
+}
+
 extern "C" int dvc_mbx_signal(uint32_t* word, uint32_t value, void* stream) {
   DVC_REQUIRE(word, "mbx_signal: null word");
   mbx_signal_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(word, value);

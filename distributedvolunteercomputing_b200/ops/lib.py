@@ -103,6 +103,9 @@ _SIGS = {
     "dvc_mbx_wait_done": ([_P, _P, _I, _P, C.c_ulonglong, _P], _I),
     "dvc_mbx_dispatch": ([_P, _P, _SZ, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _SZ, _P, _P], _I),
     "dvc_mbx_signal": ([_P, _U32, _P], _I),
+    "dvc_mbx_poll": ([_P, _P, _I, _P], _I),
+    "dvc_mbx_worker_enqueue": ([_P, _U32, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _P], _I),
+    "dvc_mbx_local_dispatch": ([_P, _P, _P, _P, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _SZ, _P, _P], _I),
     "dvc_mbx_copy_out": ([_P, _P, _SZ, _P, _P], _I),
     "dvc_plan_set_mailbox": ([_P, _P, _P, _P, _P, _P], _I),
     "dvc_resize_u8_indirect": ([_P, _LL, _I, _I, _I, _P, _LL, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _P, _P, _P], _I),

@@ -194,6 +194,16 @@ class WorkerLanes:
             self.graphs[l] = g
         g.replay()
 
+    def graph_exec(self, l: int) -> Optional[int]:
+        """The lane's instantiated CUDA graph (cudaGraphExec_t) for native launches; None when graphs are off."""
+        if not self.engine.cfg.use_cuda_graph:
+            return None
+        if l not in self.graphs:
+            with torch.cuda.device(self.dev), torch.cuda.stream(self.streams[l]):
+                self.enqueue_body(l)
+            torch.cuda.synchronize(self.dev)
+        return int(self.graphs[l].raw_cuda_graph_exec())
+
     def _enqueue_body_eager(self, l: int):
         from ..ops import kernels as K
         st, lay, cp = self.states[l], self.layout, self.ctl_ptr(l)
@@ -259,9 +269,41 @@ class WorkerLanes:
         served0 = self.served
         self._first_ev = self._last_ev = None
 
+        gexec = [self.graph_exec(l) for l in range(nl)]
+        lib = self.engine.lib
+        desc_addr = [lay.desc_addr(self.ctl_base, self.worker, l) for l in range(nl)]
+        local_ptr = [self.local_raw[l].data_ptr() for l in range(nl)]
+        sptr = [st_.cuda_stream for st_ in self.streams]
+        hs_sz = HS_DTYPE.itemsize
+
         def push(l: int, kind: str):
             nonlocal fed
             idx = free_hs[l].pop() if kind != "body" else -1
+            if gexec[l] is not None and local_feed is None and (kind != "body" or self._first_ev is not None):
+                # hot path: [wait] -> [graph] -> event in ONE native call on the lane's stream
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record(self.streams[l])                       # materialise the event handle (cheap), re-recorded below
+                if kind != "body":
+                    self.hs[idx]["status"] = 0xFFFF
+                    if kind == "full" and self._first_ev is None:
+                        # first batch of this serve(): the busy span starts after its wait (two calls, once)
+                        L.check(lib.dvc_mbx_worker_enqueue(desc_addr[l], 0, self.arena_base, local_ptr[l], self.ctl_ptr(l),
+                                                           self.hs_addr + idx * hs_sz, int(stream_timeout_s * 1e9), None, None,
+                                                           sptr[l]), "mbx_worker_enqueue")
+                        self._first_ev = torch.cuda.Event(enable_timing=True)
+                        self._first_ev.record(self.streams[l])
+                        L.check(lib.dvc_mbx_worker_enqueue(None, 0, None, None, None, None, 0, gexec[l], ev.cuda_event, sptr[l]),
+                                "mbx_worker_enqueue")
+                    else:
+                        tmo = int((stream_timeout_s if kind == "full" else probe_timeout_s) * 1e9)
+                        L.check(lib.dvc_mbx_worker_enqueue(desc_addr[l], 0, self.arena_base, local_ptr[l], self.ctl_ptr(l),
+                                                           self.hs_addr + idx * hs_sz, tmo, gexec[l] if kind == "full" else None,
+                                                           ev.cuda_event, sptr[l]), "mbx_worker_enqueue")
+                else:
+                    L.check(lib.dvc_mbx_worker_enqueue(None, 0, None, None, None, None, 0, gexec[l], ev.cuda_event, sptr[l]),
+                            "mbx_worker_enqueue")
+                queues[l].append((kind, idx, ev))
+                return
             with torch.cuda.stream(self.streams[l]):
                 if kind != "body":
                     if local_feed is not None:
@@ -387,6 +429,11 @@ class ClientBox:
         # one process driving several GPUs from several threads must re-select the device in the library's own CUDA
         # runtime on every call; a process that only ever uses the client's GPU (torchrun, spawned workers) need not
         self._set_device_each_call = False
+        self._local_gexec: Dict[Tuple[int, int], int] = {}
+        n_ev = max_workers * lanes
+        self._ev_arr = (C.c_void_p * n_ev)(*[self.events[k].cuda_event for k in range(n_ev)])
+        self._busy_arr = (C.c_ubyte * n_ev)()
+        self._done_arr = (C.c_ubyte * n_ev)()
         self.local: Dict[int, WorkerLanes] = {}        # workers living on the client's own GPU (same process)
         self._views: Dict[int, Dict[str, np.ndarray]] = {}
         self.dispatches = 0
@@ -496,6 +543,18 @@ class ClientBox:
             return
         # the client's own GPU works too: same kernels, same words, queued inline on the same stream (a wait never spins
         # on something a later launch of this GPU has to produce)
+        gexec = self._local_gexec.get((worker, lane))
+        if gexec is None and loc.engine.cfg.use_cuda_graph:
+            gexec = self._local_gexec[(worker, lane)] = loc.graph_exec(lane)
+        if gexec is not None and host_src is None:
+            rc = self.lib.dvc_mbx_local_dispatch(c["desc_addr"], c["desc_ref"], self.arena.ptr, loc.local_raw[lane].data_ptr(),
+                                                 loc.ctl_ptr(lane), gexec, c["done_addr"], hs, tmo, res,
+                                                 c["h_res"] if fetch else None, lay.copy_bytes, c["event"], c["stream"])
+            if rc:
+                L.check(rc, "mbx_local_dispatch")
+            self.busy[worker][lane] = True
+            self.dispatches += 1
+            return
         with torch.cuda.device(self.dev), torch.cuda.stream(stream):
             L.set_device(self.dev)
             if host_src is not None and kind == 1:
@@ -525,6 +584,31 @@ class ClientBox:
             return None
         self.busy[worker][lane] = False
         return "ok" if int(self.hs[k]["status"]) == L.MBX_GO else "timeout"
+
+    def poll_all(self) -> List[Tuple[int, int, str]]:
+        """Every busy lane whose dispatch has finished since the last call, as (worker, lane, "ok" | "timeout"); one
+        native call queries all events."""
+        lanes = self.layout.lanes
+        n = len(self._busy_arr)
+        busy = self.busy
+        any_busy = False
+        for k in range(n):
+            b = busy[k // lanes][k % lanes]
+            self._busy_arr[k] = b
+            any_busy = any_busy or b
+        if not any_busy:
+            return []
+        found = self.lib.dvc_mbx_poll(self._ev_arr, self._busy_arr, n, self._done_arr)
+        if found < 0:
+            L.check(found, "mbx_poll")
+        out = []
+        if found:
+            for k in range(n):
+                if self._done_arr[k]:
+                    w, l = divmod(k, lanes)
+                    busy[w][l] = False
+                    out.append((w, l, "ok" if int(self._hs_status[k]) == L.MBX_GO else "timeout"))
+        return out
 
     def wait_ns(self, worker: int, lane: int) -> int:
         return int(self.hs[worker * self.layout.lanes + lane]["wait_ns"])
@@ -705,12 +789,12 @@ class ElasticBox:
         """Retire finished dispatches, then dispatch as much queued work as the workers' credits allow.
         Returns the number of batches completed by this call."""
         done = 0
-        for key in list(self.flights.keys()):
-            fl = self.flights[key]
-            r = self.client.poll(fl.worker, fl.lane)
-            if r is None:
-                continue
-            del self.flights[key]
+        if hasattr(self.client, "poll_all"):
+            finished = [((w, l), r) for w, l, r in self.client.poll_all() if (w, l) in self.flights]
+        else:
+            finished = [(key, r) for key, r in ((key, self.client.poll(*key)) for key in list(self.flights.keys())) if r is not None]
+        for key, r in finished:
+            fl = self.flights.pop(key)
             if fl.cancelled:
                 continue
             if r == "ok":

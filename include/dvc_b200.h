@@ -317,6 +317,19 @@ int dvc_mbx_dispatch(const void* h_src, void* d_dst, size_t src_bytes, void* des
                      const void* d_result, void* h_result, size_t result_bytes, void* event, void* stream);
 /* Device->host copy of a result slot into pinned memory, then cudaEventRecord(event) (event may be NULL). */
 int dvc_mbx_copy_out(const void* d_result, void* h_result, size_t bytes, void* event, void* stream);
+/* Host-side helpers that fold what would be several Python-level CUDA calls into one (the client dispatches ~10^4
+ * batches a second on a full box).  dvc_mbx_poll: cudaEventQuery over n events, h_done[i] = 1 where busy and finished,
+ * returns how many.  dvc_mbx_worker_enqueue: [wait for a descriptor] -> [launch the lane's CUDA graph] -> [record event];
+ * NULL switches a step off.  dvc_mbx_local_dispatch: the client's own GPU as a worker, everything on one stream:
+ * post -> wait_desc (immediate) -> graph -> wait_done -> copy-out -> event. */
+int dvc_mbx_poll(void* const* h_events, const unsigned char* h_busy, int n, unsigned char* h_done);
+int dvc_mbx_worker_enqueue(const dvc_mbx_desc* desc, uint32_t expect_seq, const uint8_t* arena_base, const uint8_t* local_src,
+                           dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* h_status, unsigned long long timeout_ns,
+                           void* graph_exec, void* event, void* stream);
+int dvc_mbx_local_dispatch(void* desc_ptr, const dvc_mbx_desc* h_desc, const uint8_t* arena_base, const uint8_t* local_src,
+                           dvc_mbx_lane_ctl* ctl, void* graph_exec, void* done_ptr, dvc_mbx_host_status* h_status,
+                           unsigned long long timeout_ns, const void* d_result, void* h_result, size_t result_bytes,
+                           void* event, void* stream);
 /* st.release.sys of one word (epoch bump, hand-rolled completion after an extra copy). */
 int dvc_mbx_signal(uint32_t* word, uint32_t value, void* stream);
 /* Bind a plan to a lane: K1b's gate reads ctl->gate_now / gate_expect, K9 takes its flag value from ctl->flag_value,

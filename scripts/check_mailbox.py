@@ -119,12 +119,16 @@ def main():
 
     # ---- 4. SIGKILL mid-stream
     victim = n - 1
-    ids = [box.submit_host(pool[k % len(pool)], range(B)).batch_id for k in range(40 * n)]
+    ids = [box.submit_host(pool[k % len(pool)], range(B)).batch_id for k in range(20 * n)]
     for _ in range(200):
         box.pump()
     p, conn = box.procs.pop(victim)
     os.kill(p.pid, signal.SIGKILL)
     f0 = len(box.failed_workers)
+    k0 = len(ids)
+    while victim in box.workers_alive() and len(ids) < k0 + 400 * n:      # the scheduler still believes in the victim:
+        ids.append(box.submit_host(pool[len(ids) % len(pool)], range(B)).batch_id)    # keep the stream going until it is found
+        box.pump()
     assert box.drain(60.0), box.stats
     per = check(ids, "kill")
     assert victim in box.failed_workers[f0:], "the killed worker was never declared dead"

@@ -42,13 +42,14 @@ class FakeClient:
                 return "timeout"
             return None
         if f[0] >= self.latency:
-            self.last = f
+            self.done = getattr(self, "done", {})
+            self.done[(w, lane)] = f
             del self.flight[(w, lane)]
             return "ok"
         return None
 
     def result(self, w, lane):
-        return {"batch_id": self.last[1]}
+        return {"batch_id": self.done[(w, lane)][1]}
 
     def cancel(self, w, lane):
         f = self.flight.get((w, lane))
