@@ -46,15 +46,6 @@ def run(args, metric: str):
         x = F.interpolate(x, size=(300, 300), mode="bilinear", align_corners=False).round()
         return ((x - mean) * 0.007843).half().contiguous(memory_format=torch.channels_last)
 
-    static_in = torch.zeros((B, 3, 300, 300), dtype=torch.float16, device=dev).contiguous(memory_format=torch.channels_last)
-    with torch.no_grad():
-        for _ in range(3):
-            loc, conf = model(static_in)
-        torch.cuda.synchronize()
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            loc, conf = model(static_in)
-
     def postprocess(loc, conf):
         prob = conf.float().softmax(-1)
         l = loc.float()
@@ -86,13 +77,29 @@ def run(args, metric: str):
         out[..., 3:7] = torch.gather(bx.view(B, 2000, 4), 1, flat[..., None].expand(-1, -1, 4)) * (best > 0)[..., None]
         return out
 
+    # The WHOLE step is one CUDA graph: preprocessing, the cuDNN network and the post-processing (the greedy NMS is a
+    # fixed 100-iteration loop of tensor ops, so it captures) - the baseline pays no eager launch latency either.
+    static_raw = torch.zeros((B, H, W, 3), dtype=torch.uint8, device=dev)
+    with torch.no_grad():
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                loc, conf = model(preprocess(static_raw))
+                static_det = postprocess(loc, conf)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            loc, conf = model(preprocess(static_raw))
+            static_det = postprocess(loc, conf)
+
     rng = np.random.default_rng(100 + rank)
     pool_n = 8
     total_B = B * world
     if rank == 0:
         host_pool = torch.from_numpy(rng.integers(0, 256, (pool_n, total_B, H, W, 3), dtype=np.uint8)).pin_memory()
         dev_pool = host_pool.to(dev)
-    mine = torch.empty((B, H, W, 3), dtype=torch.uint8, device=dev)
     gathered = [torch.empty((B, 100, 7), device=dev) for _ in range(world)] if rank == 0 else None
     host_det = torch.empty((total_B, 100, 7)).pin_memory() if rank == 0 else None
 
@@ -100,13 +107,11 @@ def run(args, metric: str):
         with torch.no_grad():
             if multi:
                 chunks = list(src_pool[i % pool_n].view(world, B, H, W, 3).unbind(0)) if rank == 0 else None
-                dist.scatter(mine, chunks, src=0)
-                raw = mine
+                dist.scatter(static_raw, chunks, src=0)
             else:
-                raw = src_pool[i % pool_n]
-            static_in.copy_(preprocess(raw))
+                static_raw.copy_(src_pool[i % pool_n], non_blocking=True)
             g.replay()
-            det = postprocess(loc, conf)
+            det = static_det
             if multi:
                 dist.gather(det, gathered, dst=0)
             return det
@@ -160,7 +165,8 @@ def run(args, metric: str):
             "impl": "torch",
             "config": {"model": "MobileNet-SSD 300x300 (torch cuDNN channels_last fp16 + CUDA graph)", "global_batch": total_B,
                        "seq_len": None, "frame_hw": [H, W], "parallelism": f"dp{world} nccl scatter/gather",
-                       "nms": "per-class top-100 + vectorised greedy NMS in torch ops"},
+                       "nms": "per-class top-100 + vectorised greedy NMS in torch ops",
+                       "cuda_graph": "whole step (preprocess + network + post-processing) is one graph replay"},
             "e2e": {"value": round(frames / (float(t[1]) / 1e3), 1), "unit": "frames/s",
                     "h2d_bytes_per_step": int(total_B * H * W * 3), "d2h_bytes_per_step": int(total_B * 100 * 7 * 4)},
             "gpu_launches": 0, "clocks": clocks}), flush=True)
