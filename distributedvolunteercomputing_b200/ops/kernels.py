@@ -172,20 +172,24 @@ def gemm_head(a: torch.Tensor, wt: torch.Tensor, bias: torch.Tensor, loc: torch.
                                   block_n, L.stream_ptr(stream)), "gemm_head")
 
 
-def dwpw_fused_s1(x: torch.Tensor, wdw_9c: torch.Tensor, bdw: torch.Tensor, wpw: torch.Tensor, bpw: torch.Tensor,
-                  out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
-    """EXPERIMENTAL (csrc/dwpw_fused.cu: bit-identical to dwconv3x3 + gemm_f16 on small shapes in its one hardware run, not
-    yet timed, unused by the engine): depthwise 3x3
-    stride 1 + ReLU fused into the pointwise 1x1 + ReLU of the same block.  x [B,H,W,C_in] fp16 -> [B,H,W,C_out] fp16."""
+def dwpw_fused(x: torch.Tensor, wdw_9c: torch.Tensor, bdw: torch.Tensor, wpw: torch.Tensor, bpw: torch.Tensor, stride: int = 1,
+               out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
+    """Depthwise 3x3 (stride 1 or 2) + ReLU fused into the pointwise 1x1 + ReLU of the same block (csrc/dwpw_fused.cu).
+    x [B,H,W,C_in] fp16 -> [B,Ho,Wo,C_out] fp16."""
     assert x.dtype == torch.float16 and x.is_cuda and x.dim() == 4 and x.is_contiguous()
     assert wpw.dtype == torch.float16 and wpw.is_contiguous() and wpw.shape[1] == x.shape[3]
     B, H, W, C_in = x.shape
     C_out = wpw.shape[0]
+    Ho, Wo = (H + 2 - 3) // stride + 1, (W + 2 - 3) // stride + 1
     if out is None:
-        out = torch.empty((B, H, W, C_out), dtype=torch.float16, device=x.device)
-    L.check(L.load().dvc_dwpw_fused_s1(L.ptr(x), B, H, W, C_in, L.ptr(wdw_9c), L.ptr(bdw), L.ptr(wpw), L.ptr(bpw), C_out,
-                                       L.ptr(out), L.stream_ptr(stream)), "dwpw_fused_s1")
+        out = torch.empty((B, Ho, Wo, C_out), dtype=torch.float16, device=x.device)
+    L.check(L.load().dvc_dwpw_fused(L.ptr(x), B, H, W, C_in, stride, L.ptr(wdw_9c), L.ptr(bdw), L.ptr(wpw), L.ptr(bpw), C_out,
+                                    L.ptr(out), L.stream_ptr(stream)), "dwpw_fused")
     return out
+
+
+def dwpw_fused_s1(x, wdw_9c, bdw, wpw, bpw, out=None, stream=None) -> torch.Tensor:
+    return dwpw_fused(x, wdw_9c, bdw, wpw, bpw, 1, out, stream)
 
 
 # ------------------------------------------------------------------------------------ K6..K10

@@ -214,12 +214,13 @@ int dvc_plan_set_timestamps(dvc_plan*, unsigned long long* t_ingest, unsigned lo
 int dvc_plan_set_epoch_gate(dvc_plan*, const uint32_t* epoch_now, const uint32_t* epoch_expect, uint32_t* stale_count);
 int dvc_plan_run(dvc_plan*, void* stream);
 
-/* EXPERIMENTAL - bit-identical to dvc_dwconv3x3 + dvc_gemm_f16 on small shapes in its one hardware run, not yet timed
- * at the flagship shapes, not used by the plan executor (csrc/dwpw_fused.cu).
- * Fused depthwise 3x3 stride 1 (+bias+ReLU) -> pointwise 1x1 (+bias+ReLU) of one MobileNet block; the intermediate
- * stays in shared memory as the A operand of tcgen05.mma.  No reference counterpart (the reference runs cv2.dnn).
- * in [B,H,W,C_in] fp16, wdw [9][C_in] fp32, bdw [C_in], wpw [C_out][C_in] fp16, bpw [C_out], out [B,H,W,C_out] fp16;
- * C_in = 32 or a multiple of 64, C_out in {64,128,192,256}. */
+/* Fused depthwise 3x3 (pad 1, stride 1 or 2, +bias+ReLU) -> pointwise 1x1 (+bias+ReLU) of one MobileNet block
+ * (prototxt:42-106 ... 302-366); the intermediate stays in shared memory as the A operand of tcgen05.mma and the
+ * tensor work hides behind the depthwise arithmetic (csrc/dwpw_fused.cu).  The reference runs these as two cv2.dnn
+ * layers.  in [B,H,W,C_in] fp16, wdw [9][C_in] fp32, bdw [C_in], wpw [C_out][C_in] fp16, bpw [C_out],
+ * out [B,Ho,Wo,C_out] fp16; C_in = 32 or a multiple of 64, C_out in {64,128,192,256}. */
+int dvc_dwpw_fused(const void* in_f16, int B, int H, int W, int C_in, int stride, const float* wdw, const float* bdw,
+                   const void* wpw_f16, const float* bpw, int C_out, void* out_f16, void* stream);
 int dvc_dwpw_fused_s1(const void* in_f16, int B, int H, int W, int C_in, const float* wdw, const float* bdw,
                       const void* wpw_f16, const float* bpw, int C_out, void* out_f16, void* stream);
 

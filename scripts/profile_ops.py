@@ -13,8 +13,8 @@ raw = torch.from_numpy(rng.integers(0, 256, (64, 300, 300, 3), dtype=np.uint8)).
 t_area = K.make_area_tables(300, 300, 400, 400, dev)
 w27 = torch.randn((27, 32), device=dev) * 0.2; b32 = torch.randn((32,), device=dev) * 0.1
 def rnd(*s): return torch.randn(s, device=dev).half()
-x1 = rnd(16, 150, 150, 32); w1 = torch.randn((9, 32), device=dev); bb1 = torch.randn((32,), device=dev)
-a1 = rnd(16 * 22500, 32); wt1 = rnd(64, 32); bias1 = torch.randn((64,), device=dev)
+x1 = rnd(64, 150, 150, 32); w1 = torch.randn((9, 32), device=dev); bb1 = torch.randn((32,), device=dev)
+a1 = rnd(64 * 22500, 32); wt1 = rnd(64, 32); bias1 = torch.randn((64,), device=dev)
 x7 = rnd(64, 19, 19, 512); w7 = torch.randn((9, 512), device=dev); bb7 = torch.randn((512,), device=dev)
 a7 = rnd(64 * 361, 512); wt7 = rnd(512, 512) * 0.05; bias7 = torch.randn((512,), device=dev)
 a13 = rnd(6400, 1024); wt13 = rnd(1024, 1024) * 0.03; bias13 = torch.randn((1024,), device=dev)
@@ -27,7 +27,7 @@ idm, ixy, lm, lxy = A.text_masks("127.0.0.1:5554", 400, 400)
 masks = K.TextMasks(torch.from_numpy(idm).to(dev), ixy, torch.from_numpy(lm).to(dev), lxy)
 def once():
     f400 = K.resize_u8(raw, t_area)
-    K.preproc_conv0(f400[:16], w27, b32)
+    K.preproc_conv0(f400, w27, b32)
     K.dwconv3x3(x1, w1, bb1, 1, True)
     K.gemm_f16(a1, wt1, bias1, True)
     K.dwconv3x3(x7, w7, bb7, 1, True)

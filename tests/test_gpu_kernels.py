@@ -100,6 +100,31 @@ def test_dwconv_matches_fp32(K, B, H, W, C, stride):
     assert (out.float() - ref).abs().max().item() <= 3e-3 * max(1.0, ref.abs().max().item())
 
 
+@pytest.mark.parametrize("B,H,W,Cin,Cout,stride", [
+    (4, 150, 150, 32, 64, 1), (3, 75, 75, 128, 128, 1), (4, 38, 38, 256, 256, 1),          # conv1 / conv3 / conv5 (overhanging tiles)
+    (3, 150, 150, 64, 128, 2), (3, 75, 75, 128, 256, 2),                                   # conv2 / conv4 (stride 2)
+    (1, 8, 16, 64, 64, 1), (2, 23, 37, 256, 192, 1), (2, 19, 19, 128, 256, 2), (1, 23, 37, 64, 64, 2)])
+def test_dwpw_fused_matches_fp32_and_two_kernel_path(K, B, H, W, Cin, Cout, stride):
+    """Fused depthwise 3x3 -> pointwise 1x1 (csrc/dwpw_fused.cu) against an fp32 restatement (the intermediate rounded
+    to fp16 like both GPU paths do) and bit for bit against dwconv3x3 -> gemm_f16."""
+    x = _rand((B, H, W, Cin), 1.0, 40).half().to(DEV)
+    wdw = _rand((9, Cin), 0.3, 41).to(DEV)
+    bdw = _rand((Cin,), 0.2, 42).to(DEV)
+    wpw = (_rand((Cout, Cin), 1.0, 43) / Cin ** 0.5).half().to(DEV)
+    bpw = _rand((Cout,), 0.2, 44).to(DEV)
+    mid = K.dwconv3x3(x, wdw, bdw, stride, True)
+    Ho, Wo = mid.shape[1], mid.shape[2]
+    two = K.gemm_f16(mid.view(-1, Cin), wpw, bpw, True).view(B, Ho, Wo, Cout)
+    fused = K.dwpw_fused(x, wdw, bdw, wpw, bpw, stride)
+    torch.cuda.synchronize()
+    w4 = wdw.t().reshape(Cin, 1, 3, 3)
+    m32 = torch.relu(F.conv2d(x.float().permute(0, 3, 1, 2), w4, bdw, padding=1, stride=stride, groups=Cin)).half().float()
+    ref = torch.relu(m32.permute(0, 2, 3, 1).reshape(-1, Cin) @ wpw.float().t() + bpw).view(B, Ho, Wo, Cout)
+    assert fused.shape == ref.shape
+    assert (fused.float() - ref).abs().max().item() <= 3e-3 * max(1.0, ref.abs().max().item()) + 2e-3
+    assert torch.equal(fused, two)
+
+
 @pytest.mark.parametrize("B,H,W,C", [(2, 10, 10, 256), (3, 5, 5, 128), (2, 3, 3, 128), (4, 2, 2, 64)])
 def test_im2col_matches_unfold(K, B, H, W, C):
     x = _rand((B, H, W, C), 1.0, 10).half().to(DEV)
