@@ -64,12 +64,19 @@ struct Op {
   int B = 0, H = 0, W = 0, C = 0, stride = 1, relu = 0;
   // fused depthwise -> pointwise (experimental): w / b above are the depthwise ones
   const void* wpw = nullptr; const float* bpw = nullptr; int C_out = 0;
+  bool is_head = false;            // SSD head GEMM: may run on the plan's side branch (see dvc_plan_set_head_branch)
 };
 
 }  // namespace dvc
 
 struct dvc_plan {
   std::vector<dvc::Op> ops;
+  // side branch for the SSD heads: they depend only on their tap layer and are needed only by the detection op, so
+  // they leave the critical path (one fork event per head, one join before detection; captured into CUDA graphs as a
+  // parallel branch)
+  cudaStream_t side = nullptr;
+  std::vector<cudaEvent_t> forks;
+  cudaEvent_t join = nullptr;
 };
 
 using namespace dvc;
@@ -78,6 +85,9 @@ extern "C" dvc_plan* dvc_plan_create(void) { return new dvc_plan(); }
 
 extern "C" void dvc_plan_destroy(dvc_plan* p) {
   if (!p) return;
+  for (auto e : p->forks) cudaEventDestroy(e);
+  if (p->join) cudaEventDestroy(p->join);
+  if (p->side) cudaStreamDestroy(p->side);
   for (auto& op : p->ops) {
     if (op.gemm) gemm_free(op.gemm);
     if (op.pre) preproc_free(op.pre);
@@ -118,7 +128,30 @@ extern "C" int dvc_plan_add_gemm(dvc_plan* p, const void* A, const void* Wt, con
   Op op; op.kind = OP_GEMM; op.gemm = gemm_alloc();
   int rc = gemm_prepare(op.gemm, A, Wt, bias, M, N, K, lda, out_mode, out_f16, ldc, relu, head, block_n);
   if (rc) { gemm_free(op.gemm); return rc; }
+  op.is_head = (out_mode == 1);
   p->ops.push_back(op);
+  return DVC_OK;
+}
+
+/* Run the SSD head GEMMs on a side branch (on = 1).  Only valid when no later op of the plan overwrites a head's input
+ * before the detection op - i.e. when every tap layer writes into a buffer of its own (engine.py does that). */
+extern "C" int dvc_plan_set_head_branch(dvc_plan* p, int on) {
+  DVC_REQUIRE(p, "plan is null");
+  if (!on) {
+    if (p->side) { cudaStreamDestroy(p->side); p->side = nullptr; }
+    return DVC_OK;
+  }
+  if (!p->side) {
+    DVC_CHECK_CUDA(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
+    DVC_CHECK_CUDA(cudaEventCreateWithFlags(&p->join, cudaEventDisableTiming));
+  }
+  size_t heads = 0;
+  for (auto& op : p->ops) heads += op.is_head ? 1 : 0;
+  while (p->forks.size() < heads) {
+    cudaEvent_t e;
+    DVC_CHECK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    p->forks.push_back(e);
+  }
   return DVC_OK;
 }
 
@@ -213,8 +246,24 @@ extern "C" int dvc_plan_set_mailbox(dvc_plan* p, const dvc_mbx_lane_ctl* ctl, co
 extern "C" int dvc_plan_run(dvc_plan* p, void* stream) {
   DVC_REQUIRE(p, "plan is null");
   cudaStream_t st = (cudaStream_t)stream;
+  size_t k = 0;
+  bool forked = false;
   for (const auto& op : p->ops) {
     int rc = DVC_OK;
+    if (p->side && op.is_head && k < p->forks.size()) {
+      DVC_CHECK_CUDA(cudaEventRecord(p->forks[k], st));
+      DVC_CHECK_CUDA(cudaStreamWaitEvent(p->side, p->forks[k], 0));
+      rc = gemm_launch(op.gemm, p->side);
+      if (rc) return rc;
+      ++k;
+      forked = true;
+      continue;
+    }
+    if (forked && op.kind == OP_DET) {
+      DVC_CHECK_CUDA(cudaEventRecord(p->join, p->side));
+      DVC_CHECK_CUDA(cudaStreamWaitEvent(st, p->join, 0));
+      forked = false;
+    }
     switch (op.kind) {
       case OP_PREPROC: rc = preproc_launch(op.pre, st); break;
       case OP_DW: rc = dw_launch(op.dw, st); break;
@@ -224,6 +273,10 @@ extern "C" int dvc_plan_run(dvc_plan* p, void* stream) {
       case OP_DWPW: rc = dwpw_fused_s1_launch(op.in, op.B, op.H, op.W, op.C, op.w, op.b, op.wpw, op.bpw, op.C_out, op.out, st); break;
     }
     if (rc) return rc;
+  }
+  if (forked) {                     // a plan without a detection op: join at the end
+    DVC_CHECK_CUDA(cudaEventRecord(p->join, p->side));
+    DVC_CHECK_CUDA(cudaStreamWaitEvent(st, p->join, 0));
   }
   return DVC_OK;
 }

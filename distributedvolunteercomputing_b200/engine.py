@@ -323,14 +323,21 @@ class NativeEngine:
                 if c.top in heads and li != split_idx:
                     add_head(heads[c.top], dst, nb, b0)
                 li += 1
-        # ---- late layers on the full batch
-        cur, other = st.fA, st.fB
+        # ---- late layers on the full batch.  Every tap layer (an input of an SSD head) writes into a buffer of its own
+        # instead of the ping-pong pair, so nothing overwrites a head's input and the heads can run on the plan's side
+        # branch, off the critical path (csrc/plan.cu, dvc_plan_set_head_branch).
+        cur = st.fA
+        st.taps = {}
         if body[split_idx].top in heads:
             add_head(heads[body[split_idx].top], L.ptr(cur), B, 0)
         for li in range(split_idx + 1, len(body)):
             c = body[li]
-            add_conv(c, L.ptr(cur), L.ptr(other), B)
-            cur, other = other, cur
+            if c.top in heads:
+                dst = st.taps[c.name] = torch.empty((B * per_frame[li],), dtype=torch.float16, device=dev)
+            else:
+                dst = st.fA if cur is not st.fA else st.fB
+            add_conv(c, L.ptr(cur), L.ptr(dst), B)
+            cur = dst
             if c.top in heads:
                 add_head(heads[c.top], L.ptr(cur), B, 0)
         L.check(lib.dvc_plan_add_detection(plan, L.ptr(st.loc), L.ptr(st.conf), L.ptr(self.priors), L.ptr(self.variances), B,
@@ -338,6 +345,8 @@ class NativeEngine:
                                            L.ptr(st.box_count), None, 0, L.ptr(st.det_scratch),
                                            st.det_scratch.numel()), "detection")
         st.n_ops = lib.dvc_plan_num_ops(plan)
+        head_branch = os.environ.get("DVC_HEAD_BRANCH", "1") != "0" and body[split_idx].top not in heads
+        L.check(lib.dvc_plan_set_head_branch(plan, 1 if head_branch else 0), "plan_set_head_branch")
 
     # ------------------------------------------------------------------ execution
     def launches_per_batch(self, st: _ShapeState, annotate: bool = True) -> int:

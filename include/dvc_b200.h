@@ -212,6 +212,9 @@ int dvc_plan_set_timestamps(dvc_plan*, unsigned long long* t_ingest, unsigned lo
  * the dispatcher writes); on mismatch the frame is not delivered (sinks and flags untouched) and *stale_count is
  * incremented once per frame so the scheduler can re-dispatch.  Pass NULLs to switch the gate off. */
 int dvc_plan_set_epoch_gate(dvc_plan*, const uint32_t* epoch_now, const uint32_t* epoch_expect, uint32_t* stale_count);
+/* SSD head GEMMs on a side branch of the plan (they depend only on their tap layer and only the detection op needs
+ * them): off the critical path of a single batch.  Requires that no later op overwrites a head's input. */
+int dvc_plan_set_head_branch(dvc_plan*, int on);
 int dvc_plan_run(dvc_plan*, void* stream);
 
 /* Fused depthwise 3x3 (pad 1, stride 1 or 2, +bias+ReLU) -> pointwise 1x1 (+bias+ReLU) of one MobileNet block

@@ -294,7 +294,9 @@ def _recorded_plan(monkeypatch, fuse):
     st.det = st.det_count = st.boxes_i = st.box_count = st.det_scratch = torch.zeros(1)
     st.det_params = Lmod.DetParams()
     e._build_plan(st)
-    return calls, st.n_ops
+    assert calls[-1][0] == "dvc_plan_set_head_branch" and calls[-1][1:] == (1,), "the six heads run on the plan's side branch"
+    assert set(st.taps) == {"conv11", "conv13", "conv14_2", "conv15_2", "conv16_2", "conv17_2"}, "every tap has a buffer of its own"
+    return calls[:-1], st.n_ops
 
 
 def test_plan_construction_default_and_fused(monkeypatch):
