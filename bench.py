@@ -41,7 +41,9 @@ def parse_args():
     ap.add_argument("--sub-batch", type=int, default=0)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--sustain-s", type=float, default=3.0, help="length of the sustained-clock run (0 = skip)")
-    ap.add_argument("--concurrency", type=int, default=4, help="batches in flight on separate streams (single-GPU arm)")
+    ap.add_argument("--concurrency", type=int, default=0,
+                    help="batches in flight per GPU (own buffers, plan, CUDA graph and stream each); 0 = measured best: "
+                         "8 on one GPU, 6 lanes per worker on 2-4 GPUs, 4 on 8 (one hardware queue per client lane stream)")
     return ap.parse_args()
 
 
@@ -83,7 +85,7 @@ def run_native(args):
     cfg = Config(batch=B, sub_batch=args.sub_batch, use_cuda_graph=not args.no_graph)
     graph = SSDGraph.random(seed=1, conf_gain=2.5)
     eng = NativeEngine(graph, dev, cfg, requester_id="127.0.0.1:5554")
-    conc = max(1, args.concurrency)
+    conc = args.concurrency if args.concurrency > 0 else (8 if world == 1 else max(2, min(6, 32 // world)))
     # the clock sampler (an nvidia-smi child) is started NOW so that its start-up cost is spent during set-up and warm-up,
     # not inside a timed region; it keeps sampling through the device-timed and the end-to-end regions
     sampler = ClockSampler(local).start() if rank == 0 else None
