@@ -43,7 +43,8 @@ def parse_args():
     ap.add_argument("--sustain-s", type=float, default=3.0, help="length of the sustained-clock run (0 = skip)")
     ap.add_argument("--concurrency", type=int, default=0,
                     help="batches in flight per GPU (own buffers, plan, CUDA graph and stream each); 0 = measured best: "
-                         "8 on one GPU, 6 lanes per worker on 2-4 GPUs, 4 on 8 (one hardware queue per client lane stream)")
+                         "8 on one GPU; 4 lanes per worker on several (more lanes gain ~2 % in a seconds-long run but lengthen the "
+                         "ramp of a 20-step window)")
     return ap.parse_args()
 
 
@@ -85,7 +86,7 @@ def run_native(args):
     cfg = Config(batch=B, sub_batch=args.sub_batch, use_cuda_graph=not args.no_graph)
     graph = SSDGraph.random(seed=1, conf_gain=2.5)
     eng = NativeEngine(graph, dev, cfg, requester_id="127.0.0.1:5554")
-    conc = args.concurrency if args.concurrency > 0 else (8 if world == 1 else max(2, min(6, 32 // world)))
+    conc = args.concurrency if args.concurrency > 0 else (8 if world == 1 else 4)
     # the clock sampler (an nvidia-smi child) is started NOW so that its start-up cost is spent during set-up and warm-up,
     # not inside a timed region; it keeps sampling through the device-timed and the end-to-end regions
     sampler = ClockSampler(local).start() if rank == 0 else None
