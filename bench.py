@@ -42,9 +42,9 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--sustain-s", type=float, default=3.0, help="length of the sustained-clock run (0 = skip)")
     ap.add_argument("--concurrency", type=int, default=0,
-                    help="batches in flight per GPU (own buffers, plan, CUDA graph and stream each); 0 = measured best: "
-                         "8 on one GPU; 4 lanes per worker on several (more lanes gain ~2 % in a seconds-long run but lengthen the "
-                         "ramp of a 20-step window)")
+                    help="batches in flight per GPU (own buffers, plan, CUDA graph and stream each); 0 = 4, the same per-GPU "
+                         "configuration at every N (measured: 8 lanes give +2 percent on one GPU, 6 give +2 percent in a seconds-long "
+                         "multi-GPU run but lengthen the ramp of a 20-step window; profiles/r2/bench_native_n*_c*.json)")
     return ap.parse_args()
 
 
@@ -86,7 +86,7 @@ def run_native(args):
     cfg = Config(batch=B, sub_batch=args.sub_batch, use_cuda_graph=not args.no_graph)
     graph = SSDGraph.random(seed=1, conf_gain=2.5)
     eng = NativeEngine(graph, dev, cfg, requester_id="127.0.0.1:5554")
-    conc = args.concurrency if args.concurrency > 0 else (8 if world == 1 else 4)
+    conc = args.concurrency if args.concurrency > 0 else 4
     # the clock sampler (an nvidia-smi child) is started NOW so that its start-up cost is spent during set-up and warm-up,
     # not inside a timed region; it keeps sampling through the device-timed and the end-to-end regions
     sampler = ClockSampler(local).start() if rank == 0 else None
