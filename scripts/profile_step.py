@@ -15,3 +15,19 @@ for i in range(steps):
     e.run(st)
 torch.cuda.synchronize()
 print("ops per step", e.launches_per_batch(st))
+
+if "mbx" in sys.argv:
+    # the same batch through the mailbox data plane (client GPU as its own worker, eager): post -> wait -> K1a -> plan
+    # -> K10 -> done-wait, so the launch list shows the flow-control kernels in place
+    from distributedvolunteercomputing_b200.parallel.mailbox import ClientBox, ElasticBox, WorkerLanes
+    client = ClientBox("cuda:0", B, 300, 300, max_workers=1, lanes=1, engine=e, done_timeout_s=1.0)
+    client.attach_local(0, WorkerLanes(e, client.layout, *client.bases(), worker=0))
+    box = ElasticBox(client)
+    box.add_worker(0)
+    slot = client.alloc_slot()
+    client.slot_tensor(slot).copy_(st.raw)
+    for i in range(2):
+        box.submit_slot(slot, range(B))
+        assert box.drain(10.0)
+    torch.cuda.synchronize()
+    print("mailbox steps ok", dict(box.stats))
