@@ -218,10 +218,14 @@ class NativeEngine:
         st.t_lin = K.make_linear_tables(st.h4, st.w4, P.NET_SIZE, P.NET_SIZE, dev)
         st.loc = torch.zeros((B, g.num_priors * 4), dtype=torch.float32, device=dev)
         st.conf = torch.zeros((B, g.num_priors * g.num_classes), dtype=torch.float32, device=dev)
-        st.det = torch.zeros((B, 100, 7), dtype=torch.float32, device=dev)
-        st.det_count = torch.zeros((B,), dtype=torch.int32, device=dev)
-        st.boxes_i = torch.zeros((B, 100, 4), dtype=torch.int32, device=dev)
-        st.box_count = torch.zeros((B,), dtype=torch.int32, device=dev)
+        # one contiguous result block (det | boxes | det_count | box_count): the pipelined API reads it back with ONE copy
+        o1, o2, o3, o4 = B * 2800, B * 2800 + B * 1600, B * 2800 + B * 1600 + B * 4, B * 2800 + B * 1600 + B * 8
+        st.res_flat = torch.zeros((o4,), dtype=torch.uint8, device=dev)
+        st.res_offsets = (o1, o2, o3, o4)
+        st.det = st.res_flat[:o1].view(torch.float32).view(B, 100, 7)
+        st.boxes_i = st.res_flat[o1:o2].view(torch.int32).view(B, 100, 4)
+        st.det_count = st.res_flat[o2:o3].view(torch.int32)
+        st.box_count = st.res_flat[o3:o4].view(torch.int32)
         st.flags = torch.zeros((B,), dtype=torch.int32, device=dev)
         st.det_scratch = torch.empty((K.detection_scratch_bytes(B, g.num_priors, g.num_classes),), dtype=torch.uint8, device=dev)
         st.det_params = K.det_params(g.det, g.num_priors, st.w4, st.h4, cfg.confidence, consider_ids(cfg.consider))
@@ -562,11 +566,13 @@ class NativeEngine:
                 rec = slots.get(key)
                 if rec is None:
                     st = self.state(B, H, W, rid, slot=1 + k)
-                    rec = {"st": st, "free": None,
-                           "h_det": torch.empty((B, 100, 7), dtype=torch.float32).pin_memory(),
-                           "h_cnt": torch.empty((B,), dtype=torch.int32).pin_memory(),
-                           "h_boxes": torch.empty((B, 100, 4), dtype=torch.int32).pin_memory(),
-                           "h_bcnt": torch.empty((B,), dtype=torch.int32).pin_memory(),
+                    o1, o2, o3, o4 = st.res_offsets
+                    h_res = torch.empty((o4,), dtype=torch.uint8).pin_memory()
+                    rec = {"st": st, "free": None, "h_res": h_res,
+                           "h_det": h_res[:o1].view(torch.float32).view(B, 100, 7),
+                           "h_boxes": h_res[o1:o2].view(torch.int32).view(B, 100, 4),
+                           "h_cnt": h_res[o2:o3].view(torch.int32),
+                           "h_bcnt": h_res[o3:o4].view(torch.int32),
                            "h_frames": torch.empty((B, st.h4, st.w4, 3), dtype=torch.uint8).pin_memory() if fetch_frames else None}
                     slots[key] = rec
                 # a slot is reused only after its previous result has been handed out
@@ -587,10 +593,7 @@ class NativeEngine:
                     ev_run.record(s_run)
                 with torch.cuda.stream(s_out):
                     s_out.wait_event(ev_run)
-                    rec["h_det"].copy_(st.det, non_blocking=True)
-                    rec["h_cnt"].copy_(st.det_count, non_blocking=True)
-                    rec["h_boxes"].copy_(st.boxes_i, non_blocking=True)
-                    rec["h_bcnt"].copy_(st.box_count, non_blocking=True)
+                    rec["h_res"].copy_(st.res_flat, non_blocking=True)      # det, boxes and both counts in one copy
                     if fetch_frames:
                         rec["h_frames"].copy_(st.frames400, non_blocking=True)
                     ev_out = torch.cuda.Event()
