@@ -241,7 +241,7 @@ class WorkerLanes:
     def serve(self, should_stop: Callable[[], bool] = lambda: False, max_batches: Optional[int] = None,
               stream_timeout_s: float = 0.003, probe_timeout_s: float = 0.0005, idle_sleep_s: float = 0.0002,
               local_feed: Optional[Callable[[int], torch.Tensor]] = None, expect_work: bool = False,
-              on_ready: Optional[Callable[[], None]] = None, synced: bool = False) -> int:
+              on_ready: Optional[Callable[[], None]] = None, synced: bool = False, throttle_s: float = 0.0) -> int:
         """Serve dispatches until the client posts stop, `should_stop()` turns true or `max_batches` were served.
 
         While batches keep arriving every lane has `depth` (wait + network) pairs queued on its stream, so the GPU never
@@ -352,6 +352,8 @@ class WorkerLanes:
                             else:
                                 self.served += 1
                                 self._last_ev = ev_done
+                                if throttle_s:
+                                    time.sleep(throttle_s)       # fault injection: a slow volunteer
                         else:
                             mode[l] = "idle"
                             self.idle_polls += 1
@@ -728,7 +730,7 @@ class ElasticBox:
         return [w for w, a in self.alive.items() if a]
 
     def spawn_workers(self, workers: Sequence[Tuple[int, int]], graph, cfg, stall_after: Optional[int] = None,
-                      ready_timeout_s: float = 300.0, local_feed_spec: Optional[Tuple] = None) -> None:
+                      ready_timeout_s: float = 300.0, local_feed_spec: Optional[Tuple] = None, delay_ms: float = 0.0) -> None:
         """Start one worker PROCESS per (worker index, device index) pair - all at once, they build their engines in
         parallel - and add each to the pool once its lanes are built."""
         import multiprocessing as mp
@@ -738,7 +740,7 @@ class ElasticBox:
             self.client.reset_worker(w)            # clears an earlier stop before the newcomer reads its position
             parent, child = ctx.Pipe()
             p = ctx.Process(target=worker_process_main,
-                            args=(self.client.export(), w, dev_index, graph, cfg, child, stall_after, local_feed_spec), daemon=True)
+                            args=(self.client.export(), w, dev_index, graph, cfg, child, stall_after, local_feed_spec, delay_ms), daemon=True)
             p.start()
             started.append((w, p, parent))
         deadline = time.monotonic() + ready_timeout_s
@@ -872,12 +874,12 @@ class ElasticBox:
 
 # ====================================================================================== process / thread front-ends
 def worker_process_main(export: Dict[str, Any], worker: int, device_index: int, graph, cfg, conn=None,
-                        stall_after: Optional[int] = None, local_feed_spec: Optional[Tuple] = None):
+                        stall_after: Optional[int] = None, local_feed_spec: Optional[Tuple] = None, delay_ms: float = 0.0):
     """Entry point of a spawned worker process (multiprocessing 'spawn'): map the client's box, adopt its weights,
     serve until told to stop; then wait on the pipe: "rejoin" serves again (workers leave and join at will,
     server.py:104-154), anything else ends the process.  "ready" goes out whenever the lanes are about to serve,
     ("served", batches, stale frames) whenever a membership ends.  `stall_after` (fault injection) makes the worker go
-    silent after that many batches.  `local_feed_spec` = ("synthetic", pool, seed): sharded ingest, the worker uploads
+    silent after that many batches, `delay_ms` makes it pause that long after every batch (a slow volunteer).  `local_feed_spec` = ("synthetic", pool, seed): sharded ingest, the worker uploads
     its own synthetic frames (a pinned pool of `pool` batches) instead of pulling them from the client."""
     from ..engine import NativeEngine
     torch.cuda.set_device(device_index)
@@ -900,7 +902,7 @@ def worker_process_main(export: Dict[str, Any], worker: int, device_index: int, 
 
     while True:
         ready = (lambda: conn.send(("ready", worker))) if conn is not None else None
-        n = lanes.serve(should_stop=stop, max_batches=stall_after, local_feed=feed, on_ready=ready)
+        n = lanes.serve(should_stop=stop, max_batches=stall_after, local_feed=feed, on_ready=ready, throttle_s=delay_ms / 1e3)
         if stall_after is not None:
             while not stop():          # injected stall: alive, mapped, silent
                 time.sleep(0.01)

@@ -5,6 +5,7 @@ process owns GPU 0 and spawns one worker process per other GPU).
   2. a worker that leaves with a batch in flight has that batch rejected on its own GPU by K9's epoch gate (stale > 0),
      and the batch is delivered by someone else
   3. a worker that goes silent (fault injection) is found by the bounded device-side wait and its batches move on
+  3b. a worker that pauses 5 ms after every batch only loses its own share: the others keep their rate (no lock-step)
   4. a worker process killed with SIGKILL mid-stream costs no frame: the job completes, bit-identical
 Prints one "mailbox check ok" line per stage."""
 import argparse
@@ -114,6 +115,36 @@ def main():
     assert box.failed_workers[f0:] == [victim], box.failed_workers
     print(f"mailbox check ok: silent worker gpu{victim} found by the device-side time-out after {time.monotonic() - t0:.2f} s, "
           f"{box.stats['redispatched']} batches re-dispatched so far", flush=True)
+    retire(victim)
+    box.spawn_worker(victim, victim, graph, cfg)
+
+    # ---- 3b. one slow worker (pauses 5 ms after every batch) must not slow the others down
+    def window(seconds):
+        counts = {}
+        box.on_result = lambda b, v, w: counts.__setitem__(w, counts.get(w, 0) + 1)
+        t_end = time.monotonic() + seconds
+        while time.monotonic() < t_end:
+            while box.sched.pending() < 4 * n:
+                box.submit_host(pool[0], range(B))
+            box.pump()
+        assert box.drain(60.0)
+        return counts
+
+    window(0.3)
+    normal = window(1.0)
+    victim = n - 1
+    box.remove_worker(victim)
+    retire(victim)
+    box.spawn_workers([(victim, victim)], graph, cfg, delay_ms=5.0)
+    slow = window(1.0)
+    others_normal = sum(c for w, c in normal.items() if w != victim)
+    others_slow = sum(c for w, c in slow.items() if w != victim)
+    assert slow.get(victim, 0) < 0.6 * normal[victim], (normal, slow)
+    assert others_slow >= 0.9 * others_normal, f"the other workers stalled behind the slow one: {normal} -> {slow}"
+    print(f"mailbox check ok: gpu{victim} delayed 5 ms per batch serves {slow.get(victim, 0)} instead of {normal[victim]} batches/s; "
+          f"the other workers {others_normal} -> {others_slow} batches/s (no lock-step)", flush=True)
+    box.on_result = lambda b, v, w: got.__setitem__(b.batch_id, ({k: a.copy() for k, a in v.items()}, w))
+    box.remove_worker(victim)
     retire(victim)
     box.spawn_worker(victim, victim, graph, cfg)
 

@@ -24,7 +24,7 @@ def test_mailbox_elastic_equals_single_gpu(n):
     p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "check_mailbox.py"), "--gpus", str(n)], cwd=ROOT,
                        capture_output=True, text=True, timeout=900)
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
-    assert p.stdout.count("mailbox check ok") == 4 and "SIGKILL" in p.stdout
+    assert p.stdout.count("mailbox check ok") == 5 and "SIGKILL" in p.stdout and "no lock-step" in p.stdout
 
 
 @pytest.mark.parametrize("n", [2, 8])
