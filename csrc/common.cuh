@@ -318,6 +318,24 @@ __device__ __forceinline__ float lds_f1(uint32_t saddr) {
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(saddr));
   return r;
 }
+__device__ __forceinline__ uint32_t lds_u8(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds_v2(uint32_t saddr) {
+  uint2 r;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(saddr));
+  return r;
+}
+__device__ __forceinline__ void sts_u16(uint32_t saddr, unsigned short v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(saddr), "h"(v) : "memory");
+}
 __device__ __forceinline__ void sts_v4(uint32_t saddr, const uint4& v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }

@@ -395,8 +395,8 @@ __global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const P
   const int nvec = (int)((end - start_al + 15) >> 4);
   {
     const uint4* gsrc = reinterpret_cast<const uint4*>(frame + start_al);
-    uint4* sdst = reinterpret_cast<uint4*>(s_band);
-    for (int i = tid; i < nvec; i += PC_THREADS) sdst[i] = ldg_v4(gsrc + i);
+    const uint32_t sdst = smem_u32(s_band);
+    for (int i = tid; i < nvec; i += PC_THREADS) sts_v4(sdst + (uint32_t)i * 16u, ldg_v4(gsrc + i));
   }
   if (tid < 32) s_b[tid] = a.b0[tid];
   for (int i = tid; i < PC_NET; i += PC_THREADS) {
@@ -422,33 +422,52 @@ __global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const P
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // ---- bilinear resample (cv2 Q11 fixed point) + normalise into the fp16 conv patch
-  const uint8_t* bandp = s_band + skew;
+  // ---- bilinear resample (cv2 Q11 fixed point) + normalise into the fp16 conv patch.
+  // Everything is addressed with 32-bit shared-memory addresses and explicit ld.shared / st.shared: the generic-pointer
+  // form of this loop compiled to 169 instructions per pixel (64-bit address arithmetic for each of the 12 byte loads)
+  // and was 62 % of the kernel's instructions (ncu, profiles/ncu/hot_kernels_details.txt).  The row parameters are
+  // staged once per band.
+  int4* s_row = reinterpret_cast<int4*>(smem + off_bar + 64);             // [PC_PROWS] {row0 offset, row1 offset, q0, q1 | valid<<31}
+  if (tid < PC_PROWS) {
+    const int iy = 2 * oy0 - 1 + tid;
+    int4 rp = make_int4(0, 0, 0, 0);
+    if (iy >= 0 && iy < PC_NET) {
+      const int sy0 = a.ys[iy], sy1 = min(sy0 + 1, a.sh - 1);
+      rp = make_int4((sy0 - r_lo) * row_bytes, (sy1 - r_lo) * row_bytes, a.yq[2 * iy], a.yq[2 * iy + 1] | (int)0x80000000);
+    }
+    s_row[tid] = rp;
+  }
+  __syncthreads();
+  const uint32_t band_s = smem_u32(s_band) + (uint32_t)skew;
+  const uint32_t patch_s = smem_u32(s_patch), xs_s = smem_u32(s_xs), xq_s = smem_u32(s_xq), row_s = smem_u32(s_row);
+  const int sw1 = a.sw - 1;
   for (int i = tid; i < PC_PROWS * PC_PCOLS; i += PC_THREADS) {
     const int pr = i / PC_PCOLS, pc = i - pr * PC_PCOLS;
-    const int iy = 2 * oy0 - 1 + pr, ix = pc - 1;
-    float v0 = 0.f, v1 = 0.f, v2 = 0.f;   // zero padding of the normalised blob (pad: 1)
-    if (iy >= 0 && iy < PC_NET && ix >= 0) {
-      const int sy0 = a.ys[iy], sy1 = min(sy0 + 1, a.sh - 1);
-      const int q0 = a.yq[2 * iy], q1 = a.yq[2 * iy + 1];
-      const int sx0 = s_xs[ix], sx1 = min(sx0 + 1, a.sw - 1);
-      const int a0 = s_xq[2 * ix], a1 = s_xq[2 * ix + 1];
-      const uint8_t* r0 = bandp + (size_t)(sy0 - r_lo) * row_bytes;
-      const uint8_t* r1 = bandp + (size_t)(sy1 - r_lo) * row_bytes;
+    const int ix = pc - 1;
+    const uint4 rp = lds_v4(row_s + (uint32_t)pr * 16u);
+    unsigned short h0 = 0, h1 = 0, h2 = 0;   // zero padding of the normalised blob (pad: 1)
+    if ((int)rp.w < 0 && ix >= 0) {
+      const int q0 = (int)rp.z, q1 = (int)(rp.w & 0x7FFFFFFFu);
+      const int sx0 = (int)lds_u32(xs_s + (uint32_t)ix * 4u), sx1 = min(sx0 + 1, sw1);
+      const uint2 aq = lds_v2(xq_s + (uint32_t)ix * 8u);
+      const int a0 = (int)aq.x, a1 = (int)aq.y;
+      const uint32_t p00 = band_s + rp.x + (uint32_t)(sx0 * 3), p01 = band_s + rp.x + (uint32_t)(sx1 * 3);
+      const uint32_t p10 = band_s + rp.y + (uint32_t)(sx0 * 3), p11 = band_s + rp.y + (uint32_t)(sx1 * 3);
       int px[3];
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const int h0 = r0[sx0 * 3 + c] * a0 + r0[sx1 * 3 + c] * a1;
-        const int h1 = r1[sx0 * 3 + c] * a0 + r1[sx1 * 3 + c] * a1;
-        px[c] = min(max((((q0 * (h0 >> 4)) >> 16) + ((q1 * (h1 >> 4)) >> 16) + 2) >> 2, 0), 255);
+        const int t0 = (int)lds_u8(p00 + c) * a0 + (int)lds_u8(p01 + c) * a1;
+        const int t1 = (int)lds_u8(p10 + c) * a0 + (int)lds_u8(p11 + c) * a1;
+        px[c] = min(max((((q0 * (t0 >> 4)) >> 16) + ((q1 * (t1 >> 4)) >> 16) + 2) >> 2, 0), 255);
       }
-      v0 = __fmul_rn(__fsub_rn((float)px[0], a.mean0), a.scale);
-      v1 = __fmul_rn(__fsub_rn((float)px[1], a.mean1), a.scale);
-      v2 = __fmul_rn(__fsub_rn((float)px[2], a.mean2), a.scale);
+      h0 = __half_as_ushort(__float2half_rn(__fmul_rn(__fsub_rn((float)px[0], a.mean0), a.scale)));
+      h1 = __half_as_ushort(__float2half_rn(__fmul_rn(__fsub_rn((float)px[1], a.mean1), a.scale)));
+      h2 = __half_as_ushort(__float2half_rn(__fmul_rn(__fsub_rn((float)px[2], a.mean2), a.scale)));
     }
-    s_patch[i * 3 + 0] = __float2half_rn(v0);
-    s_patch[i * 3 + 1] = __float2half_rn(v1);
-    s_patch[i * 3 + 2] = __float2half_rn(v2);
+    const uint32_t o = patch_s + (uint32_t)i * 6u;
+    sts_u16(o, h0);
+    sts_u16(o + 2, h1);
+    sts_u16(o + 4, h2);
   }
   __syncthreads();
 
@@ -489,22 +508,22 @@ __global__ void __launch_bounds__(PC_THREADS, 3) preproc_conv0_tc_kernel(const P
       for (int e = 0; e < 8; ++e) pk[e] = 0u;
       if (pix < npix) {
         const int oy = pix / PC_OUT, ox = pix - oy * PC_OUT;
-        const __half* p0 = s_patch + ((2 * oy) * PC_PCOLS + 2 * ox) * 3;
+        const uint32_t p0 = patch_s + (uint32_t)(((2 * oy) * PC_PCOLS + 2 * ox) * 6);     // 32-bit shared address
         if (fhalf == 0) {
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
             const int k0 = 2 * e, k1 = 2 * e + 1;       // k = ky*9 + (kx*3+c)
-            const __half h0 = p0[(k0 / 9) * PC_PCOLS * 3 + (k0 % 9)];
-            const __half h1 = p0[(k1 / 9) * PC_PCOLS * 3 + (k1 % 9)];
-            pk[e] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+            const uint32_t h0 = lds_u16(p0 + (uint32_t)(((k0 / 9) * PC_PCOLS * 3 + (k0 % 9)) * 2));
+            const uint32_t h1 = lds_u16(p0 + (uint32_t)(((k1 / 9) * PC_PCOLS * 3 + (k1 % 9)) * 2));
+            pk[e] = h0 | (h1 << 16);
           }
         } else {
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
             const int k0 = 16 + 2 * e, k1 = 17 + 2 * e;
-            const __half h0 = k0 < 27 ? p0[(k0 / 9) * PC_PCOLS * 3 + (k0 % 9)] : __ushort_as_half((unsigned short)0);
-            const __half h1 = k1 < 27 ? p0[(k1 / 9) * PC_PCOLS * 3 + (k1 % 9)] : __ushort_as_half((unsigned short)0);
-            pk[e] = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+            const uint32_t h0 = k0 < 27 ? lds_u16(p0 + (uint32_t)(((k0 / 9) * PC_PCOLS * 3 + (k0 % 9)) * 2)) : 0u;
+            const uint32_t h1 = k1 < 27 ? lds_u16(p0 + (uint32_t)(((k1 / 9) * PC_PCOLS * 3 + (k1 % 9)) * 2)) : 0u;
+            pk[e] = h0 | (h1 << 16);
           }
         }
       }
@@ -561,7 +580,7 @@ int preproc_prepare(PreprocLaunch* L, const uint8_t* src400, long long src_frame
   if (band_rows_max > sh) band_rows_max = sh;
   a.band_bytes = ((band_rows_max * sw * 3 + 31) & ~15) + 16;
   L->smem = PC_BAND_OFF + a.band_bytes;
-  L->smem_tc = TC_OFF_A + tc_ab_bytes(a.band_bytes) + TC_PATCH_BYTES + 3 * PC_NET * 4 + 32 * 4 + 64 + 1024;
+  L->smem_tc = TC_OFF_A + tc_ab_bytes(a.band_bytes) + TC_PATCH_BYTES + 3 * PC_NET * 4 + 32 * 4 + 64 + PC_PROWS * 16 + 64 + 1024;
   const char* env = getenv("DVC_CONV0_CUDA_CORES");            // A/B switch: the fp32 CUDA-core variant
   L->use_tc = !(env && env[0] == '1') && L->smem_tc <= 110 * 1024;   // taller source frames fall back to the CUDA-core variant
   DVC_REQUIRE(L->smem <= 226 * 1024, "preproc: source band of %d rows x %d px does not fit shared memory", band_rows_max, sw);
