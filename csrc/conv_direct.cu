@@ -126,7 +126,7 @@ struct DwArgs {
   __half* out;
 };
 
-template <int STRIDE>
+template <int STRIDE, int NPX>
 __global__ void __launch_bounds__(256) dw3x3_tma_kernel(const __grid_constant__ CUtensorMap tm, const DwArgs a) {
   extern __shared__ uint8_t dw_smem_raw[];
   uint8_t* tile = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dw_smem_raw) + 127) & ~uintptr_t(127));
@@ -164,57 +164,63 @@ __global__ void __launch_bounds__(256) dw3x3_tma_kernel(const __grid_constant__ 
   const float4 b1 = __ldg(reinterpret_cast<const float4*>(a.bias + c0 + 4));
   mbar_wait(&bar, 0);
   const uint32_t tile_s = smem_u32(tile) + (uint32_t)(cg * 16);
-  // Work item = two horizontally adjacent outputs: they share STRIDE+3 input columns per kernel row, so a
-  // pair costs 3*(STRIDE+3) shared-memory loads instead of 18, and carries 16 independent accumulators.
-  constexpr int NC = STRIDE + 3;
-  const int ppr = (a.TX + 1) >> 1;
-  const int npairs = ppr * a.TY;
-  for (int p = pt; p < npairs; p += pxt) {
-    const int oy = p / ppr, ox = (p - oy * ppr) * 2;
+  // Work item = NPX horizontally adjacent outputs x 8 channels: they share (NPX-1)*STRIDE+3 input columns per kernel row
+  // (NPX = 2: 12 / 15 shared-memory loads instead of 18; NPX = 4, stride 1: 18 instead of 36) and the per-item address
+  // and loop instructions are paid once per NPX outputs - the kernel is issue-bound (ncu: 55 % issue utilisation, half
+  // of it FHFMA), so instructions per output are what counts.  NPX = 4 needs TX % 4 == 0 (the host picks such a tile).
+  constexpr int NC = (NPX - 1) * STRIDE + 3;
+  const int ppr = NPX == 2 ? ((a.TX + 1) >> 1) : (a.TX / NPX);
+  const int nitems = ppr * a.TY;
+  for (int p = pt; p < nitems; p += pxt) {
+    const int oy = p / ppr, ox = (p - oy * ppr) * NPX;
     const int gx = tx * a.TX + ox, gy = ty * a.TY + oy;
     if (gx >= a.Wo || gy >= a.Ho) continue;
-    const bool two = (ox + 1 < a.TX) && (gx + 1 < a.Wo);
-    float acc0[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-    float acc1[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    float acc[NPX][8];
+#pragma unroll
+    for (int q = 0; q < NPX; ++q) {
+      acc[q][0] = b0.x; acc[q][1] = b0.y; acc[q][2] = b0.z; acc[q][3] = b0.w;
+      acc[q][4] = b1.x; acc[q][5] = b1.y; acc[q][6] = b1.z; acc[q][7] = b1.w;
+    }
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky) {
       uint4 v[NC];
       const int rowbase = (oy * STRIDE + ky) * a.BW;
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
-        const int col = min(ox * STRIDE + c, a.BW - 1);
+        const int col = NPX == 2 ? min(ox * STRIDE + c, a.BW - 1) : ox * STRIDE + c;
         v[c] = lds_v4(tile_s + (uint32_t)((rowbase + col) * a.CT * 2));
       }
 #pragma unroll
       for (int kx = 0; kx < 3; ++kx) {
         const int t = ky * 3 + kx;
-        fhfma2(acc0[0], acc0[1], v[kx].x, wq[t][0]);
-        fhfma2(acc0[2], acc0[3], v[kx].y, wq[t][1]);
-        fhfma2(acc0[4], acc0[5], v[kx].z, wq[t][2]);
-        fhfma2(acc0[6], acc0[7], v[kx].w, wq[t][3]);
-        fhfma2(acc1[0], acc1[1], v[STRIDE + kx].x, wq[t][0]);
-        fhfma2(acc1[2], acc1[3], v[STRIDE + kx].y, wq[t][1]);
-        fhfma2(acc1[4], acc1[5], v[STRIDE + kx].z, wq[t][2]);
-        fhfma2(acc1[6], acc1[7], v[STRIDE + kx].w, wq[t][3]);
+#pragma unroll
+        for (int q = 0; q < NPX; ++q) {
+          fhfma2(acc[q][0], acc[q][1], v[q * STRIDE + kx].x, wq[t][0]);
+          fhfma2(acc[q][2], acc[q][3], v[q * STRIDE + kx].y, wq[t][1]);
+          fhfma2(acc[q][4], acc[q][5], v[q * STRIDE + kx].z, wq[t][2]);
+          fhfma2(acc[q][6], acc[q][7], v[q * STRIDE + kx].w, wq[t][3]);
+        }
       }
     }
-    if (a.relu) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { acc0[j] = fmaxf(acc0[j], 0.f); acc1[j] = fmaxf(acc1[j], 0.f); }
-    }
     __half* o = a.out + (((size_t)n * a.Ho + gy) * a.Wo + gx) * a.C + c0;
-    *reinterpret_cast<uint4*>(o) =
-        make_uint4(pack_half2(acc0[0], acc0[1]), pack_half2(acc0[2], acc0[3]), pack_half2(acc0[4], acc0[5]), pack_half2(acc0[6], acc0[7]));
-    if (two)
-      *reinterpret_cast<uint4*>(o + a.C) =
-          make_uint4(pack_half2(acc1[0], acc1[1]), pack_half2(acc1[2], acc1[3]), pack_half2(acc1[4], acc1[5]), pack_half2(acc1[6], acc1[7]));
+#pragma unroll
+    for (int q = 0; q < NPX; ++q) {
+      if (q == 0 || ((ox + q < a.TX) && (gx + q < a.Wo))) {
+        if (a.relu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[q][j] = fmaxf(acc[q][j], 0.f);
+        }
+        *reinterpret_cast<uint4*>(o + (size_t)q * a.C) = make_uint4(pack_half2(acc[q][0], acc[q][1]), pack_half2(acc[q][2], acc[q][3]),
+                                                                   pack_half2(acc[q][4], acc[q][5]), pack_half2(acc[q][6], acc[q][7]));
+      }
+    }
   }
 }
 
 struct DwLaunch {
   CUtensorMap tm;
   DwArgs args;
-  int grid, smem, stride, threads;
+  int grid, smem, stride, threads, npx;
   bool tma;
   const void* in;
 };
@@ -248,9 +254,23 @@ int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stri
   const int smem_limit = dw_env_int("DVC_DW_SMEM_KB", DW_SMEM_LIMIT / 1024, 4, DW_SMEM_LIMIT / 1024) * 1024;
   L->threads = dw_env_int("DVC_DW_THREADS", 128, 64, 256) & ~31;   // 128: 4 CTAs per SM (register-bound), ~200 KB of TMA in flight per SM
   const int min_outs = L->threads / 4;
+  // stride 1: four outputs per work item when a tile whose width is a multiple of 4 costs at most 8 % more than the
+  // unconstrained best (DVC_DW_NPX=2 forces the pair kernel)
+  double best4 = 1e30;
+  int bx4 = 0, by4 = 0;
   for (int TY = 1; TY <= (a.Ho < 64 ? a.Ho : 64); ++TY) {
-    for (int TX = 1; TX <= (a.Wo < 64 ? a.Wo : 64); ++TX) {
+    for (int TX = 1; TX <= 64; ++TX) {
       const int outs = TX * TY;
+      if (TX % 4 == 0 && stride == 1 && TX <= ((a.Wo + 3) & ~3) && outs <= 1024 && !(outs < min_outs && (TX < a.Wo || TY < a.Ho))) {
+        const int BW4 = TX + 2, BH4 = TY + 2;
+        if (BW4 <= 256 && BH4 <= 256 && BW4 * BH4 * a.CT * 2 <= smem_limit) {
+          const int ntx = ceil_div(a.Wo, TX), nty = ceil_div(a.Ho, TY);
+          const double cost = (double)ntx * nty * BW4 * BH4 / ((double)H * W) + 1.5 * (double)ntx * TX * nty * TY / ((double)a.Wo * a.Ho)
+                              + 0.02 * (256.0 / outs);
+          if (cost < best4) { best4 = cost; bx4 = TX; by4 = TY; }
+        }
+      }
+      if (TX > (a.Wo < 64 ? a.Wo : 64)) continue;
       if (outs > 1024) continue;
       if (outs < min_outs && (TX < a.Wo || TY < a.Ho)) continue;
       const int BW = (TX - 1) * stride + 3, BH = (TY - 1) * stride + 3;
@@ -262,6 +282,11 @@ int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stri
     }
   }
   DVC_REQUIRE(bx > 0, "dwconv: no tile fits shared memory (W=%d H=%d C=%d)", W, H, C);
+  L->npx = 2;
+  const double slack = 1.0 + dw_env_int("DVC_DW_NPX4_SLACK", 8, 0, 100) / 100.0;
+  if (stride == 1 && bx4 > 0 && best4 <= slack * best && dw_env_int("DVC_DW_NPX", 4, 2, 4) == 4) {
+    L->npx = 4; bx = bx4; by = by4;
+  }
   a.TX = bx; a.TY = by;
   a.BW = (bx - 1) * stride + 3; a.BH = (by - 1) * stride + 3;
   a.tiles_x = ceil_div(a.Wo, bx); a.tiles_y = ceil_div(a.Ho, by);
@@ -278,12 +303,14 @@ int dw_launch(const DwLaunch* L, cudaStream_t st) {
   int dev = 0;
   DVC_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63].load(std::memory_order_acquire)) {
-    DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
-    DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
+    DVC_CHECK_CUDA(cudaFuncSetAttribute(dw3x3_tma_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM_LIMIT + 1024));
     attr_set[dev & 63].store(true, std::memory_order_release);
   }
-  if (L->stride == 1) DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<1>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));
-  else DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<2>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));
+  if (L->stride == 1 && L->npx == 4) DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<1, 4>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));
+  else if (L->stride == 1) DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<1, 2>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));
+  else DVC_CHECK_CUDA(launch_pdl(dw3x3_tma_kernel<2, 2>, dim3(L->grid), dim3(L->threads), (size_t)L->smem, st, 1, L->tm, L->args));
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
