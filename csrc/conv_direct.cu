@@ -171,8 +171,12 @@ __global__ void __launch_bounds__(256) dw3x3_tma_kernel(const __grid_constant__ 
   constexpr int NC = (NPX - 1) * STRIDE + 3;
   const int ppr = NPX == 2 ? ((a.TX + 1) >> 1) : (a.TX / NPX);
   const int nitems = ppr * a.TY;
-  for (int p = pt; p < nitems; p += pxt) {
-    const int oy = p / ppr, ox = (p - oy * ppr) * NPX;
+  // (row, item-in-row) advance incrementally: one runtime division per CTA instead of one per item
+  const int step_y = pxt / ppr, step_x = pxt - step_y * ppr;
+  int oy = pt / ppr, oxi = pt - oy * ppr;
+  for (int p = pt; p < nitems; p += pxt, oxi += step_x, oy += step_y) {
+    if (oxi >= ppr) { oxi -= ppr; ++oy; }
+    const int ox = oxi * NPX;
     const int gx = tx * a.TX + ox, gy = ty * a.TY + oy;
     if (gx >= a.Wo || gy >= a.Ho) continue;
     float acc[NPX][8];
@@ -283,7 +287,7 @@ int dw_prepare(DwLaunch* L, const void* in, int B, int H, int W, int C, int stri
   }
   DVC_REQUIRE(bx > 0, "dwconv: no tile fits shared memory (W=%d H=%d C=%d)", W, H, C);
   L->npx = 2;
-  const double slack = 1.0 + dw_env_int("DVC_DW_NPX4_SLACK", 8, 0, 100) / 100.0;
+  const double slack = 1.0 + dw_env_int("DVC_DW_NPX4_SLACK", 20, 0, 100) / 100.0;
   if (stride == 1 && bx4 > 0 && best4 <= slack * best && dw_env_int("DVC_DW_NPX", 4, 2, 4) == 4) {
     L->npx = 4; bx = bx4; by = by4;
   }
