@@ -513,11 +513,12 @@ class NativeEngine:
 
     def process(self, frames, requester_id: Optional[str] = None, annotate: bool = True) -> BatchResult:
         """frames: uint8 [B,H,W,3] (numpy / CPU tensor / CUDA tensor). Synchronous convenience API."""
+        from .utils.trace import span
         t = torch.as_tensor(frames) if not isinstance(frames, torch.Tensor) else frames
         B, H, W, _ = t.shape
         st = self.state(B, H, W, requester_id)
-        with torch.cuda.device(self.device):
-            st.raw.copy_(t, non_blocking=True)
+        with torch.cuda.device(self.device), span("engine.process", getattr(self, "metrics", None), frames=B):
+            st.raw.copy_(t, non_blocking=True)         # NVTX range "engine.process" brackets upload, kernels and the wait
             self.run(st, annotate)
             torch.cuda.current_stream().synchronize()
         return self.result(st)

@@ -75,13 +75,11 @@ class BoxCluster:
         """Non-client ranks: serve until the client ends the phase.  Returns the batches served; `serve_ms` is the
         device time between entering and leaving the loop (CUDA events on this rank)."""
         assert not self.is_client
-        with torch.cuda.device(self.dev):
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            n = self.lanes.serve(local_feed=local_feed, expect_work=True, synced=True) if self._synced else 0
-            b.record()
-            b.synchronize()
-            self.serve_ms = a.elapsed_time(b)
+        from ..utils.trace import DeviceTimer, span
+        with torch.cuda.device(self.dev), span(f"mailbox.serve.rank{self.rank}"):
+            with DeviceTimer() as t:
+                n = self.lanes.serve(local_feed=local_feed, expect_work=True, synced=True) if self._synced else 0
+            self.serve_ms = t.ms()
         return n
 
     def end(self):

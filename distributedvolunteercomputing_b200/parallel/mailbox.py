@@ -678,7 +678,7 @@ class ElasticBox:
     reset_worker / alloc_slot / free_slot surface (tests use a CPU stand-in)."""
 
     def __init__(self, client, scheduler: Optional[Scheduler] = None, on_result: Optional[Callable] = None,
-                 requester: str = "client", fetch: bool = True, log: Optional[Callable[[str], None]] = None):
+                 requester: str = "client", fetch: bool = True, log: Optional[Callable[[str], None]] = None, metrics=None):
         self.client = client
         self.lay = client.layout
         self.sched = scheduler or Scheduler(policy="least_loaded", requester_works=True, worker_timeout_s=3600.0)
@@ -686,6 +686,7 @@ class ElasticBox:
         self.requester = requester
         self.fetch = fetch
         self.log = log or (lambda m: None)
+        self.metrics = metrics             # utils.metrics.Metrics (optional): per-batch latency, membership events
         self.flights: Dict[Tuple[int, int], _Flight] = {}
         self.alive: Dict[int, bool] = {}
         self.epoch_counter = 0
@@ -707,6 +708,8 @@ class ElasticBox:
         self.alive[w] = True
         self.sched.join(self.name(w), capacity=self.lay.lanes)
         self.stats["joins"] += 1
+        if self.metrics is not None:
+            self.metrics.emit("join", worker=self.name(w), epoch=self.epoch_counter)
 
     def remove_worker(self, w: int, reason: str = "leave", stop: bool = True) -> int:
         """Worker `w` leaves now (or was found dead).  Its in-flight batches are re-queued; returns how many."""
@@ -724,6 +727,8 @@ class ElasticBox:
             self.client.stop_worker(w)
         self.stats["leaves" if reason == "leave" else "failures"] += 1
         self.stats["redispatched"] += len(requeued)
+        if self.metrics is not None:
+            self.metrics.emit("leave", worker=self.name(w), reason=reason, epoch=self.epoch_counter, redispatched=len(requeued))
         return len(requeued)
 
     def workers_alive(self) -> List[int]:
@@ -804,6 +809,9 @@ class ElasticBox:
                 if first is not None:
                     done += 1
                     self.stats["completed"] += 1
+                    if self.metrics is not None:
+                        self.metrics.observe("batch_latency_ms", (time.monotonic() - fl.t0) * 1e3)
+                        self.metrics.inc("frames_out", len(fl.batch.frame_ids))
                     if self.on_result is not None:
                         self.on_result(fl.batch, self.client.result(fl.worker, fl.lane) if self.fetch else None, fl.worker)
                     pl = fl.batch.payload
