@@ -90,7 +90,6 @@ _SIGS = {
     "dvc_dwpw_fused": ([_P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _I, _P, _P], _I),
     "dvc_plan_run": ([_P, _P], _I),
     "dvc_plan_set_head_branch": ([_P, _I], _I),
-    "dvc_dwconv3x3_direct": ([_P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P], _I),
     "dvc_p2p_alloc": ([_SZ, C.POINTER(C.c_void_p)], _I),
     "dvc_p2p_free": ([_P], _I),
     "dvc_p2p_get_handle": ([_P, _P], _I),

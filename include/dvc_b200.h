@@ -74,8 +74,7 @@ int dvc_preproc_conv0(const uint8_t* src400, long long src_frame_stride, const i
 int dvc_dwconv3x3(const void* in_f16, int B, int H, int W, int C, int stride, const float* w, const float* b,
                   int relu, void* out_f16, void* stream);
 
-int dvc_dwconv3x3_direct(const void* in_f16, int B, int H, int W, int C, int stride, const float* w, const float* b,
-                         int relu, void* out_f16, void* stream);   /* non-TMA variant, for A/B measurements */
+   /* non-TMA variant, for A/B measurements */
 
 /* ---- K2/K5: pointwise conv as GEMM on tcgen05 tensor cores with TMA-fed operands and a
  * TMEM accumulator: out[M,N] = act(A[M,K] * Wt[N,K]^T + bias[N]).  A and Wt are K-major

@@ -167,6 +167,26 @@ def test_preproc_conv0_matches_restatement(K, h4, mean):
     assert err <= 4e-3 * max(1.0, ref.abs().max().item()), err   # fp16 im2col operands on the tensor-core path
 
 
+@pytest.mark.parametrize("h4,forced", [(300, True), (1300, False)])
+def test_preproc_conv0_cuda_core_fallback(K, h4, forced, monkeypatch):
+    """K1b has two conv0 back ends: the tcgen05 one and an fp32 CUDA-core one.  The second is chosen when the source band
+    of a very tall 400-wide frame does not leave room for the tensor-core staging (h4 = 1300: a 4:13 portrait frame) and
+    by DVC_CONV0_CUDA_CORES=1; both must match the restatement."""
+    if forced:
+        monkeypatch.setenv("DVC_CONV0_CUDA_CORES", "1")
+    rng = np.random.default_rng(h4)
+    frames = rng.integers(0, 256, (2, h4, 400, 3), dtype=np.uint8)
+    w = _rand((32, 3, 3, 3), 0.3, 11)
+    b = _rand((32,), 0.2, 12)
+    w27 = w.permute(2, 3, 1, 0).reshape(27, 32).contiguous().to(DEV)
+    out = K.preproc_conv0(torch.from_numpy(frames).to(DEV), w27, b.to(DEV), mean=P.MEAN_COMPAT)
+    torch.cuda.synchronize()
+    blobs = np.concatenate([P.blob_from_image(P.resize_linear_u8(f, 300, 300), P.MEAN_COMPAT) for f in frames])
+    ref = F.relu(F.conv2d(torch.from_numpy(blobs), w, b, stride=2, padding=1)).permute(0, 2, 3, 1)
+    err = (out.float().cpu() - ref).abs().max().item()
+    assert err <= 4e-3 * max(1.0, ref.abs().max().item()), err
+
+
 def test_preproc_frame_index_gathers_ring_slots(K):
     rng = np.random.default_rng(5)
     ring = torch.from_numpy(rng.integers(0, 256, (6, 300, 400, 3), dtype=np.uint8)).to(DEV)
