@@ -107,6 +107,7 @@ def run_native(args):
 
     sustained = None
     e2e_sharded = None
+    coll_in_regions = 0
     if not multi:
         st = eng.state(B, H, W)
         # ---- inputs: POOL distinct batches, on the device (kernel timing) and pinned on the host (e2e)
@@ -239,6 +240,20 @@ def run_native(args):
                 done += box.pump()
             return done
 
+        # every torch.distributed collective this process issues is counted; the counter is read around each timed
+        # region: it must not move there (the barriers of begin() / end() lie outside)
+        coll = [0]
+        in_region = [0]
+        for name in ("barrier", "all_reduce", "broadcast", "broadcast_object_list", "all_gather", "all_gather_object",
+                     "scatter", "gather", "reduce_scatter", "all_to_all", "send", "recv"):
+            if hasattr(dist, name):
+                def wrap(fn):
+                    def counted(*a, **k):
+                        coll[0] += 1
+                        return fn(*a, **k)
+                    return counted
+                setattr(dist, name, wrap(getattr(dist, name)))
+
         def phase(n_batches, mode, fetch, time_limit_s=None):
             """One membership phase on every rank; returns (device ms on this rank, batches done)."""
             cluster.begin()
@@ -246,14 +261,18 @@ def run_native(args):
                 box.fetch = fetch
                 torch.cuda.synchronize()
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                c0 = coll[0]
                 a.record()
                 n = run_batches(n_batches, mode, time_limit_s)
                 b.record()
                 b.synchronize()
+                in_region[0] += coll[0] - c0
                 ms = a.elapsed_time(b)
                 cluster.end()
                 return ms, n
+            c0 = coll[0]
             cluster.serve(local_feed=(lambda i: my_pool[i % POOL]) if mode == "local" else None)
+            in_region[0] += coll[0] - c0
             cluster.end()
             return cluster.lanes.busy_ms, 0
 
@@ -314,6 +333,7 @@ def run_native(args):
                        "api": "ElasticBox.submit_local: every rank uploads its own 64-frame shard over its own PCIe link "
                               "(WorkerLanes.serve(local_feed=...)); detections gathered on the client GPU over NVLink"}
         det_sum = int(sum(int(cluster.client.device_result(w, 0)["det_count"].sum().item()) for w in range(world))) if rank == 0 else 0
+        (coll_in_regions,) = max_over_ranks(in_region[0])
         per_batch_launches = cluster.launches_per_batch() + 2          # + the client's post and done-wait kernels
         launches_timed = per_batch_launches * K
         parallelism = f"dp{world} (scheduler-dispatched batches; frame scatter fused into K1a and detection gather fused into K9 over NVLink, ordered by device-side mailboxes)"
@@ -338,6 +358,7 @@ def run_native(args):
         "gpu_launches_note": "derived: kernels per batch (plan ops + resize + overlay + mailbox kernels) x batches in the timed region; "
                              "all but the eager ones run inside CUDA-graph replays",
         "gpu_launches_eager_counted_by_library": int(launches_eager),
+        "collectives_in_timed_regions": int(coll_in_regions),      # torch.distributed calls between the start and stop events, max over ranks
         "clocks": clocks, "detections_last_batch": det_sum,
     }
     if rank == 0:
