@@ -221,6 +221,24 @@ class Scheduler:
 
     # ------------------------------------------------------------------ dispatch
     def _pick_worker(self, requester: str) -> Optional[WorkerInfo]:
+        if self.policy != "round_robin":
+            # least loaded, one pass (this runs once per dispatch: ~10^4 times a second on a full box).  Same rule as
+            # Membership.eligible + min(inflight / capacity, completed, addr).
+            best, best_key = None, None
+            rw = self.requester_works
+            with self.members.lock:
+                for w in self.members.workers.values():
+                    if not w.alive or w.inflight >= w.capacity:
+                        continue
+                    if w.addr == requester:
+                        if not rw:
+                            continue
+                    elif w.role != "worker":
+                        continue
+                    key = (w.inflight / (w.capacity if w.capacity > 0 else 1), w.completed, w.addr)
+                    if best_key is None or key < best_key:
+                        best, best_key = w, key
+            return best
         cands = [w for w in self.members.eligible(requester, self.requester_works) if w.inflight < w.capacity]
         if not cands:
             return None
