@@ -332,7 +332,7 @@ def run_native(args):
                        "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                        "api": "ElasticBox.submit_local: every rank uploads its own 64-frame shard over its own PCIe link "
                               "(WorkerLanes.serve(local_feed=...)); detections gathered on the client GPU over NVLink"}
-        det_sum = int(sum(int(cluster.client.device_result(w, 0, 1)["det_count"].sum().item()) for w in range(world))) if rank == 0 else 0
+        det_sum = int(sum(int(cluster.client.device_result(w, 0)["det_count"].sum().item()) for w in range(world))) if rank == 0 else 0
         (coll_in_regions,) = max_over_ranks(in_region[0])
         per_batch_launches = cluster.launches_per_batch() + 2          # + the client's post and done-wait kernels
         launches_timed = per_batch_launches * K

@@ -64,10 +64,6 @@ struct DetArgs {
   // mailbox binding (csrc/mailbox.cu, optional): the flag value comes from the lane's control block, and the last CTA
   // of the batch publishes it in *done_word (a word on the client GPU) once every frame's rows are system-visible
   const uint32_t* flag_value_ptr; uint32_t* done_word; uint32_t* done_counter;
-  // when `mbx` is set the sinks, the flag value and the done word of THIS batch are read from the lane's control block
-  // (one of the lane's two result slots on the client, chosen by the wait kernel); boxes also go to local memory
-  const dvc_mbx_lane_ctl* mbx; long long off_det, off_boxes, off_det_count, off_box_count, off_flags;
-  int* local_boxes; int* local_box_count;
   // global scratch (per frame): prob [C][P], kept_n [C], kept_score [C][K], kept_idx [C][K], kept_box [C][K][4]
   float* prob; int* kept_n; float* kept_score; int* kept_idx; float* kept_box;
 };
@@ -327,26 +323,13 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
     row[3] = bx[0]; row[4] = bx[1]; row[5] = bx[2]; row[6] = bx[3];
   }
   __syncthreads();
-  // sinks: fixed pointers, or (mailbox lane) the result slot the wait kernel chose for this batch
-  float* det_base = a.det; int* det_count = a.det_count; int* boxes_base = a.boxes_i; int* box_count = a.box_count;
-  uint32_t* flags = a.flags; uint32_t* done_word = a.done_word;
-  uint32_t fv = a.flag_value_ptr ? *reinterpret_cast<const volatile uint32_t*>(a.flag_value_ptr) : a.flag_value;
-  if (a.mbx) {
-    uint8_t* r = *reinterpret_cast<uint8_t* const volatile*>(&a.mbx->res);
-    det_base = reinterpret_cast<float*>(r + a.off_det); boxes_base = reinterpret_cast<int*>(r + a.off_boxes);
-    det_count = reinterpret_cast<int*>(r + a.off_det_count); box_count = reinterpret_cast<int*>(r + a.off_box_count);
-    flags = reinterpret_cast<uint32_t*>(r + a.off_flags);
-    done_word = *reinterpret_cast<uint32_t* const volatile*>(&a.mbx->done);
-    fv = *reinterpret_cast<const volatile uint32_t*>(&a.mbx->flag_value);
-  }
   // rows (zero padded) go out with coalesced stores; `det` may be peer memory (the gather)
-  float* det = det_base + (size_t)slot * DVC_MAX_DET * DVC_DET_ROW;
+  float* det = a.det + (size_t)slot * DVC_MAX_DET * DVC_DET_ROW;
   for (int e = tid; e < DVC_MAX_DET * DVC_DET_ROW; e += MERGE_THREADS) det[e] = s_rows[e];
   // application filter (conf > 0.2, class in CONSIDER) -> integer boxes, in row order
   if (warp == 0) {
     int base = 0;
-    int* bi = boxes_base + (size_t)slot * DVC_MAX_DET * 4;
-    int* bl = a.local_boxes ? a.local_boxes + (size_t)f * DVC_MAX_DET * 4 : nullptr;      // local copy for the overlay kernel
+    int* bi = a.boxes_i + (size_t)slot * DVC_MAX_DET * 4;
     for (int r0 = 0; r0 < n_out; r0 += 32) {
       const int r = r0 + lane;
       bool ok = false;
@@ -360,25 +343,21 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
         const int pos = base + __popc(m & ((1u << lane) - 1));
         const double dw = (double)a.p.out_w, dh = (double)a.p.out_h;
         const double v[4] = {(double)row[3] * dw, (double)row[4] * dh, (double)row[5] * dw, (double)row[6] * dh};
-        for (int k = 0; k < 4; ++k) {
-          const int iv = (int)fmin(fmax(v[k], -2147483000.0), 2147483000.0);
-          bi[pos * 4 + k] = iv;
-          if (bl) bl[pos * 4 + k] = iv;
-        }
+        for (int k = 0; k < 4; ++k) bi[pos * 4 + k] = (int)fmin(fmax(v[k], -2147483000.0), 2147483000.0);
       }
       base += __popc(m);
     }
     if (lane == 0) {
-      box_count[slot] = base;
-      det_count[slot] = n_out;
-      if (a.local_box_count) a.local_box_count[f] = base;
+      a.box_count[slot] = base;
+      a.det_count[slot] = n_out;
     }
   }
   // delivery: make the rows visible system-wide, then publish the slot flag
   __threadfence_system();
   __syncthreads();
   if (tid == 0) {
-    if (flags) st_release_sys_u32(flags + slot, fv);
+    const uint32_t fv = a.flag_value_ptr ? *reinterpret_cast<const volatile uint32_t*>(a.flag_value_ptr) : a.flag_value;
+    if (a.flags) st_release_sys_u32(a.flags + slot, fv);
     if (a.done_counter) {
       // batch-level completion: every CTA's rows were fenced to system scope above; the device-scope atomic chains
       // them (cumulativity) to the last arriver, whose release.sys store is what the client's ld.acquire.sys observes
@@ -386,7 +365,7 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_deliver_kernel(const DetA
       if ((prev & 0xFFFFu) == (uint32_t)a.B - 1u) {
         atomicExch(a.done_counter, 0u);
         __threadfence_system();
-        if ((prev >> 16) == 0u && done_word) st_release_sys_u32(done_word, fv);
+        if ((prev >> 16) == 0u && a.done_word) st_release_sys_u32(a.done_word, fv);
       }
     }
     if (a.t_done) a.t_done[f] = globaltimer_ns();
@@ -435,8 +414,6 @@ int det_prepare(DetLaunch* L, const float* loc, const float* conf, const float* 
   a.epoch_now = nullptr; a.epoch_expect = nullptr; a.stale_count = nullptr;      // gate off until det_set_epoch_gate
   a.t_done = nullptr;
   a.flag_value_ptr = nullptr; a.done_word = nullptr; a.done_counter = nullptr;
-  a.mbx = nullptr; a.off_det = a.off_boxes = a.off_det_count = a.off_box_count = a.off_flags = 0;
-  a.local_boxes = nullptr; a.local_box_count = nullptr;
   const int C = p->num_classes, P = p->num_priors;
   uint8_t* s = reinterpret_cast<uint8_t*>(scratch);
   a.prob = reinterpret_cast<float*>(s);
@@ -477,12 +454,8 @@ void det_set_timestamps(DetLaunch* L, unsigned long long* t_done) { L->args.t_do
 void det_set_epoch_gate(DetLaunch* L, const uint32_t* now, const uint32_t* expect, uint32_t* stale_count) {
   L->args.epoch_now = now; L->args.epoch_expect = expect; L->args.stale_count = stale_count;
 }
-void det_set_mailbox(DetLaunch* L, const dvc_mbx_lane_ctl* ctl, uint32_t* done_counter, long long off_det, long long off_boxes,
-                     long long off_det_count, long long off_box_count, long long off_flags, int* local_boxes, int* local_box_count) {
-  DetArgs& a = L->args;
-  a.mbx = ctl; a.done_counter = done_counter; a.flag_value_ptr = nullptr; a.done_word = nullptr;
-  a.off_det = off_det; a.off_boxes = off_boxes; a.off_det_count = off_det_count; a.off_box_count = off_box_count; a.off_flags = off_flags;
-  a.local_boxes = local_boxes; a.local_box_count = local_box_count;
+void det_set_mailbox(DetLaunch* L, const uint32_t* flag_value_ptr, uint32_t* done_word, uint32_t* done_counter) {
+  L->args.flag_value_ptr = flag_value_ptr; L->args.done_word = done_word; L->args.done_counter = done_counter;
 }
 void det_set_sinks(DetLaunch* L, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index) {
   L->args.det = det; L->args.det_count = det_count; L->args.boxes_i = boxes_i; L->args.box_count = box_count;

@@ -2,8 +2,7 @@
 //
 // The reference orders its data plane with one blocking REQ/REP round trip per chunk (send_image waits for the
 // hub's b'OK': server.py:62,73,89 and worker.py:157,180) and dispatches from a host loop (server.py:77-91).
-// Here the requesting client's GPU owns, per (worker, lane), two descriptors, two completion words and two result
-// slots used alternately by sequence parity (so batch n+1 can be posted while n still runs); the words are
+// Here the requesting client's GPU owns one descriptor and one completion word per (worker, lane); the words are
 // written with st.release.sys and polled with ld.acquire.sys by the kernels below, so neither a collective nor a
 // host round trip sits between "frames are in the arena" -> "worker pulls them" -> "rows are back".
 //
@@ -57,15 +56,13 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned 
 
 // One thread.  The descriptor is usually on another GPU: every poll is one NVLink round trip (~2 us), so the loop
 // generates next to no traffic and needs no back-off beyond a short nanosleep.
-__global__ void mbx_wait_desc_kernel(const dvc_mbx_desc* desc_pair, uint32_t expect_seq, const uint8_t* arena_base,
-                                     const uint8_t* local_src, uint8_t* res_pair, size_t res_slot_bytes, uint32_t* done_pair,
-                                     dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* hs, unsigned long long timeout_ns) {
+__global__ void mbx_wait_desc_kernel(const dvc_mbx_desc* desc, uint32_t expect_seq, const uint8_t* arena_base,
+                                     const uint8_t* local_src, dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* hs,
+                                     unsigned long long timeout_ns) {
   if (threadIdx.x != 0) return;
   const unsigned long long t0 = globaltimer_ns();
   uint32_t status = DVC_MBX_NOTHING, seq = 0;
   if (expect_seq == 0u) expect_seq = ctl->next_seq;     // the lane keeps its own position: waits can be queued ahead
-  const uint32_t par = expect_seq & 1u;                 // descriptor / result slot / done word of this batch
-  const dvc_mbx_desc* desc = desc_pair + par;
   for (;;) {
     seq = ld_acquire_sys_u32(&desc->seq);
     if (seq == expect_seq) { status = DVC_MBX_GO; break; }
@@ -84,11 +81,7 @@ __global__ void mbx_wait_desc_kernel(const dvc_mbx_desc* desc_pair, uint32_t exp
     ctl->gate_now = epoch;
     ctl->gate_expect = epoch;
     ctl->flag_value = seq;
-    uint32_t nxt = seq + 1u;
-    if (nxt >= DVC_MBX_SEQ_STOP) nxt = 1u;              // 0 and 0xFFFFFFFF are never sequence numbers
-    ctl->next_seq = nxt;
-    ctl->res = res_pair + (size_t)par * res_slot_bytes;
-    ctl->done = done_pair + par;
+    ctl->next_seq = seq + 1u;
   } else {
     ctl->src = local_src;
     ctl->gate_now = 0u;              // K1a / K1b skip their reads, K9 delivers nothing and does not count it as stale
@@ -157,13 +150,12 @@ extern "C" int dvc_mbx_post(void* const* h_desc_ptrs, const dvc_mbx_desc* h_desc
   return DVC_OK;
 }
 
-extern "C" int dvc_mbx_wait_desc(const dvc_mbx_desc* desc_pair, uint32_t expect_seq, const uint8_t* arena_base, const uint8_t* local_src,
-                                 uint8_t* res_pair, size_t res_slot_bytes, uint32_t* done_pair, dvc_mbx_lane_ctl* ctl,
-                                 dvc_mbx_host_status* h_status, unsigned long long timeout_ns, void* stream) {
-  DVC_REQUIRE(desc_pair && ctl && res_pair && done_pair, "mbx_wait_desc: descriptors, result slots, done words and control block are required");
+extern "C" int dvc_mbx_wait_desc(const dvc_mbx_desc* desc, uint32_t expect_seq, const uint8_t* arena_base, const uint8_t* local_src,
+                                 dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* h_status, unsigned long long timeout_ns,
+                                 void* stream) {
+  DVC_REQUIRE(desc && ctl, "mbx_wait_desc: descriptor and control block are required");
   DVC_REQUIRE(expect_seq != DVC_MBX_SEQ_STOP, "mbx_wait_desc: sequence number 0xFFFFFFFF is reserved for stop");
-  mbx_wait_desc_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(desc_pair, expect_seq, arena_base, local_src, res_pair, res_slot_bytes,
-                                                           done_pair, ctl, h_status, timeout_ns);
+  mbx_wait_desc_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(desc, expect_seq, arena_base, local_src, ctl, h_status, timeout_ns);
   count_launch();
   DVC_CHECK_CUDA(cudaGetLastError());
   return DVC_OK;
@@ -188,16 +180,12 @@ extern "C" int dvc_mbx_wait_done(void* const* h_done_ptrs, const uint32_t* h_seq
 
 extern "C" int dvc_mbx_dispatch(const void* h_src, void* d_dst, size_t src_bytes, void* desc_ptr, const dvc_mbx_desc* h_desc,
                                 void* done_ptr, dvc_mbx_host_status* h_status, unsigned long long timeout_ns,
-                                const void* d_result, void* h_result, size_t result_bytes, void* event, void* stream,
-                                void* post_stream) {
+                                const void* d_result, void* h_result, size_t result_bytes, void* event, void* stream) {
   DVC_REQUIRE(desc_ptr && h_desc && done_ptr, "mbx_dispatch: descriptor and done word are required");
   cudaStream_t st = (cudaStream_t)stream;
-  // the upload and the post go to `post_stream` when given: the lane's own stream may still be parked in the done-wait
-  // of the previous batch, and the whole point of the second descriptor is that this post does not wait for it
-  cudaStream_t ps = post_stream ? (cudaStream_t)post_stream : st;
-  if (h_src && src_bytes) DVC_CHECK_CUDA(cudaMemcpyAsync(d_dst, h_src, src_bytes, cudaMemcpyHostToDevice, ps));
+  if (h_src && src_bytes) DVC_CHECK_CUDA(cudaMemcpyAsync(d_dst, h_src, src_bytes, cudaMemcpyHostToDevice, st));
   void* dp[1] = {desc_ptr};
-  int rc = dvc_mbx_post(dp, h_desc, 1, (void*)ps);
+  int rc = dvc_mbx_post(dp, h_desc, 1, stream);
   if (rc) return rc;
   void* wp[1] = {done_ptr};
   const uint32_t sq[1] = {h_desc->seq};
@@ -230,12 +218,10 @@ extern "C" int dvc_mbx_poll(void* const* h_events, const unsigned char* h_busy, 
 }
 
 extern "C" int dvc_mbx_worker_enqueue(const dvc_mbx_desc* desc, uint32_t expect_seq, const uint8_t* arena_base,
-                                      const uint8_t* local_src, uint8_t* res_pair, size_t res_slot_bytes, uint32_t* done_pair,
-                                      dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* h_status,
+                                      const uint8_t* local_src, dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* h_status,
                                       unsigned long long timeout_ns, void* graph_exec, void* event, void* stream) {
   if (desc) {
-    int rc = dvc_mbx_wait_desc(desc, expect_seq, arena_base, local_src, res_pair, res_slot_bytes, done_pair, ctl, h_status,
-                               timeout_ns, stream);
+    int rc = dvc_mbx_wait_desc(desc, expect_seq, arena_base, local_src, ctl, h_status, timeout_ns, stream);
     if (rc) return rc;
   }
   if (graph_exec) DVC_CHECK_CUDA(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream));
@@ -243,16 +229,15 @@ extern "C" int dvc_mbx_worker_enqueue(const dvc_mbx_desc* desc, uint32_t expect_
   return DVC_OK;
 }
 
-extern "C" int dvc_mbx_local_dispatch(void* desc_ptr, const dvc_mbx_desc* h_desc, const dvc_mbx_desc* desc_pair,
-                                      const uint8_t* arena_base, const uint8_t* local_src, uint8_t* res_pair,
-                                      size_t res_slot_bytes, uint32_t* done_pair, dvc_mbx_lane_ctl* ctl, void* graph_exec, void* done_ptr,
+extern "C" int dvc_mbx_local_dispatch(void* desc_ptr, const dvc_mbx_desc* h_desc, const uint8_t* arena_base,
+                                      const uint8_t* local_src, dvc_mbx_lane_ctl* ctl, void* graph_exec, void* done_ptr,
                                       dvc_mbx_host_status* h_status, unsigned long long timeout_ns, const void* d_result,
                                       void* h_result, size_t result_bytes, void* event, void* stream) {
   DVC_REQUIRE(desc_ptr && h_desc && ctl && graph_exec && done_ptr, "mbx_local_dispatch: missing argument");
   void* dp[1] = {desc_ptr};
   int rc = dvc_mbx_post(dp, h_desc, 1, stream);
   if (rc) return rc;
-  rc = dvc_mbx_wait_desc(desc_pair, h_desc->seq, arena_base, local_src, res_pair, res_slot_bytes, done_pair, ctl, nullptr,
+  rc = dvc_mbx_wait_desc(reinterpret_cast<const dvc_mbx_desc*>(desc_ptr), h_desc->seq, arena_base, local_src, ctl, nullptr,
                          1000000ull, stream);
   if (rc) return rc;
   DVC_CHECK_CUDA(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream));

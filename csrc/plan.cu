@@ -38,8 +38,7 @@ void det_set_timestamps(DetLaunch*, unsigned long long* t_done);
 void preproc_set_timestamps(PreprocLaunch*, unsigned long long* t_ingest);
 void preproc_set_epoch_gate(PreprocLaunch*, const uint32_t* now, const uint32_t* expect);
 void det_set_epoch_gate(DetLaunch*, const uint32_t* now, const uint32_t* expect, uint32_t* stale_count);
-void det_set_mailbox(DetLaunch*, const dvc_mbx_lane_ctl* ctl, uint32_t* done_counter, long long off_det, long long off_boxes,
-                     long long off_det_count, long long off_box_count, long long off_flags, int* local_boxes, int* local_box_count);
+void det_set_mailbox(DetLaunch*, const uint32_t* flag_value_ptr, uint32_t* done_word, uint32_t* done_counter);
 void det_set_sinks(DetLaunch*, float* det, int* det_count, int* boxes_i, int* box_count, uint32_t* flags, const int* slot_index);
 
 struct DwLaunch;
@@ -231,14 +230,13 @@ extern "C" int dvc_plan_set_epoch_gate(dvc_plan* p, const uint32_t* epoch_now, c
   return DVC_OK;
 }
 
-extern "C" int dvc_plan_set_mailbox(dvc_plan* p, const dvc_mbx_lane_ctl* ctl, const uint32_t* live_epoch, uint32_t* done_counter,
-                                    uint32_t* stale_count, long long off_det, long long off_boxes, long long off_det_count,
-                                    long long off_box_count, long long off_flags, int* local_boxes, int* local_box_count) {
+extern "C" int dvc_plan_set_mailbox(dvc_plan* p, const dvc_mbx_lane_ctl* ctl, const uint32_t* live_epoch, uint32_t* done_word,
+                                    uint32_t* done_counter, uint32_t* stale_count) {
   DVC_REQUIRE(p && ctl && live_epoch && done_counter, "plan_set_mailbox: plan, control block, epoch word and counter are required");
   for (auto& op : p->ops) {
     if (op.kind == OP_DET) {
       det_set_epoch_gate(op.det, live_epoch, &ctl->gate_expect, stale_count);
-      det_set_mailbox(op.det, ctl, done_counter, off_det, off_boxes, off_det_count, off_box_count, off_flags, local_boxes, local_box_count);
+      det_set_mailbox(op.det, &ctl->flag_value, done_word, done_counter);
     }
     if (op.kind == OP_PREPROC) preproc_set_epoch_gate(op.pre, &ctl->gate_now, &ctl->gate_expect);
   }

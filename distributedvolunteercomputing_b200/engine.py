@@ -389,25 +389,20 @@ class NativeEngine:
                 delattr(st, key)
         st.remote = True
 
-    def bind_mailbox(self, st: _ShapeState, ctl_ptr: int, live_epoch_ptr: int, done_counter: torch.Tensor,
-                     stale_count: Optional[torch.Tensor], offsets: Tuple[int, int, int, int, int]):
+    def bind_mailbox(self, st: _ShapeState, ctl_ptr: int, live_epoch_ptr: int, done_word_ptr: int, done_counter: torch.Tensor,
+                     stale_count: Optional[torch.Tensor] = None):
         """Bind this state's plan to one mailbox lane (parallel/mailbox.py, csrc/mailbox.cu): K1b runs only when the
-        lane's wait kernel saw a dispatch; K9 reads its sinks (result slot base + `offsets` of rows, integer boxes, the
-        two count arrays and the flags), its flag value and its done word from the lane's control block at run time,
-        publishes the done word once the whole batch is delivered, and rejects the batch when the client's epoch word
-        for this worker has moved on.  The integer boxes also stay in this state's own `boxes_i` / `box_count` for the
-        overlay kernel.  Must precede graph capture."""
+        lane's wait kernel saw a dispatch, K9 publishes the lane's sequence number in the client's done word once the
+        whole batch is delivered and rejects the batch when the client's epoch word for this worker has moved on.
+        Call after `bind_remote`; must precede graph capture."""
         L = self.L
         assert done_counter.is_cuda and done_counter.dtype == torch.int32
         st.mailbox = (done_counter, stale_count)            # keep the tensors alive
-        o = [int(x) for x in offsets]
-        L.check(self.lib.dvc_plan_set_mailbox(st.plan, ctl_ptr, live_epoch_ptr, L.ptr(done_counter),
-                                              L.ptr(stale_count) if stale_count is not None else None, o[0], o[1], o[2], o[3], o[4],
-                                              L.ptr(st.boxes_i), L.ptr(st.box_count)), "plan_set_mailbox")
+        L.check(self.lib.dvc_plan_set_mailbox(st.plan, ctl_ptr, live_epoch_ptr, done_word_ptr, L.ptr(done_counter),
+                                              L.ptr(stale_count) if stale_count is not None else None), "plan_set_mailbox")
         for key in ("graph_ann", "graph_noann"):
             if hasattr(st, key):
                 delattr(st, key)
-        st.remote = True
 
     def enable_timestamps(self, st: _ShapeState, on: bool = True):
         """Device-side trace points: per frame, the %globaltimer nanosecond when K1b starts pulling it and when K9

@@ -43,7 +43,7 @@ class MbxLaneCtl(C.Structure):
     """dvc_mbx_lane_ctl: worker-local control block of one lane (device memory)."""
     _fields_ = [("src", C.c_void_p), ("gate_now", C.c_uint32), ("gate_expect", C.c_uint32), ("flag_value", C.c_uint32),
                 ("status", C.c_uint32), ("batch_id", C.c_uint32), ("n_valid", C.c_uint32), ("next_seq", C.c_uint32),
-                ("reserved", C.c_uint32), ("res", C.c_void_p), ("done", C.c_void_p)]
+                ("reserved", C.c_uint32)]
 
 
 class MbxHostStatus(C.Structure):
@@ -100,15 +100,15 @@ _SIGS = {
     "dvc_push_multicast": ([_P, _P, _I, _SZ, _P], _I),
     "dvc_peer_read": ([_P, _SZ, _P, _P], _I),
     "dvc_mbx_post": ([_P, _P, _I, _P], _I),
-    "dvc_mbx_wait_desc": ([_P, _U32, _P, _P, _P, _SZ, _P, _P, _P, C.c_ulonglong, _P], _I),
+    "dvc_mbx_wait_desc": ([_P, _U32, _P, _P, _P, _P, C.c_ulonglong, _P], _I),
     "dvc_mbx_wait_done": ([_P, _P, _I, _P, C.c_ulonglong, _P], _I),
-    "dvc_mbx_dispatch": ([_P, _P, _SZ, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _SZ, _P, _P, _P], _I),
+    "dvc_mbx_dispatch": ([_P, _P, _SZ, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _SZ, _P, _P], _I),
     "dvc_mbx_signal": ([_P, _U32, _P], _I),
     "dvc_mbx_poll": ([_P, _P, _I, _P], _I),
-    "dvc_mbx_worker_enqueue": ([_P, _U32, _P, _P, _P, _SZ, _P, _P, _P, C.c_ulonglong, _P, _P, _P], _I),
-    "dvc_mbx_local_dispatch": ([_P, _P, _P, _P, _P, _P, _SZ, _P, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _SZ, _P, _P], _I),
+    "dvc_mbx_worker_enqueue": ([_P, _U32, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _P], _I),
+    "dvc_mbx_local_dispatch": ([_P, _P, _P, _P, _P, _P, _P, _P, C.c_ulonglong, _P, _P, _SZ, _P, _P], _I),
     "dvc_mbx_copy_out": ([_P, _P, _SZ, _P, _P], _I),
-    "dvc_plan_set_mailbox": ([_P, _P, _P, _P, _P, _LL, _LL, _LL, _LL, _LL, _P, _P], _I),
+    "dvc_plan_set_mailbox": ([_P, _P, _P, _P, _P, _P], _I),
     "dvc_resize_u8_indirect": ([_P, _LL, _I, _I, _I, _P, _LL, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _P, _P, _P], _I),
 }
 

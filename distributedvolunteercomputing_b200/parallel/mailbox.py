@@ -61,11 +61,9 @@ class BoxLayout:
         self.raw_stride = (self.H * self.W * 3 + 15) & ~15
         self.slot_bytes = self.B * self.raw_stride
         self.arena_bytes = self.arena_slots * self.slot_bytes
-        nl = self.max_workers * self.lanes
-        n = 2 * nl                         # every lane has a PAIR of descriptors / done words / result slots (sequence parity)
+        n = self.max_workers * self.lanes
         self.epoch_off = 0
-        self.pos_off = _up(4 * self.max_workers)              # one word per lane: the client's current sequence number
-        self.desc_off = _up(self.pos_off + 4 * nl)
+        self.desc_off = _up(4 * self.max_workers)
         self.done_off = _up(self.desc_off + n * DESC_BYTES)
         self.weights_off = _up(self.done_off + 4 * n)
         self.ctl_bytes = _up(self.weights_off + self.weights_bytes)
@@ -82,20 +80,14 @@ class BoxLayout:
     def epoch_addr(self, base: int, w: int) -> int:
         return base + self.epoch_off + 4 * w
 
-    def pos_addr(self, base: int, w: int, l: int) -> int:
-        return base + self.pos_off + 4 * (w * self.lanes + l)
+    def desc_addr(self, base: int, w: int, l: int) -> int:
+        return base + self.desc_off + (w * self.lanes + l) * DESC_BYTES
 
-    def index(self, w: int, l: int, p: int = 0) -> int:
-        return (w * self.lanes + l) * 2 + p
+    def done_addr(self, base: int, w: int, l: int) -> int:
+        return base + self.done_off + (w * self.lanes + l) * 4
 
-    def desc_addr(self, base: int, w: int, l: int, p: int = 0) -> int:
-        return base + self.desc_off + self.index(w, l, p) * DESC_BYTES
-
-    def done_addr(self, base: int, w: int, l: int, p: int = 0) -> int:
-        return base + self.done_off + self.index(w, l, p) * 4
-
-    def res_addr(self, base: int, w: int, l: int, p: int = 0) -> int:
-        return base + self.index(w, l, p) * self.res_slot_bytes
+    def res_addr(self, base: int, w: int, l: int) -> int:
+        return base + (w * self.lanes + l) * self.res_slot_bytes
 
     def arena_off(self, slot: int) -> int:
         return slot * self.slot_bytes
@@ -142,14 +134,19 @@ class WorkerLanes:
             self._hs_keep, self.hs, self.hs_addr = pinned_status(nl * 4)
             self.states = []
             self.graphs: Dict[int, Any] = {}
+            self.my_boxes, self.my_box_count = [], []
             for l in range(nl):
                 st = engine.state(lay.B, lay.H, lay.W, slot=300 + worker * 16 + l)
-                # K1b reads this GPU's own 400-wide frames; K9's sinks are resolved at run time from the control block
-                # (one of the lane's two result slots on the client); the integer boxes also stay local for K10
-                engine.L.check(engine.lib.dvc_plan_set_source(st.plan, L.ptr(st.frames400_flat), st.stride400, None), "plan_set_source")
-                engine.bind_mailbox(st, self.ctl_ptr(l), lay.epoch_addr(ctl_base, worker), self.done_counter[l:l + 1], self.stale,
-                                    (lay.det_off, lay.boxes_off, lay.det_count_off, lay.box_count_off, lay.flags_off))
+                res = lay.res_addr(res_base, worker, l)
+                engine.bind_remote(st, frames_ptr=L.ptr(st.frames400_flat), frame_stride=st.stride400,
+                                   det_ptr=res + lay.det_off, det_count_ptr=res + lay.det_count_off,
+                                   boxes_ptr=res + lay.boxes_off, box_count_ptr=res + lay.box_count_off,
+                                   flags_ptr=res + lay.flags_off, flag_value=0)
+                engine.bind_mailbox(st, self.ctl_ptr(l), lay.epoch_addr(ctl_base, worker), lay.done_addr(ctl_base, worker, l),
+                                    self.done_counter[l:l + 1], self.stale)
                 self.states.append(st)
+                self.my_boxes.append(p2p.tensor_from_ptr(res + lay.boxes_off, (lay.B, 100, 4), torch.int32, self.dev))
+                self.my_box_count.append(p2p.tensor_from_ptr(res + lay.box_count_off, (lay.B,), torch.int32, self.dev))
             # build every lane's CUDA graph now (gates closed: nothing is pulled, nothing is delivered)
             for l in range(nl):
                 with torch.cuda.stream(self.streams[l]):
@@ -175,9 +172,8 @@ class WorkerLanes:
         lay = self.layout
         hs = self.hs_addr + hs_index * HS_DTYPE.itemsize if hs_index is not None else None
         L.check(self.engine.lib.dvc_mbx_wait_desc(lay.desc_addr(self.ctl_base, self.worker, l), expect_seq, self.arena_base,
-                                                  self.local_raw[l].data_ptr(), lay.res_addr(self.res_base, self.worker, l),
-                                                  lay.res_slot_bytes, lay.done_addr(self.ctl_base, self.worker, l), self.ctl_ptr(l),
-                                                  hs, int(timeout_s * 1e9), L.stream_ptr()), "mbx_wait_desc")
+                                                  self.local_raw[l].data_ptr(), self.ctl_ptr(l), hs, int(timeout_s * 1e9),
+                                                  L.stream_ptr()), "mbx_wait_desc")
 
     def enqueue_body(self, l: int):
         """K1a (peer pull of the batch named by the lane's control block) -> network -> K9 (peer push + done word) ->
@@ -218,7 +214,7 @@ class WorkerLanes:
             nl_, lh, lw = m.label_masks.shape
             idh, idw = m.id_mask.shape
             L.check(self.engine.lib.dvc_annotate(L.ptr(st.frames400_flat), st.stride400, None, lay.B, st.h4, st.w4,
-                                                 L.ptr(st.boxes_i), L.ptr(st.box_count), None, L.ptr(m.id_mask),
+                                                 L.ptr(self.my_boxes[l]), L.ptr(self.my_box_count[l]), None, L.ptr(m.id_mask),
                                                  m.id_xy[0], m.id_xy[1], idw, idh, L.ptr(m.label_masks), nl_, m.label_xy[0],
                                                  m.label_xy[1], lw, lh, L.stream_ptr()), "annotate")
 
@@ -233,12 +229,11 @@ class WorkerLanes:
         lay = self.layout
         with torch.cuda.device(self.dev):
             for l in range(lay.lanes):
-                d = p2p.tensor_from_ptr(lay.desc_addr(self.ctl_base, self.worker, l), (2 * DESC_BYTES // 4,), torch.int32, self.dev).cpu()
-                if (int(d[0]) & 0xFFFFFFFF) == L.MBX_SEQ_STOP or (int(d[DESC_BYTES // 4]) & 0xFFFFFFFF) == L.MBX_SEQ_STOP:
+                d = p2p.tensor_from_ptr(lay.desc_addr(self.ctl_base, self.worker, l), (DESC_BYTES // 4,), torch.int32, self.dev)
+                seq = int(d[0].item()) & 0xFFFFFFFF
+                if seq == L.MBX_SEQ_STOP:
                     return False
-                pos = p2p.tensor_from_ptr(lay.pos_addr(self.ctl_base, self.worker, l), (1,), torch.int32, self.dev)
-                seq = int(pos[0].item()) & 0xFFFFFFFF            # the client's current sequence number of this lane
-                nxt = torch.tensor([seq + 1 if seq + 1 < L.MBX_SEQ_STOP else 1], dtype=torch.int64).to(torch.int32)
+                nxt = torch.tensor([seq + 1], dtype=torch.int32)
                 self.ctl[l, CTL_NEXT_SEQ_OFF:CTL_NEXT_SEQ_OFF + 4].copy_(nxt.view(torch.uint8))
             torch.cuda.synchronize(self.dev)
         return True
@@ -277,9 +272,6 @@ class WorkerLanes:
         gexec = [self.graph_exec(l) for l in range(nl)]
         lib = self.engine.lib
         desc_addr = [lay.desc_addr(self.ctl_base, self.worker, l) for l in range(nl)]
-        res_pair = [lay.res_addr(self.res_base, self.worker, l) for l in range(nl)]
-        done_pair = [lay.done_addr(self.ctl_base, self.worker, l) for l in range(nl)]
-        rsb = lay.res_slot_bytes
         local_ptr = [self.local_raw[l].data_ptr() for l in range(nl)]
         sptr = [st_.cuda_stream for st_ in self.streams]
         hs_sz = HS_DTYPE.itemsize
@@ -295,22 +287,21 @@ class WorkerLanes:
                     self.hs[idx]["status"] = 0xFFFF
                     if kind == "full" and self._first_ev is None:
                         # first batch of this serve(): the busy span starts after its wait (two calls, once)
-                        L.check(lib.dvc_mbx_worker_enqueue(desc_addr[l], 0, self.arena_base, local_ptr[l], res_pair[l], rsb,
-                                                           done_pair[l], self.ctl_ptr(l), self.hs_addr + idx * hs_sz,
-                                                           int(stream_timeout_s * 1e9), None, None, sptr[l]), "mbx_worker_enqueue")
+                        L.check(lib.dvc_mbx_worker_enqueue(desc_addr[l], 0, self.arena_base, local_ptr[l], self.ctl_ptr(l),
+                                                           self.hs_addr + idx * hs_sz, int(stream_timeout_s * 1e9), None, None,
+                                                           sptr[l]), "mbx_worker_enqueue")
                         self._first_ev = torch.cuda.Event(enable_timing=True)
                         self._first_ev.record(self.streams[l])
-                        L.check(lib.dvc_mbx_worker_enqueue(None, 0, None, None, None, 0, None, None, None, 0, gexec[l], ev.cuda_event,
-                                                           sptr[l]), "mbx_worker_enqueue")
+                        L.check(lib.dvc_mbx_worker_enqueue(None, 0, None, None, None, None, 0, gexec[l], ev.cuda_event, sptr[l]),
+                                "mbx_worker_enqueue")
                     else:
                         tmo = int((stream_timeout_s if kind == "full" else probe_timeout_s) * 1e9)
-                        L.check(lib.dvc_mbx_worker_enqueue(desc_addr[l], 0, self.arena_base, local_ptr[l], res_pair[l], rsb,
-                                                           done_pair[l], self.ctl_ptr(l), self.hs_addr + idx * hs_sz, tmo,
-                                                           gexec[l] if kind == "full" else None, ev.cuda_event, sptr[l]),
-                                "mbx_worker_enqueue")
+                        L.check(lib.dvc_mbx_worker_enqueue(desc_addr[l], 0, self.arena_base, local_ptr[l], self.ctl_ptr(l),
+                                                           self.hs_addr + idx * hs_sz, tmo, gexec[l] if kind == "full" else None,
+                                                           ev.cuda_event, sptr[l]), "mbx_worker_enqueue")
                 else:
-                    L.check(lib.dvc_mbx_worker_enqueue(None, 0, None, None, None, 0, None, None, None, 0, gexec[l], ev.cuda_event,
-                                                       sptr[l]), "mbx_worker_enqueue")
+                    L.check(lib.dvc_mbx_worker_enqueue(None, 0, None, None, None, None, 0, gexec[l], ev.cuda_event, sptr[l]),
+                            "mbx_worker_enqueue")
                 queues[l].append((kind, idx, ev))
                 return
             with torch.cuda.stream(self.streams[l]):
@@ -412,44 +403,39 @@ class ClientBox:
             self.arena = p2p.DevBuffer(lay.arena_bytes, self.dev)
             if engine is not None and wbytes:
                 engine.export_weights(self.ctl.tensor(torch.uint8, (wbytes,), offset_bytes=lay.weights_off))
-            nl = max_workers * lanes
-            n = 2 * nl                         # (worker, lane, parity): two dispatches may be outstanding per lane
+            n = max_workers * lanes
             self._hs_keep, self.hs, self.hs_addr = pinned_status(n)
             self.h_res = torch.empty((n, lay.copy_bytes), dtype=torch.uint8).pin_memory()
-            # posts first: they must never queue behind a parked done-wait, so they get their own streams (one per worker)
-            self.post_streams = [torch.cuda.Stream(device=self.dev) for _ in range(max_workers)]
-            self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(nl)]          # one per lane: done-waits in order
+            self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(n)]
             self.events = [torch.cuda.Event() for _ in range(n)]
             for k in range(n):                 # materialise the lazily created CUDA events
-                self.events[k].record(self.streams[k // 2])
+                self.events[k].record(self.streams[k])
             self.ctrl_stream = torch.cuda.Stream(device=self.dev)
             torch.cuda.synchronize(self.dev)
-        self.seq = [[0] * lanes for _ in range(max_workers)]       # last sequence number posted per lane (parity = seq & 1)
+        self.seq = [[0] * lanes for _ in range(max_workers)]
         self.epoch = [0] * max_workers
-        self.busy = [False] * n                                    # per (worker, lane, parity), see layout.index
+        self.busy = [[False] * lanes for _ in range(max_workers)]
         self.free_slots = list(range(slots - 1, -1, -1))
         self._hs_status = self.hs["status"]
         self._cache = []
-        for k in range(n):
-            w, l, par = k // (2 * lanes), (k // 2) % lanes, k & 1
+        for k in range(max_workers * lanes):
+            w, l = divmod(k, lanes)
             d = L.MbxDesc()
-            self._cache.append({"desc": d, "desc_ref": C.byref(d), "desc_addr": lay.desc_addr(self.ctl.ptr, w, l, par),
-                                "done_addr": lay.done_addr(self.ctl.ptr, w, l, par), "hs": self.hs_addr + k * HS_DTYPE.itemsize,
-                                "res": lay.res_addr(self.res.ptr, w, l, par), "h_res": self.h_res[k].data_ptr(),
-                                "event": self.events[k].cuda_event, "stream": self.streams[k // 2].cuda_stream,
-                                "post_stream": self.post_streams[w].cuda_stream,
-                                "desc_pair": lay.desc_addr(self.ctl.ptr, w, l, 0), "res_pair": lay.res_addr(self.res.ptr, w, l, 0),
-                                "done_pair": lay.done_addr(self.ctl.ptr, w, l, 0),
-                                "desc_addr_arr": (C.c_void_p * 1)(lay.desc_addr(self.ctl.ptr, w, l, par)),
-                                "done_addr_arr": (C.c_void_p * 1)(lay.done_addr(self.ctl.ptr, w, l, par)),
+            self._cache.append({"desc": d, "desc_ref": C.byref(d), "desc_addr": lay.desc_addr(self.ctl.ptr, w, l),
+                                "done_addr": lay.done_addr(self.ctl.ptr, w, l), "hs": self.hs_addr + k * HS_DTYPE.itemsize,
+                                "res": lay.res_addr(self.res.ptr, w, l), "h_res": self.h_res[k].data_ptr(),
+                                "event": self.events[k].cuda_event, "stream": self.streams[k].cuda_stream,
+                                "desc_addr_arr": (C.c_void_p * 1)(lay.desc_addr(self.ctl.ptr, w, l)),
+                                "done_addr_arr": (C.c_void_p * 1)(lay.done_addr(self.ctl.ptr, w, l)),
                                 "seq_arr": (C.c_uint32 * 1)(0)})
         # one process driving several GPUs from several threads must re-select the device in the library's own CUDA
         # runtime on every call; a process that only ever uses the client's GPU (torchrun, spawned workers) need not
         self._set_device_each_call = False
         self._local_gexec: Dict[Tuple[int, int], int] = {}
-        self._ev_arr = (C.c_void_p * n)(*[self.events[k].cuda_event for k in range(n)])
-        self._busy_arr = (C.c_ubyte * n)()
-        self._done_arr = (C.c_ubyte * n)()
+        n_ev = max_workers * lanes
+        self._ev_arr = (C.c_void_p * n_ev)(*[self.events[k].cuda_event for k in range(n_ev)])
+        self._busy_arr = (C.c_ubyte * n_ev)()
+        self._done_arr = (C.c_ubyte * n_ev)()
         self.local: Dict[int, WorkerLanes] = {}        # workers living on the client's own GPU (same process)
         self._views: Dict[int, Dict[str, np.ndarray]] = {}
         self.dispatches = 0
@@ -489,78 +475,52 @@ class ClientBox:
                                             self.ctrl_stream.cuda_stream), "mbx_signal")
             self.ctrl_stream.synchronize()
 
-    def _post_both(self, worker: int, seq_value: int):
-        """Write `seq_value` into both descriptors of every lane of `worker` (stop, or 0 = nothing posted)."""
+    def _post_all_lanes(self, worker: int, seqs: Sequence[int]):
         lay = self.layout
-        for l0 in range(0, lay.lanes, L.MBX_MAX_GROUP // 2):
-            ls = range(l0, min(lay.lanes, l0 + L.MBX_MAX_GROUP // 2))
-            addrs = [lay.desc_addr(self.ctl.ptr, worker, l, par) for l in ls for par in (0, 1)]
-            n = len(addrs)
-            ptrs = (C.c_void_p * n)(*addrs)
-            descs = (L.MbxDesc * n)(*[L.MbxDesc(seq_value & 0xFFFFFFFF, self.epoch[worker], 0, 0, 0, 0, 0) for _ in range(n)])
+        n = lay.lanes
+        ptrs = (C.c_void_p * n)(*[lay.desc_addr(self.ctl.ptr, worker, l) for l in range(n)])
+        descs = (L.MbxDesc * n)(*[L.MbxDesc(int(seqs[l]) & 0xFFFFFFFF, self.epoch[worker], 0, 0, 0, 0, 0) for l in range(n)])
+        with torch.cuda.device(self.dev):
+            L.set_device(self.dev)
             L.check(self.lib.dvc_mbx_post(ptrs, descs, n, self.ctrl_stream.cuda_stream), "mbx_post")
+            self.ctrl_stream.synchronize()
 
-    def cancel(self, worker: int, lane: int, par: int):
-        """Release a pending done-wait now (the worker is gone, nobody will publish the word): the client writes the
-        awaited sequence number itself.  The caller ignores what the poll then reports."""
-        k = self.layout.index(worker, lane, par)
-        if not self.busy[k]:
+    def cancel(self, worker: int, lane: int):
+        """Release the lane's pending done-wait now (the worker is gone, nobody will publish the word): the client writes
+        the awaited sequence number itself.  The caller ignores what the lane's poll then reports."""
+        if not self.busy[worker][lane]:
             return
         with torch.cuda.device(self.dev):
             L.set_device(self.dev)
-            L.check(self.lib.dvc_mbx_signal(self._cache[k]["done_addr"], self._cache[k]["desc"].seq,
+            L.check(self.lib.dvc_mbx_signal(self.layout.done_addr(self.ctl.ptr, worker, lane), self.seq[worker][lane],
                                             self.ctrl_stream.cuda_stream), "mbx_signal")
 
     def stop_worker(self, worker: int):
-        """Tell the worker's serving loop to return (both descriptors of every lane get the stop sequence number)."""
-        with torch.cuda.device(self.dev):
-            L.set_device(self.dev)
-            self._post_both(worker, L.MBX_SEQ_STOP)
-            self.ctrl_stream.synchronize()
+        """Tell the worker's serving loop to return (every lane's descriptor gets the stop sequence number)."""
+        self._post_all_lanes(worker, [L.MBX_SEQ_STOP] * self.layout.lanes)
 
     def reset_worker(self, worker: int):
-        """Before a worker (re)joins: the lanes' position words show the client's current sequence numbers and the
-        descriptors are cleared (which also clears a stop)."""
-        lay = self.layout
-        with torch.cuda.device(self.dev):
-            L.set_device(self.dev)
-            self._post_both(worker, 0)
-            for l in range(lay.lanes):
-                L.check(self.lib.dvc_mbx_signal(lay.pos_addr(self.ctl.ptr, worker, l), self.seq[worker][l],
-                                                self.ctrl_stream.cuda_stream), "mbx_signal")
-            self.ctrl_stream.synchronize()
+        """Before a worker (re)joins: descriptors show the client's current position again (clears a stop)."""
+        self._post_all_lanes(worker, self.seq[worker])
 
     # ------------------------------------------------------------------ dispatch / poll
-    def room(self, worker: int, lane: int) -> bool:
-        """True when the lane can take another dispatch: the slot pair member its next sequence number maps to is free
-        (at most two dispatches are outstanding per lane; the worker runs them back to back)."""
-        nxt = self.seq[worker][lane] + 1
-        if nxt >= L.MBX_SEQ_STOP:
-            nxt = 1
-        return not self.busy[self.layout.index(worker, lane, nxt & 1)]
-
-    def outstanding(self, worker: int, lane: int) -> int:
-        k = self.layout.index(worker, lane, 0)
-        return int(self.busy[k]) + int(self.busy[k + 1])
-
     def dispatch(self, worker: int, lane: int, slot: int, n_valid: int, batch_id: int, kind: int = 0,
-                 host_src: Optional[torch.Tensor] = None, fetch: bool = True) -> int:
-        """Hand arena slot `slot` to (worker, lane).  Queued on the client: [upload of `host_src` into the slot] -> post
-        descriptor (worker's post stream) and wait for the done word -> read the result slot back into pinned memory ->
-        event (lane's stream).  Returns the parity of the slot pair member used (pass it to `poll` / `result`)."""
+                 host_src: Optional[torch.Tensor] = None, fetch: bool = True):
+        """Hand arena slot `slot` to (worker, lane).  Everything is queued on the (worker, lane) stream of the client:
+        [upload of `host_src` into the slot] -> post descriptor -> wait for the done word -> read the result slot back
+        into pinned memory -> event.  Returns at once; see `poll`."""
         lay = self.layout
+        assert not self.busy[worker][lane]
+        k = worker * lay.lanes + lane
         self.seq[worker][lane] += 1
         if self.seq[worker][lane] >= L.MBX_SEQ_STOP:
             self.seq[worker][lane] = 1
         seq = self.seq[worker][lane]
-        par = seq & 1
-        k = lay.index(worker, lane, par)
-        assert not self.busy[k], "both dispatches of this lane are still outstanding"
-        c = self._cache[k]                 # per (worker, lane, parity): addresses and handles resolved once
+        c = self._cache[k]                 # per (worker, lane): addresses and handles resolved once
         desc = c["desc"]
         desc.seq, desc.epoch, desc.n_valid, desc.kind = seq, self.epoch[worker], n_valid, kind
         desc.src_off, desc.batch_id = lay.arena_off(slot), batch_id & 0xFFFFFFFF
-        stream = self.streams[k // 2]
+        stream = self.streams[k]
         hs = c["hs"]
         self._hs_status[k] = 0xFFFF
         res = c["res"]
@@ -577,27 +537,26 @@ class ClientBox:
                 L.set_device(self.dev)
             rc = self.lib.dvc_mbx_dispatch(src_ptr, self.arena.ptr + desc.src_off, src_bytes, c["desc_addr"], c["desc_ref"],
                                            c["done_addr"], hs, tmo, res, c["h_res"] if fetch else None, lay.copy_bytes,
-                                           c["event"], c["stream"], c["post_stream"])
+                                           c["event"], c["stream"])
             if rc:
                 L.check(rc, "mbx_dispatch")
-            self.busy[k] = True
+            self.busy[worker][lane] = True
             self.dispatches += 1
-            return par
-        # the client's own GPU works too: same kernels, same words, queued inline on the lane's stream (a wait never spins
-        # on something a later launch of this GPU has to produce); a second dispatch simply queues behind the first
+            return
+        # the client's own GPU works too: same kernels, same words, queued inline on the same stream (a wait never spins
+        # on something a later launch of this GPU has to produce)
         gexec = self._local_gexec.get((worker, lane))
         if gexec is None and loc.engine.cfg.use_cuda_graph:
             gexec = self._local_gexec[(worker, lane)] = loc.graph_exec(lane)
         if gexec is not None and host_src is None:
-            rc = self.lib.dvc_mbx_local_dispatch(c["desc_addr"], c["desc_ref"], c["desc_pair"], self.arena.ptr,
-                                                 loc.local_raw[lane].data_ptr(), c["res_pair"], lay.res_slot_bytes, c["done_pair"],
+            rc = self.lib.dvc_mbx_local_dispatch(c["desc_addr"], c["desc_ref"], self.arena.ptr, loc.local_raw[lane].data_ptr(),
                                                  loc.ctl_ptr(lane), gexec, c["done_addr"], hs, tmo, res,
                                                  c["h_res"] if fetch else None, lay.copy_bytes, c["event"], c["stream"])
             if rc:
                 L.check(rc, "mbx_local_dispatch")
-            self.busy[k] = True
+            self.busy[worker][lane] = True
             self.dispatches += 1
-            return par
+            return
         with torch.cuda.device(self.dev), torch.cuda.stream(stream):
             L.set_device(self.dev)
             if host_src is not None and kind == 1:
@@ -615,27 +574,28 @@ class ClientBox:
                 L.check(self.lib.dvc_mbx_copy_out(res, c["h_res"], lay.copy_bytes, c["event"], sp), "mbx_copy_out")
             else:
                 self.events[k].record(stream)
-        self.busy[k] = True
+        self.busy[worker][lane] = True
         self.dispatches += 1
-        return par
 
-    def poll(self, worker: int, lane: int, par: int) -> Optional[str]:
-        """None while that dispatch is still running (or nothing is), else "ok" / "timeout" once."""
-        k = self.layout.index(worker, lane, par)
-        if not self.busy[k] or not self.events[k].query():
+    def poll(self, worker: int, lane: int) -> Optional[str]:
+        """None while the lane's dispatch is still running (or nothing is), else "ok" / "timeout" once."""
+        if not self.busy[worker][lane]:
             return None
-        self.busy[k] = False
+        k = worker * self.layout.lanes + lane
+        if not self.events[k].query():
+            return None
+        self.busy[worker][lane] = False
         return "ok" if int(self.hs[k]["status"]) == L.MBX_GO else "timeout"
 
-    def poll_all(self) -> List[Tuple[int, int, int, str]]:
-        """Every dispatch that has finished since the last call, as (worker, lane, parity, "ok" | "timeout"); one native
-        call queries all events."""
+    def poll_all(self) -> List[Tuple[int, int, str]]:
+        """Every busy lane whose dispatch has finished since the last call, as (worker, lane, "ok" | "timeout"); one
+        native call queries all events."""
         lanes = self.layout.lanes
         n = len(self._busy_arr)
         busy = self.busy
         any_busy = False
         for k in range(n):
-            b = busy[k]
+            b = busy[k // lanes][k % lanes]
             self._busy_arr[k] = b
             any_busy = any_busy or b
         if not any_busy:
@@ -647,16 +607,17 @@ class ClientBox:
         if found:
             for k in range(n):
                 if self._done_arr[k]:
-                    busy[k] = False
-                    out.append((k // (2 * lanes), (k // 2) % lanes, k & 1, "ok" if int(self._hs_status[k]) == L.MBX_GO else "timeout"))
+                    w, l = divmod(k, lanes)
+                    busy[w][l] = False
+                    out.append((w, l, "ok" if int(self._hs_status[k]) == L.MBX_GO else "timeout"))
         return out
 
-    def wait_ns(self, worker: int, lane: int, par: int = 0) -> int:
-        return int(self.hs[self.layout.index(worker, lane, par)]["wait_ns"])
+    def wait_ns(self, worker: int, lane: int) -> int:
+        return int(self.hs[worker * self.layout.lanes + lane]["wait_ns"])
 
-    def result(self, worker: int, lane: int, par: int = 0) -> Dict[str, np.ndarray]:
-        """Views into the pinned copy of that dispatch's result slot; valid until the slot pair member is dispatched again."""
-        k = self.layout.index(worker, lane, par)
+    def result(self, worker: int, lane: int) -> Dict[str, np.ndarray]:
+        """Views into the pinned copy of the lane's last result slot; valid until the lane's next dispatch."""
+        k = worker * self.layout.lanes + lane
         v = self._views.get(k)
         if v is None:
             lay, B = self.layout, self.layout.B
@@ -668,10 +629,10 @@ class ClientBox:
             self._views[k] = v
         return v
 
-    def device_result(self, worker: int, lane: int, par: int = 0) -> Dict[str, torch.Tensor]:
+    def device_result(self, worker: int, lane: int) -> Dict[str, torch.Tensor]:
         """The result slot itself (device tensors on the client GPU)."""
         lay, B = self.layout, self.layout.B
-        off = lay.res_addr(0, worker, lane, par)
+        off = lay.res_addr(0, worker, lane)
         return {"det": self.res.tensor(torch.float32, (B, 100, 7), offset_bytes=off + lay.det_off),
                 "boxes_i": self.res.tensor(torch.int32, (B, 100, 4), offset_bytes=off + lay.boxes_off),
                 "det_count": self.res.tensor(torch.int32, (B,), offset_bytes=off + lay.det_count_off),
@@ -699,7 +660,6 @@ class _Flight:
     batch: Batch
     worker: int
     lane: int
-    par: int
     slot: int
     t0: float
     cancelled: bool = False
@@ -727,8 +687,7 @@ class ElasticBox:
         self.fetch = fetch
         self.log = log or (lambda m: None)
         self.metrics = metrics             # utils.metrics.Metrics (optional): per-batch latency, membership events
-        self.flights: Dict[Tuple[int, int, int], _Flight] = {}       # (worker, lane, slot-pair parity)
-        self.depth = 2                     # dispatches outstanding per lane (the lane's two descriptors)
+        self.flights: Dict[Tuple[int, int], _Flight] = {}
         self.alive: Dict[int, bool] = {}
         self.epoch_counter = 0
         self.stats = collections.Counter()
@@ -747,7 +706,7 @@ class ElasticBox:
         self.client.reset_worker(w)
         self.client.set_epoch(w, self.epoch_counter)
         self.alive[w] = True
-        self.sched.join(self.name(w), capacity=self.lay.lanes * self.depth)
+        self.sched.join(self.name(w), capacity=self.lay.lanes)
         self.stats["joins"] += 1
         if self.metrics is not None:
             self.metrics.emit("join", worker=self.name(w), epoch=self.epoch_counter)
@@ -760,10 +719,10 @@ class ElasticBox:
         self.epoch_counter += 1
         self.client.set_epoch(w, self.epoch_counter)          # K14: whatever it still delivers is stale from here on
         requeued = self.sched.leave(self.name(w), reason)
-        for (fw, fl, fp), flight in self.flights.items():
+        for (fw, fl), flight in self.flights.items():
             if fw == w and not flight.cancelled:
                 flight.cancelled = True            # re-queued above; its done word will not come, do not wait for it
-                self.client.cancel(fw, fl, fp)
+                self.client.cancel(fw, fl)
         if stop:
             self.client.stop_worker(w)
         self.stats["leaves" if reason == "leave" else "failures"] += 1
@@ -838,7 +797,7 @@ class ElasticBox:
         Returns the number of batches completed by this call."""
         done = 0
         if hasattr(self.client, "poll_all"):
-            finished = [((w, l, q), r) for w, l, q, r in self.client.poll_all() if (w, l, q) in self.flights]
+            finished = [((w, l), r) for w, l, r in self.client.poll_all() if (w, l) in self.flights]
         else:
             finished = [(key, r) for key, r in ((key, self.client.poll(*key)) for key in list(self.flights.keys())) if r is not None]
         for key, r in finished:
@@ -854,7 +813,7 @@ class ElasticBox:
                         self.metrics.observe("batch_latency_ms", (time.monotonic() - fl.t0) * 1e3)
                         self.metrics.inc("frames_out", len(fl.batch.frame_ids))
                     if self.on_result is not None:
-                        self.on_result(fl.batch, self.client.result(fl.worker, fl.lane, fl.par) if self.fetch else None, fl.worker)
+                        self.on_result(fl.batch, self.client.result(fl.worker, fl.lane) if self.fetch else None, fl.worker)
                     pl = fl.batch.payload
                     if not pl["keep"] and pl["slot"] is not None:
                         self.client.free_slot(pl["slot"])
@@ -873,14 +832,7 @@ class ElasticBox:
                 break
             batch, winfo, _epoch = d
             w = int(winfo.addr[3:])
-            # the emptiest lane that has room (a lane takes two dispatches: the second is posted while the first runs, so
-            # the worker goes from one to the next without a host round trip)
-            lane, best = None, 99
-            for l in range(self.lay.lanes):
-                if self.client.room(w, l):
-                    o = self.client.outstanding(w, l)
-                    if o < best:
-                        lane, best = l, o
+            lane = next((l for l in range(self.lay.lanes) if (w, l) not in self.flights), None)
             if lane is None or not self.alive.get(w):
                 self.sched.undo_dispatch(batch.batch_id)      # an old flight of a revived worker still holds the lane
                 break
@@ -895,9 +847,9 @@ class ElasticBox:
                         break
                 # a re-dispatched batch is uploaded again on ITS lane's stream: the first upload was ordered on another
                 host = pl["host"]
-            par = self.client.dispatch(w, lane, pl["slot"], len(batch.frame_ids), batch.batch_id, kind=pl.get("kind", 0),
-                                       host_src=host, fetch=self.fetch)
-            self.flights[(w, lane, par)] = _Flight(batch, w, lane, par, pl["slot"], time.monotonic())
+            self.client.dispatch(w, lane, pl["slot"], len(batch.frame_ids), batch.batch_id, kind=pl.get("kind", 0),
+                                 host_src=host, fetch=self.fetch)
+            self.flights[(w, lane)] = _Flight(batch, w, lane, pl["slot"], time.monotonic())
             self.stats["dispatched"] += 1
         return done
 

@@ -284,8 +284,6 @@ typedef struct dvc_mbx_lane_ctl {
   uint32_t n_valid;
   uint32_t next_seq;   /* the lane's position: the sequence number its next wait expects (advanced on every GO) */
   uint32_t reserved;
-  uint8_t* res;        /* result slot of this batch on the client (one of the lane's two, by sequence parity): K9's sinks */
-  uint32_t* done;      /* the done word K9 publishes for this batch (one of the lane's two) */
 } dvc_mbx_lane_ctl;
 
 /* Host-visible (pinned, mapped) mirror of what a wait saw; `wait_ns` is how long the kernel polled. */
@@ -303,15 +301,12 @@ typedef struct dvc_mbx_host_status {
 /* Client: publish n descriptors (n <= DVC_MBX_MAX_GROUP).  h_desc_ptrs[i] is the device address of descriptor i
  * (client-local); h_descs[i] its new contents (seq included).  Host arrays, copied into the launch. */
 int dvc_mbx_post(void* const* h_desc_ptrs, const dvc_mbx_desc* h_descs, int n, void* stream);
-/* Worker: wait (at most timeout_ns) for the lane's next dispatch, then fill *ctl and *h_status.
- * A lane has TWO descriptors, two result slots and two done words, used alternately by sequence parity, so the client
- * can post batch n+1 while the worker still runs batch n: the worker then starts n+1 with no host round trip in
- * between.  `desc_pair` / `res_pair` / `done_pair` are the bases of those pairs (peer addresses on the client GPU);
- * the kernel polls desc_pair[seq & 1] until its seq equals expect_seq (0: use and advance ctl->next_seq, so several
- * waits can be queued ahead) or DVC_MBX_SEQ_STOP.  `arena_base` is the worker's mapping of the arena, `local_src` the
- * worker's own frame buffer (kind 1).  h_status is pinned mapped host memory (device-accessible address) or NULL. */
-int dvc_mbx_wait_desc(const dvc_mbx_desc* desc_pair, uint32_t expect_seq, const uint8_t* arena_base, const uint8_t* local_src,
-                      uint8_t* res_pair, size_t res_slot_bytes, uint32_t* done_pair,
+/* Worker: wait (at most timeout_ns) until desc->seq == expect_seq (0: use and advance ctl->next_seq, so several
+ * waits can be queued ahead of their batches) or == DVC_MBX_SEQ_STOP, then fill *ctl and
+ * *h_status.  `desc` usually is a peer address on the client GPU; `arena_base` is the worker's
+ * mapping of the arena, `local_src` the worker's own frame buffer (kind 1).  h_status is pinned mapped host memory
+ * (device-accessible address) or NULL. */
+int dvc_mbx_wait_desc(const dvc_mbx_desc* desc, uint32_t expect_seq, const uint8_t* arena_base, const uint8_t* local_src,
                       dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* h_status, unsigned long long timeout_ns, void* stream);
 /* Client: wait (at most timeout_ns) until *done_ptrs[i] == seqs[i] for every i < n; h_status[i].status = GO or
  * NOTHING (timed out).  h_status is pinned mapped host memory, one entry per waited word. */
@@ -319,11 +314,10 @@ int dvc_mbx_wait_done(void* const* h_done_ptrs, const uint32_t* h_seqs, int n, d
                       unsigned long long timeout_ns, void* stream);
 /* Client, one call per dispatch to a remote worker, all on `stream`: optional host->device copy of the frames into
  * the arena, dvc_mbx_post of one descriptor, dvc_mbx_wait_done on its done word, optional device->host copy of the
- * result slot, optional cudaEventRecord(event).  Pointers that are NULL switch their step off.  With `post_stream` the
- * upload and the post are queued there instead (the lane's stream may still be parked in the previous batch's done-wait). */
+ * result slot, optional cudaEventRecord(event).  Pointers that are NULL switch their step off. */
 int dvc_mbx_dispatch(const void* h_src, void* d_dst, size_t src_bytes, void* desc_ptr, const dvc_mbx_desc* h_desc,
                      void* done_ptr, dvc_mbx_host_status* h_status, unsigned long long timeout_ns,
-                     const void* d_result, void* h_result, size_t result_bytes, void* event, void* stream, void* post_stream);
+                     const void* d_result, void* h_result, size_t result_bytes, void* event, void* stream);
 /* Device->host copy of a result slot into pinned memory, then cudaEventRecord(event) (event may be NULL). */
 int dvc_mbx_copy_out(const void* d_result, void* h_result, size_t bytes, void* event, void* stream);
 /* Host-side helpers that fold what would be several Python-level CUDA calls into one (the client dispatches ~10^4
@@ -332,26 +326,21 @@ int dvc_mbx_copy_out(const void* d_result, void* h_result, size_t bytes, void* e
  * NULL switches a step off.  dvc_mbx_local_dispatch: the client's own GPU as a worker, everything on one stream:
  * post -> wait_desc (immediate) -> graph -> wait_done -> copy-out -> event. */
 int dvc_mbx_poll(void* const* h_events, const unsigned char* h_busy, int n, unsigned char* h_done);
-int dvc_mbx_worker_enqueue(const dvc_mbx_desc* desc_pair, uint32_t expect_seq, const uint8_t* arena_base, const uint8_t* local_src,
-                           uint8_t* res_pair, size_t res_slot_bytes, uint32_t* done_pair,
+int dvc_mbx_worker_enqueue(const dvc_mbx_desc* desc, uint32_t expect_seq, const uint8_t* arena_base, const uint8_t* local_src,
                            dvc_mbx_lane_ctl* ctl, dvc_mbx_host_status* h_status, unsigned long long timeout_ns,
                            void* graph_exec, void* event, void* stream);
-int dvc_mbx_local_dispatch(void* desc_ptr, const dvc_mbx_desc* h_desc, const dvc_mbx_desc* desc_pair, const uint8_t* arena_base,
-                           const uint8_t* local_src, uint8_t* res_pair, size_t res_slot_bytes, uint32_t* done_pair,
+int dvc_mbx_local_dispatch(void* desc_ptr, const dvc_mbx_desc* h_desc, const uint8_t* arena_base, const uint8_t* local_src,
                            dvc_mbx_lane_ctl* ctl, void* graph_exec, void* done_ptr, dvc_mbx_host_status* h_status,
                            unsigned long long timeout_ns, const void* d_result, void* h_result, size_t result_bytes,
                            void* event, void* stream);
 /* st.release.sys of one word (epoch bump, hand-rolled completion after an extra copy). */
 int dvc_mbx_signal(uint32_t* word, uint32_t value, void* stream);
-/* Bind a plan to a lane: K1b's gate reads ctl->gate_now / gate_expect; K9 takes its sinks (ctl->res + the given byte
- * offsets of rows, integer boxes, the two count arrays and the per-frame flags), its flag value and its done word from
- * the control block at run time, compares *live_epoch (the client's word for this worker, a peer address) with
- * ctl->gate_expect, counts rejected frames in *stale_count and lets the last CTA of the batch publish the done word.
- * Integer boxes and their counts are also written to local_boxes / local_box_count (this GPU) for the overlay kernel.
- * `done_counter` is one zero-initialised device word owned by the lane. */
-int dvc_plan_set_mailbox(dvc_plan*, const dvc_mbx_lane_ctl* ctl, const uint32_t* live_epoch, uint32_t* done_counter,
-                         uint32_t* stale_count, long long off_det, long long off_boxes, long long off_det_count,
-                         long long off_box_count, long long off_flags, int* local_boxes, int* local_box_count);
+/* Bind a plan to a lane: K1b's gate reads ctl->gate_now / gate_expect, K9 takes its flag value from ctl->flag_value,
+ * compares *live_epoch (the client's word for this worker, a peer address) with ctl->gate_expect, counts rejected
+ * frames in *stale_count and lets the last CTA of the batch publish *done_word = flag value.  `done_counter` is one
+ * zero-initialised device word owned by the lane. */
+int dvc_plan_set_mailbox(dvc_plan*, const dvc_mbx_lane_ctl* ctl, const uint32_t* live_epoch, uint32_t* done_word,
+                         uint32_t* done_counter, uint32_t* stale_count);
 /* K1a whose source base pointer is read from device memory at run time (`*src_indirect`, e.g. &ctl->src) and which is
  * gated like dvc_resize_u8_gated. */
 int dvc_resize_u8_indirect(const uint8_t* const* src_indirect, long long src_frame_stride, int B, int sh, int sw,

@@ -58,7 +58,6 @@ def test_dispatch_equals_plain_engine(setup):
             assert np.array_equal(g["boxes_i"][k, :ref.box_count[k]], ref.boxes_i[k, :ref.box_count[k]])
         total += int(ref.det_count.sum())
     assert total > 0, "the comparison must see detections"
-    assert box.stats["dispatched"] == 5 and max(client.seq[0]) >= 2, "lanes took a second dispatch while the first was running"
     # the last batch's annotated frames stay on the worker: lane of the last dispatch
     ref = eng.process(batches[-1]).numpy()
     assert any(np.array_equal(lanes.frames400(l).cpu().numpy(), ref.frames400) for l in range(2))
@@ -74,8 +73,8 @@ def test_silent_worker_times_out_without_hanging(setup):
         box.submit_host(frames(B, 50 + i), range(B))
     assert box.drain(20.0), box.stats
     assert box.stats["completed"] == 6 and box.failed_workers == [1] and box.stats["redispatched"] >= 1
-    waited = max(client.wait_ns(1, l, q) for l in range(client.layout.lanes) for q in (0, 1))
-    assert waited >= 0.04e9, "the wait kernel ran into its deadline, it did not spin for ever"
+    k = 1 * client.layout.lanes
+    assert int(client.hs[k]["wait_ns"]) >= 0.04e9, "the wait kernel ran into its deadline, it did not spin for ever"
     box.remove_worker(0, stop=False)
 
 
@@ -87,16 +86,16 @@ def test_stale_epoch_is_rejected_by_k9(setup):
     client.epoch[0] -= 1                   # the descriptor will carry an epoch older than the live word
     slot = client.alloc_slot()
     client.slot_tensor(slot).copy_(frames(B, 99))
-    for q in (0, 1):
-        client.device_result(0, 0, q)["det_count"].fill_(-7)
-    par = client.dispatch(0, 0, slot, B, 1234)
+    dr = client.device_result(0, 0)
+    dr["det_count"].fill_(-7)
+    client.dispatch(0, 0, slot, B, 1234)
     torch.cuda.synchronize()
-    assert client.poll(0, 0, par) == "timeout", "a batch whose frames were rejected never publishes its done word"
+    assert client.poll(0, 0) == "timeout", "a batch whose frames were rejected never publishes its done word"
     assert lanes.stale_count() - stale0 == B
-    assert all((client.device_result(0, 0, q)["det_count"] == -7).all() for q in (0, 1)), "stale rows were delivered"
+    assert (dr["det_count"] == -7).all(), "stale rows were delivered"
     client.epoch[0] += 1
-    par = client.dispatch(0, 0, slot, B, 1235)   # the lane is usable again (its arrival counter went back to zero)
+    client.dispatch(0, 0, slot, B, 1235)   # the lane is usable again (its arrival counter went back to zero)
     torch.cuda.synchronize()
-    assert client.poll(0, 0, par) == "ok" and (client.device_result(0, 0, par)["det_count"] >= 0).all()
+    assert client.poll(0, 0) == "ok" and (dr["det_count"] >= 0).all()
     client.free_slot(slot)
     box.remove_worker(0, stop=False)
