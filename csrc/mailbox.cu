@@ -81,7 +81,7 @@ __global__ void mbx_wait_desc_kernel(const dvc_mbx_desc* desc, uint32_t expect_s
     ctl->gate_now = epoch;
     ctl->gate_expect = epoch;
     ctl->flag_value = seq;
-    ctl->next_seq = seq + 1u;
+    ctl->next_seq = (seq + 1u >= DVC_MBX_SEQ_STOP) ? 1u : seq + 1u;      // 0 and 0xFFFFFFFF are never sequence numbers (the client wraps to 1 too)
   } else {
     ctl->src = local_src;
     ctl->gate_now = 0u;              // K1a / K1b skip their reads, K9 delivers nothing and does not count it as stale

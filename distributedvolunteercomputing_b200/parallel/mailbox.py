@@ -233,7 +233,7 @@ class WorkerLanes:
                 seq = int(d[0].item()) & 0xFFFFFFFF
                 if seq == L.MBX_SEQ_STOP:
                     return False
-                nxt = torch.tensor([seq + 1], dtype=torch.int32)
+                nxt = torch.tensor([seq + 1 if seq + 1 < L.MBX_SEQ_STOP else 1], dtype=torch.int64).to(torch.int32)
                 self.ctl[l, CTL_NEXT_SEQ_OFF:CTL_NEXT_SEQ_OFF + 4].copy_(nxt.view(torch.uint8))
             torch.cuda.synchronize(self.dev)
         return True
