@@ -174,3 +174,27 @@ def test_dropped_batches_are_reported():
         s.next_dispatch()
         s.fail(b.batch_id)
     assert [d.batch_id for d in dropped] == [b.batch_id] and list(s.dropped)[0] is b
+
+
+def test_box_layout_regions_do_not_overlap_and_are_aligned():
+    """Every descriptor, done word, epoch word and result slot has its own bytes; descriptors are 8-byte aligned (the post
+    kernel checks that), result slots 256-byte, arena slots 16-byte (K1a's vector loads)."""
+    for (W_, Ln, B, H, Wd) in [(8, 4, 64, 300, 300), (2, 2, 4, 120, 160), (8, 3, 16, 720, 1280), (3, 1, 1, 1080, 1920), (5, 2, 7, 97, 399)]:
+        lay = BoxLayout(W_, Ln, B, H, Wd, arena_slots=W_ * Ln + 4, weights_bytes=12345)
+        spans = []
+        for w in range(W_):
+            spans.append((lay.epoch_addr(0, w), 4))
+            for l in range(Ln):
+                spans.append((lay.desc_addr(0, w, l), 32))
+                spans.append((lay.done_addr(0, w, l), 4))
+                assert lay.desc_addr(0, w, l) % 8 == 0
+        spans.append((lay.weights_off, lay.weights_bytes))
+        spans.sort()
+        for (a, n), (b, _) in zip(spans, spans[1:]):
+            assert a + n <= b, (spans,)
+        assert spans[-1][0] + spans[-1][1] <= lay.ctl_bytes
+        res = sorted(lay.res_addr(0, w, l) for w in range(W_) for l in range(Ln))
+        assert all(b - a >= lay.res_slot_bytes for a, b in zip(res, res[1:])) and res[-1] + lay.res_slot_bytes <= lay.res_bytes
+        assert all(r % 256 == 0 for r in res) and lay.flags_off + 4 * B <= lay.res_slot_bytes and lay.copy_bytes == lay.flags_off
+        assert lay.raw_stride % 16 == 0 and lay.raw_stride >= H * Wd * 3 and lay.arena_off(3) == 3 * B * lay.raw_stride
+        assert lay.arena_bytes == lay.arena_slots * lay.slot_bytes
