@@ -22,6 +22,7 @@ from typing import Callable, Dict, List, Optional
 import numpy as np
 
 from ..config import Config
+from ..engine import BatchResult
 from ..utils.metrics import Metrics
 from .scheduler import Batch, ReorderBuffer, Scheduler
 
@@ -49,6 +50,54 @@ class _Worker:
         self.thread.start()
 
     def loop(self):
+        if hasattr(self.engine, "process_stream") and self.cluster.cfg.pipelined_worker:
+            return self._loop_pipelined()
+        return self._loop_blocking()
+
+    def _loop_pipelined(self):
+        """GPU engines: batches go through `NativeEngine.process_stream`, so the upload of batch i+1, the kernels of
+        batch i and the read-back of batch i-1 overlap; an empty queue flushes the pipeline (a `None` item), so the last
+        batch of a stream is answered at once.  Same bookkeeping as the blocking loop."""
+        cl = self.cluster
+        flying = []                       # batches handed to the engine, in order
+        stop = [False]
+
+        def batches():
+            while True:
+                try:
+                    b = self.q.get(timeout=0.002 if flying else 0.1)
+                except queue.Empty:
+                    yield None
+                    continue
+                if b is None:
+                    stop[0] = True
+                    return
+                if self.hang:
+                    continue              # fault injection: the batch stays in flight until the watchdog re-dispatches it
+                frames, t_submit, fetch = b.payload
+                flying.append((b, t_submit))
+                yield (frames, b.requester)
+
+        try:
+            for res in self.engine.process_stream(batches(), depth=2, annotate=cl.annotate, fetch_frames=True):
+                b, t_submit = flying.pop(0)
+                if not self.alive and cl.drop_results_of_departed:
+                    continue
+                if cl.sched.complete(b.batch_id, self.name) is None:
+                    cl.metrics.inc("duplicate_batches")
+                    continue
+                # the yielded result aliases the slot's pinned buffers (valid until the next item): take copies
+                f = lambda t: None if t is None else np.array(t.numpy() if hasattr(t, "numpy") else t)
+                cl.deliver(b, BatchResult(f(res.det), f(res.det_count), f(res.boxes_i), f(res.box_count), f(res.frames400)),
+                           self.name, t_submit)
+        except BaseException as e:        # a failing worker must not lose work: it is retired, its batches move on
+            cl.metrics.inc("worker_errors")
+            cl.log(f"worker {self.name} failed: {e!r}")
+            cl.last_error = repr(e)
+            self.alive = False
+            cl.sched.leave(self.name)
+
+    def _loop_blocking(self):
         cl = self.cluster
         while True:
             b = self.q.get()

@@ -182,6 +182,24 @@ def test_process_stream_flushes_on_none_and_takes_per_batch_ids(engines):
     assert np.array_equal(seen[1][0], ref.det_count) and np.array_equal(seen[1][1], ref.frames400)
 
 
+def test_local_cluster_drives_gpu_engines_through_process_stream(engines):
+    """LocalCluster with a NativeEngine worker: batches go through the pipelined API and equal the synchronous results."""
+    from distributedvolunteercomputing_b200.parallel.local_cluster import LocalCluster
+    nat, _ = engines
+    frames = _frames(12, 240, 320, seed=91)
+    ref = [nat.process(frames[i:i + 4]).numpy() for i in range(0, 12, 4)]
+    ref_counts = np.concatenate([r.det_count for r in ref])
+    ref_frames = np.concatenate([r.frames400 for r in ref])
+    got = {}
+    cl = LocalCluster(Config(batch=4, worker_timeout_s=30.0), on_frame=lambda r, fr: got.__setitem__(fr.frame_id, (len(fr.det), fr.frame400.copy())))
+    cl.join("gpu0", nat)
+    cl.submit("127.0.0.1:5554", frames, 1)
+    assert cl.wait("127.0.0.1:5554", 12, 60), cl.last_error
+    cl.close()
+    assert [got[i + 1][0] for i in range(12)] == ref_counts.tolist()
+    assert all(np.array_equal(got[i + 1][1], ref_frames[i]) for i in range(12))
+
+
 def test_network_volunteer_uses_the_pipelined_path(graph, tmp_path):
     """server + a GPU volunteer (NativeEngine through process_stream) + a requester over loopback: every frame comes back."""
     cv2 = pytest.importorskip("cv2")

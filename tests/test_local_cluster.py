@@ -82,3 +82,46 @@ def test_multi_client_fair_share_and_isolation():
         assert cl.wait(c, 40, timeout=60)
     assert all(per[c] == list(range(1, 41)) for c in clients)
     cl.close()
+
+
+def test_gpu_style_engine_runs_through_the_pipelined_loop():
+    """An engine with `process_stream` (NativeEngine) is driven through it: batches overlap, an empty queue flushes the
+    pipeline, results are copied out of the (re-used) slot buffers and arrive in order."""
+    import numpy as np
+    from distributedvolunteercomputing_b200.config import Config
+    from distributedvolunteercomputing_b200.engine import BatchResult
+    from distributedvolunteercomputing_b200.parallel.local_cluster import LocalCluster
+
+    class Eng:
+        def __init__(self):
+            self.slot = np.zeros((4, 2, 2, 3), np.uint8)        # ONE buffer re-used for every result, like a pinned slot
+            self.seen = 0
+
+        def process_stream(self, batches, depth=2, annotate=True, fetch_frames=False, requester_id=None):
+            pend = []
+            for item in batches:
+                if item is None:
+                    while pend:
+                        yield pend.pop(0)
+                    continue
+                frames, rid = item
+                self.seen += 1
+                B = len(frames)
+                self.slot[:B] = np.asarray(frames)[:, :2, :2]
+                z = np.zeros
+                pend.append(BatchResult(z((B, 100, 7), np.float32), z((B,), np.int32), z((B, 100, 4), np.int32), z((B,), np.int32), self.slot[:B]))
+                while len(pend) >= depth:
+                    yield pend.pop(0)
+            while pend:
+                yield pend.pop(0)
+
+    got = {}
+    cl = LocalCluster(Config(batch=4, worker_timeout_s=5.0), on_frame=lambda r, fr: got.__setitem__(fr.frame_id, fr.frame400.copy()))
+    engines = [Eng(), Eng()]
+    for i, e in enumerate(engines):
+        cl.join(f"g{i}", e)
+    frames = np.random.default_rng(0).integers(0, 255, (40, 8, 8, 3), dtype=np.uint8)
+    cl.submit("c", frames, 1)
+    assert cl.wait("c", 40, 10), (len(got), cl.last_error)
+    assert sorted(got) == list(range(1, 41)) and all(e.seen > 0 for e in engines)
+    cl.close()
