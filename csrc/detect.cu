@@ -126,7 +126,6 @@ __global__ void __launch_bounds__(NMS_THREADS) class_nms_kernel(const DetArgs a)
   float* sel_box = reinterpret_cast<float*>(sel_idx + DET_MAXK);       // [DET_MAXK][4]
   uint32_t* mask = reinterpret_cast<uint32_t*>(sel_box + DET_MAXK * 4);  // [DET_MAXK][4]: later boxes this one suppresses
   uint32_t* keepw = mask + DET_MAXK * 4;                        // [4] survivor bits
-  __shared__ int s_warp[NMS_THREADS / 32 + 1];
   __shared__ int s_n;
 
   int* kept_n = a.kept_n + (size_t)f * C;
@@ -135,28 +134,22 @@ __global__ void __launch_bounds__(NMS_THREADS) class_nms_kernel(const DetArgs a)
     return;
   }
   const float* prob = a.prob + ((size_t)f * C + c) * P;
-  // ---- compaction of priors above the confidence threshold (stable: ascending prior index)
-  int base = 0;
-  for (int i0 = 0; i0 < P; i0 += NMS_THREADS) {
-    const int i = i0 + tid;
-    const float sc = i < P ? prob[i] : 0.f;
-    const bool ok = i < P && sc > a.p.conf_thresh;
-    const unsigned bal = __ballot_sync(0xffffffff, ok);
-    if (lane == 0) s_warp[warp] = __popc(bal);
-    __syncthreads();
-    int off = base;
-    for (int w = 0; w < warp; ++w) off += s_warp[w];
-    if (ok) {
-      const int pos = off + __popc(bal & ((1u << lane) - 1));
+  // ---- compaction of priors above the confidence threshold.  The order inside the candidate list does not matter: the
+  // ranking below uses the strict total order (score desc, prior index asc), so an unordered shared-memory counter
+  // replaces the per-chunk ballot / prefix / two-barrier scheme (15 chunks of 128 priors).
+  if (tid == 0) s_n = 0;
+  __syncthreads();
+  for (int i = tid; i < P; i += NMS_THREADS) {
+    const float sc = prob[i];
+    if (sc > a.p.conf_thresh) {
+      const int pos = atomicAdd(&s_n, 1);
       cs[pos] = sc;
       ci[pos] = i;
     }
-    int tot = 0;
-    for (int w = 0; w < NMS_THREADS / 32; ++w) tot += s_warp[w];
-    base += tot;
-    __syncthreads();
   }
-  const int n_c = base;
+  __syncthreads();
+  const int n_c = s_n;
+  __syncthreads();                       // s_n is re-used for the survivor count further down
   // ---- rank by counting; ranks < top_k land in sorted position
   for (int e = tid; e < n_c; e += NMS_THREADS) {
     const float s = cs[e];
