@@ -288,3 +288,26 @@ def test_trace_span_records_metrics():
     with span("batch", m, n=3):
         time.sleep(0.01)
     assert m.percentile("batch_ms", 50) >= 5.0
+
+
+def test_chunk_given_up_by_the_pool_reaches_the_requester_as_a_gap(tmp_path):
+    """Two volunteers that swallow every chunk: each chunk times out on its volunteer and is dropped (max_attempts = 1) - and the
+    requester is TOLD (a `dropped` marker per chunk), so its in-order writer finishes instead of waiting for ever."""
+    port = _udp_port()
+    srv = coordinator("127.0.0.1", _cfg(port, worker_timeout_s=0.6))
+    srv.sched.max_attempts = 1           # the first time-out already gives the chunk up (both volunteers are then presumed dead)
+    try:
+        video = write_synthetic_video(str(tmp_path / "in.mp4"), 16, 96, 128)
+        a = client("127.0.0.1", "127.0.0.1", _cfg(port, inject_stall_after=1), engine=StubEngine(), out_dir=str(tmp_path))
+        b = client("127.0.0.1", "127.0.0.1", _cfg(port, inject_stall_after=1), engine=StubEngine(), out_dir=str(tmp_path))
+        for c in (a, b):
+            c.chunks_taken = 10 ** 6          # every chunk counts as "after the limit": swallowed
+        r = client("127.0.0.1", "127.0.0.1", _cfg(port), engine=StubEngine(), out_dir=str(tmp_path))
+        assert a.ready.wait(5) and b.ready.wait(5) and r.ready.wait(5)
+        r.become_requester(video)
+        assert r.wait_job(30) is not None, "the requester was never told about the dropped chunks"
+        assert r.tracker.lost == 16 and srv.sched.stats["dropped_after_max_attempts"] == 2
+        assert srv.metrics.counters["dropped_chunks"] == 2 and not srv.missing
+        a.exit_threads(); b.exit_threads(); r.exit_threads()
+    finally:
+        srv.exit_threads()
