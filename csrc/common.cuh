@@ -43,6 +43,11 @@ int make_tmap_2d_f16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
 int make_tmap_nhwc_f16(CUtensorMap* out, const void* base, uint64_t n, uint64_t h, uint64_t w, uint64_t c,
                        uint32_t box_c, uint32_t box_w, uint32_t box_h);
 
+// Same tensor in im2col mode for a 3x3 / stride-2 / pad-1 convolution: one load = `pixels` consecutive output pixels x
+// box_c (= 64) channels of one filter tap, 128-byte swizzled rows (see tma_load_im2col_4d and csrc/core.cu).
+int make_tmap_im2col3x3s2_f16(CUtensorMap* out, const void* base, uint64_t n, uint64_t h, uint64_t w, uint64_t c,
+                              uint32_t box_c, uint32_t pixels);
+
 // Programmatic dependent launch (DVC_PDL=0 turns it off): a kernel launched through launch_pdl may become resident
 // while its predecessor on the stream is still draining.  Every such kernel calls pdl_launch_dependents() first and
 // pdl_wait() before it touches anything a predecessor wrote (or still reads); only constant data - weights, biases,
@@ -143,6 +148,15 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* t
   asm volatile(
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+// TMA im2col-mode load (4-D NHWC map from make_tmap_im2col3x3s2_f16): {c, w, h, n} is the first pixel's base coordinate
+// in input space, {kw, kh} the filter-tap offset added to every pixel of the column.
+__device__ __forceinline__ void tma_load_im2col_4d(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c, int w, int h,
+                                                   int n, int kw, int kh) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)kw), "h"((uint16_t)kh)
       : "memory");
 }
 // Mixed-precision FMA pair: acc0 += lo(x)*lo(w), acc1 += hi(x)*hi(w) with fp16 inputs and fp32

@@ -53,6 +53,14 @@ struct GemmArgs {
   int ldc;
   int relu;
   dvc_head_out head;
+  // implicit 3x3 / stride-2 / pad-1 convolution (conv_c > 0): A is never materialised, tmA is an im2col-mode map over the
+  // NHWC input and K runs over (kh, kw, c) with c fastest, i.e. the layout im2col3x3s2_kernel would have written
+  int conv_c, conv_wo, conv_howo;
+};
+
+// The activation operand of an implicit convolution (gemm_prepare's optional last argument).
+struct ConvA {
+  int B, H, W, C;
 };
 
 // PAIR = 1 is the cta_group::2 build: ptxas marks a kernel containing cta_group::2 instructions as needing an even
@@ -151,7 +159,18 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             continue;
           }
           mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
-          tma_load_2d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], kb * BK, m_tile * BM);
+          if (g.conv_c) {
+            // K block kb = 64 channels of one filter tap; the 128 rows are 128 consecutive output pixels, which the
+            // TMA unit walks (w, then h, then n) from the tile's first pixel, zero-filling the padding halo
+            const int m0 = m_tile * BM;
+            const int n_img = m0 / g.conv_howo, r = m0 - n_img * g.conv_howo;
+            const int oh = r / g.conv_wo, ow = r - oh * g.conv_wo;
+            const int tap = (kb * BK) / g.conv_c, c0 = kb * BK - tap * g.conv_c;
+            const int kh = tap / 3, kw = tap - kh * 3;
+            tma_load_im2col_4d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], c0, 2 * ow - 1, 2 * oh - 1, n_img, kw, kh);
+          } else {
+            tma_load_2d(sA + s * A_STAGE_BYTES, &tmA, &full_bar[s], kb * BK, m_tile * BM);
+          }
           if (!g.b_resident) {
             tma_load_2d(sB + s * b_stage_bytes, &tmB, &full_bar[s], kb * BK, n_tile * g.block_n);
           }
@@ -351,8 +370,8 @@ struct GemmLaunch {
   int smem;
 };
 
-int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
-                 int out_mode, void* out, int ldc, int relu, const dvc_head_out* head, int block_n) {
+static int gemm_prepare_impl(GemmLaunch* L, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
+                             int out_mode, void* out, int ldc, int relu, const dvc_head_out* head, int block_n, const ConvA* conv) {
   DVC_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
   DVC_REQUIRE(N % 16 == 0 && N <= BIAS_MAX_N, "gemm: N=%d must be a multiple of 16 (pad the weights) and <= %d", N, BIAS_MAX_N);
   DVC_REQUIRE(K % 16 == 0 && lda % 8 == 0, "gemm: K=%d must be a multiple of 16 and lda=%d of 8", K, lda);
@@ -367,6 +386,13 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
     DVC_REQUIRE(head->n_loc + head->n_conf <= N, "gemm: head columns %d > N=%d", head->n_loc + head->n_conf, N);
   }
   GemmArgs& g = L->args;
+  g.conv_c = g.conv_wo = g.conv_howo = 0;
+  if (conv) {
+    const int Ho = (conv->H - 1) / 2 + 1, Wo = (conv->W - 1) / 2 + 1;
+    DVC_REQUIRE(conv->C % BK == 0 && conv->H >= 2 && conv->W >= 2 && M == conv->B * Ho * Wo && K == 9 * conv->C,
+                "gemm: implicit conv needs C %% %d == 0 (C=%d), H, W >= 2 and M, K matching the input shape", BK, conv->C);
+    g.conv_c = conv->C; g.conv_wo = Wo; g.conv_howo = Ho * Wo;
+  }
   g.M = M; g.N = N; g.K = K;
   g.block_n = block_n;
   g.n_tiles = N / block_n;
@@ -389,7 +415,7 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
   {
     const char* env = getenv("DVC_GEMM_2CTA");
     const int want = env ? atoi(env) : 0;
-    if (want && cluster == 1 && !g.b_resident && block_n % 32 == 0 && g.m_tiles >= 2 && g.num_kb >= want) {
+    if (want && !conv && cluster == 1 && !g.b_resident && block_n % 32 == 0 && g.m_tiles >= 2 && g.num_kb >= want) {
       g.two_cta = 1;
       cluster = 2;
     }
@@ -417,7 +443,8 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
   if (g.num_ctiles < num_clusters) num_clusters = g.num_ctiles;
   L->grid = num_clusters * cluster;
   L->smem = g.stages * stage_bytes + fixed;
-  int rc = make_tmap_2d_f16(&L->tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
+  int rc = conv ? make_tmap_im2col3x3s2_f16(&L->tmA, A, (uint64_t)conv->B, (uint64_t)conv->H, (uint64_t)conv->W, (uint64_t)conv->C, BK, BM)
+                : make_tmap_2d_f16(&L->tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BM, BK);
   if (rc) return rc;
   rc = make_tmap_2d_f16(&L->tmB, Wt, (uint64_t)N, (uint64_t)K, (uint64_t)K, (uint32_t)(block_n / cluster), BK);
   if (rc) return rc;
@@ -428,6 +455,11 @@ int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias
     L->tmC = L->tmA;
   }
   return DVC_OK;
+}
+
+int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
+                 int out_mode, void* out, int ldc, int relu, const dvc_head_out* head, int block_n) {
+  return gemm_prepare_impl(L, A, Wt, bias, M, N, K, lda, out_mode, out, ldc, relu, head, block_n, nullptr);
 }
 
 int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
@@ -455,10 +487,83 @@ int gemm_launch(const GemmLaunch* L, cudaStream_t st) {
   return DVC_OK;
 }
 
+// 3x3 / stride-2 / pad-1 dense convolution (the SSD extras conv14_2 .. conv17_2, prototxt:922-1146) as an implicit
+// GEMM: out[B*Ho*Wo, N] = act(patches(in) * Wt[N, 9*C]^T + bias) with the patch rows gathered by the TMA unit.
+int gemm_prepare_conv3x3s2(GemmLaunch* L, const void* in, int B, int H, int W, int C, const void* Wt, const float* bias, int N,
+                           void* out, int ldc, int relu, int block_n) {
+  DVC_REQUIRE(B > 0 && H >= 2 && W >= 2 && C > 0, "conv3x3s2: bad shape B=%d H=%d W=%d C=%d", B, H, W, C);
+  const ConvA conv{B, H, W, C};
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  return gemm_prepare_impl(L, in, Wt, bias, B * Ho * Wo, N, 9 * C, 9 * C, 0, out, ldc, relu, nullptr, block_n, &conv);
+}
+
+// Test hook for the im2col tensor map: one CTA fetches one [128 pixels x 64 channels] operand tile exactly as the GEMM
+// producer does and writes it back un-swizzled, so the gather can be compared against a host-side unfold.  The wait is
+// bounded (status 1 = the expected bytes never arrived).
+__global__ void __launch_bounds__(128, 1)
+im2col_tile_kernel(const __grid_constant__ CUtensorMap tmA, int c0, int w0, int h0, int n0, int kw, int kh, __half* __restrict__ out,
+                   int* __restrict__ status) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* tile = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar;
+  __shared__ int ok;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+    ok = 0;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(&bar, (uint32_t)A_STAGE_BYTES);
+    tma_load_im2col_4d(tile, &tmA, &bar, c0, w0, h0, n0, kw, kh);
+    const unsigned long long t0 = globaltimer_ns();
+    while (!mbar_try_wait(&bar, 0)) {
+      if (globaltimer_ns() - t0 > 200000000ull) break;
+    }
+    ok = mbar_try_wait(&bar, 0) ? 1 : 0;
+  }
+  __syncthreads();
+  if (!ok) {
+    if (threadIdx.x == 0) *status = 1;
+    return;
+  }
+  const int r = threadIdx.x;                    // row r: 8 x 16-byte chunks, chunk j stored at position j ^ (r & 7)
+  for (int j = 0; j < 8; ++j) {
+    const uint4 v = *reinterpret_cast<const uint4*>(tile + r * 128 + ((j ^ (r & 7)) << 4));
+    *reinterpret_cast<uint4*>(out + r * BK + j * 8) = v;
+  }
+  if (threadIdx.x == 0) *status = 0;
+}
+
 GemmLaunch* gemm_alloc() { return new GemmLaunch(); }
 void gemm_free(GemmLaunch* L) { delete L; }
 
 }  // namespace dvc
+
+extern "C" int dvc_conv3x3s2_f16(const void* in_f16, int B, int H, int W, int C, const void* Wt, const float* bias, int N,
+                                 void* out_f16, int ldc, int relu, int block_n, void* stream) {
+  dvc::GemmLaunch L;
+  int rc = dvc::gemm_prepare_conv3x3s2(&L, in_f16, B, H, W, C, Wt, bias, N, out_f16, ldc, relu, block_n);
+  if (rc) return rc;
+  return dvc::gemm_launch(&L, (cudaStream_t)stream);
+}
+
+extern "C" int dvc_debug_im2col_tile(const void* in_f16, int B, int H, int W, int C, int m0, int kb, void* out_tile_f16,
+                                     int* status, void* stream) {
+  using namespace dvc;
+  DVC_REQUIRE(C % BK == 0 && kb >= 0 && kb < 9 * C / BK && m0 >= 0, "im2col tile: bad C=%d kb=%d m0=%d", C, kb, m0);
+  CUtensorMap tm;
+  int rc = make_tmap_im2col3x3s2_f16(&tm, in_f16, (uint64_t)B, (uint64_t)H, (uint64_t)W, (uint64_t)C, BK, BM);
+  if (rc) return rc;
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  const int n_img = m0 / (Ho * Wo), r = m0 - n_img * Ho * Wo, oh = r / Wo, ow = r - oh * Wo;
+  const int tap = (kb * BK) / C, c0 = kb * BK - tap * C, kh = tap / 3, kw = tap - kh * 3;
+  im2col_tile_kernel<<<1, 128, A_STAGE_BYTES + 1024, (cudaStream_t)stream>>>(tm, c0, 2 * ow - 1, 2 * oh - 1, n_img, kw, kh,
+                                                                               (__half*)out_tile_f16, status);
+  count_launch();
+  DVC_CHECK_CUDA(cudaGetLastError());
+  return DVC_OK;
+}
 
 extern "C" int dvc_gemm_f16(const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda, int out_mode,
                             void* out_f16, int ldc, int relu, const dvc_head_out* head, int block_n, void* stream) {

@@ -15,6 +15,8 @@ struct DetLaunch;
 
 int gemm_prepare(GemmLaunch* L, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda, int out_mode,
                  void* out, int ldc, int relu, const dvc_head_out* head, int block_n);
+int gemm_prepare_conv3x3s2(GemmLaunch* L, const void* in, int B, int H, int W, int C, const void* Wt, const float* bias, int N,
+                           void* out, int ldc, int relu, int block_n);
 int gemm_launch(const GemmLaunch* L, cudaStream_t st);
 GemmLaunch* gemm_alloc();
 void gemm_free(GemmLaunch*);
@@ -159,6 +161,17 @@ extern "C" int dvc_plan_add_im2col(dvc_plan* p, const void* in_f16, int B, int H
   DVC_REQUIRE(p, "plan is null");
   DVC_REQUIRE(C % 8 == 0, "im2col: C=%d unsupported", C);
   Op op; op.kind = OP_IM2COL; op.in = in_f16; op.out = out_f16; op.B = B; op.H = H; op.W = W; op.C = C;
+  p->ops.push_back(op);
+  return DVC_OK;
+}
+
+/* Dense 3x3 / stride-2 / pad-1 convolution as an implicit GEMM (no im2col buffer): see gemm_prepare_conv3x3s2. */
+extern "C" int dvc_plan_add_conv3x3s2(dvc_plan* p, const void* in_f16, int B, int H, int W, int C, const void* Wt, const float* bias,
+                                      int N, void* out_f16, int ldc, int relu, int block_n) {
+  DVC_REQUIRE(p, "plan is null");
+  Op op; op.kind = OP_GEMM; op.gemm = gemm_alloc();
+  int rc = gemm_prepare_conv3x3s2(op.gemm, in_f16, B, H, W, C, Wt, bias, N, out_f16, ldc, relu, block_n);
+  if (rc) { gemm_free(op.gemm); return rc; }
   p->ops.push_back(op);
   return DVC_OK;
 }

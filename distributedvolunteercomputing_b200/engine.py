@@ -256,7 +256,10 @@ class NativeEngine:
         st.sB = torch.empty((sub * early_max,), dtype=torch.float16, device=dev)
         st.fA = torch.empty((B * late_max,), dtype=torch.float16, device=dev)
         st.fB = torch.empty((B * late_max,), dtype=torch.float16, device=dev)
-        col_max = max([c.out_hw[0] * c.out_hw[1] * 9 * c.cin for c in body if c.k == 3 and not c.depthwise and c.name != "conv0"] + [8])
+        implicit_conv = os.environ.get("DVC_IMPLICIT_CONV", "1") != "0"     # 0: explicit im2col buffer + GEMM
+        # patch buffer only for the dense 3x3 layers that do not take the implicit-GEMM path
+        col_max = max([c.out_hw[0] * c.out_hw[1] * 9 * c.cin for c in body if c.k == 3 and not c.depthwise and c.name != "conv0"
+                       and not (implicit_conv and c.cin % 64 == 0)] + [8])
         st.col = torch.empty((B * col_max,), dtype=torch.float16, device=dev)
         plan = lib.dvc_plan_create()
         st.plan = plan
@@ -274,6 +277,11 @@ class NativeEngine:
                                               c.cin, 0, dst_ptr, c.cout, int(c.relu), None, 0), c.name)
             else:
                 assert c.k == 3 and c.stride == 2 and c.pad == 1, c
+                if implicit_conv and c.cin % 64 == 0:
+                    # implicit GEMM: the patch rows are gathered by im2col-mode TMA loads inside the GEMM kernel
+                    L.check(lib.dvc_plan_add_conv3x3s2(plan, src_ptr, nb, c.in_hw[0], c.in_hw[1], c.cin, L.ptr(self.w[c.name]),
+                                                       L.ptr(self.b[c.name]), c.cout, dst_ptr, c.cout, int(c.relu), 0), c.name)
+                    return
                 L.check(lib.dvc_plan_add_im2col(plan, src_ptr, nb, c.in_hw[0], c.in_hw[1], c.cin, L.ptr(st.col)), c.name + "/im2col")
                 M = nb * c.out_hw[0] * c.out_hw[1]
                 L.check(lib.dvc_plan_add_gemm(plan, L.ptr(st.col), L.ptr(self.w[c.name]), L.ptr(self.b[c.name]), M, c.cout,
@@ -493,6 +501,8 @@ class NativeEngine:
                     y = K.dwconv3x3(src, self.w[c.name], self.b[c.name], c.stride, c.relu)
                 elif c.k == 1:
                     y = K.gemm_f16(src.view(-1, c.cin), self.w[c.name], self.b[c.name], c.relu).view(B, c.out_hw[0], c.out_hw[1], c.cout)
+                elif c.cin % 64 == 0 and os.environ.get("DVC_IMPLICIT_CONV", "1") != "0":
+                    y = K.conv3x3s2_f16(src, self.w[c.name], self.b[c.name], c.relu)
                 else:
                     col = K.im2col3x3s2(src)
                     y = K.gemm_f16(col, self.w[c.name], self.b[c.name], c.relu).view(B, c.out_hw[0], c.out_hw[1], c.cout)

@@ -147,6 +147,33 @@ def im2col3x3s2(x: torch.Tensor, stream=None) -> torch.Tensor:
     return out
 
 
+def conv3x3s2_f16(x: torch.Tensor, wt: torch.Tensor, bias: torch.Tensor, relu: bool = True, block_n: int = 0, stream=None) -> torch.Tensor:
+    """Dense 3x3 / stride-2 / pad-1 convolution (SSD extras, prototxt:922-1146) as an implicit GEMM: NHWC fp16 in,
+    wt [Cout, 9*Cin] in (kh, kw, cin) order, no patch buffer (the GEMM's activation tiles are im2col-mode TMA loads)."""
+    assert x.dtype == torch.float16 and x.is_cuda and x.is_contiguous() and x.dim() == 4
+    B, H, W, Cc = x.shape
+    assert wt.dtype == torch.float16 and wt.shape[1] == 9 * Cc and wt.is_contiguous() and bias.dtype == torch.float32
+    Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    N = wt.shape[0]
+    out = torch.empty((B, Ho, Wo, N), dtype=torch.float16, device=x.device)
+    L.check(L.load().dvc_conv3x3s2_f16(L.ptr(x), B, H, W, Cc, L.ptr(wt), L.ptr(bias), N, L.ptr(out), N, int(relu), block_n,
+                                       L.stream_ptr(stream)), "conv3x3s2_f16")
+    return out
+
+
+def debug_im2col_tile(x: torch.Tensor, m0: int, kb: int):
+    """Operand tile [128, 64] the implicit convolution's producer fetches for (first output pixel m0, K block kb),
+    and the load status (0 = ok).  Test hook for the im2col tensor map."""
+    assert x.dtype == torch.float16 and x.is_cuda and x.is_contiguous() and x.dim() == 4
+    B, H, W, Cc = x.shape
+    tile = torch.zeros((128, 64), dtype=torch.float16, device=x.device)
+    status = torch.full((1,), -1, dtype=torch.int32, device=x.device)
+    L.check(L.load().dvc_debug_im2col_tile(L.ptr(x), B, H, W, Cc, int(m0), int(kb), L.ptr(tile), L.ptr(status),
+                                           L.stream_ptr(None)), "debug_im2col_tile")
+    torch.cuda.synchronize(x.device)
+    return tile, int(status.item())
+
+
 def gemm_f16(a: torch.Tensor, wt: torch.Tensor, bias: torch.Tensor, relu: bool = True, block_n: int = 0,
              out: Optional[torch.Tensor] = None, stream=None) -> torch.Tensor:
     """out[M,N] = act(a[M,K] @ wt[N,K]^T + bias) on tcgen05 tensor cores (fp16 in, fp32 accumulate)."""

@@ -67,6 +67,8 @@ _SIGS = {
     "dvc_dwconv3x3": ([_P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P], _I),
     "dvc_gemm_f16": ([_P, _P, _P, _I, _I, _I, _I, _I, _P, _I, _I, _P, _I, _P], _I),
     "dvc_im2col3x3s2": ([_P, _I, _I, _I, _I, _P, _P], _I),
+    "dvc_conv3x3s2_f16": ([_P, _I, _I, _I, _I, _P, _P, _I, _P, _I, _I, _I, _P], _I),
+    "dvc_debug_im2col_tile": ([_P, _I, _I, _I, _I, _I, _I, _P, _P, _P], _I),
     "dvc_priorbox": ([_P, _P, _I, _I, _I, _I, _I, _P, _I, _F, _P, _I, _P], _I),
     "dvc_detection_scratch_bytes": ([_I, _I, _I], _SZ),
     "dvc_detection_output": ([_P, _P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _U32, _P, _SZ, _P], _I),
@@ -79,6 +81,7 @@ _SIGS = {
     "dvc_plan_add_dwconv": ([_P, _P, _I, _I, _I, _I, _I, _P, _P, _I, _P], _I),
     "dvc_plan_add_gemm": ([_P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _I, _I, _P, _I], _I),
     "dvc_plan_add_im2col": ([_P, _P, _I, _I, _I, _I, _P], _I),
+    "dvc_plan_add_conv3x3s2": ([_P, _P, _I, _I, _I, _I, _P, _P, _I, _P, _I, _I, _I], _I),
     "dvc_plan_add_detection": ([_P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _P, _P, _P, _U32, _P, _SZ], _I),
     "dvc_plan_set_source": ([_P, _P, _LL, _P], _I),
     "dvc_plan_set_sinks": ([_P, _P, _P, _P, _P, _P, _P], _I),

@@ -103,6 +103,17 @@ int dvc_gemm_f16(const void* A, const void* Wt, const float* bias, int M, int N,
  * (kh,kw,c) column order; the dense extras convs (prototxt:922-954 ...) are then a GEMM. */
 int dvc_im2col3x3s2(const void* in_f16, int B, int H, int W, int C, void* out_f16, void* stream);
 
+/* ---- K4 (implicit): the same convolution without the patch buffer.  out[B*Ho*Wo, N] = act(patches(in) * Wt[N, 9*C]^T +
+ * bias): the K2 GEMM kernel with its activation operand fetched by im2col-mode TMA loads (128 output pixels x 64
+ * channels of one filter tap per load, padding halo zero-filled by the TMA unit).  C must be a multiple of 64;
+ * Wt is in (kh, kw, c) column order as for dvc_im2col3x3s2 + dvc_gemm_f16, and the result is bit-identical to that pair. */
+int dvc_conv3x3s2_f16(const void* in_f16, int B, int H, int W, int C, const void* Wt_f16, const float* bias, int N,
+                      void* out_f16, int ldc, int relu, int block_n, void* stream);
+/* Test hook: fetch operand tile (first output pixel m0, K block kb) of that convolution into out_tile_f16[128][64];
+ * *status (device int) = 0 on success, 1 if the load did not complete. */
+int dvc_debug_im2col_tile(const void* in_f16, int B, int H, int W, int C, int m0, int kb, void* out_tile_f16, int* status,
+                          void* stream);
+
 /* ---- K6: PriorBox for one tap (prototxt:1239-1256), written at prior_off in [P,4] arrays. */
 int dvc_priorbox(float* boxes, float* variances, int prior_off, int grid_h, int grid_w, int img_h, int img_w,
                  const float* anchor_wh, int anchors, float offset, const float* h_var4, int clip, void* stream);
@@ -190,6 +201,8 @@ int dvc_plan_add_dwconv(dvc_plan*, const void* in_f16, int B, int H, int W, int 
 int dvc_plan_add_gemm(dvc_plan*, const void* A, const void* Wt, const float* bias, int M, int N, int K, int lda,
                       int out_mode, void* out_f16, int ldc, int relu, const dvc_head_out* head, int block_n);
 int dvc_plan_add_im2col(dvc_plan*, const void* in_f16, int B, int H, int W, int C, void* out_f16);
+int dvc_plan_add_conv3x3s2(dvc_plan*, const void* in_f16, int B, int H, int W, int C, const void* Wt_f16, const float* bias,
+                           int N, void* out_f16, int ldc, int relu, int block_n);
 /* EXPERIMENTAL: dvc_dwpw_fused_s1 as a plan op (the engine adds it only when DVC_FUSE_DWPW=1). */
 int dvc_plan_add_dwpw_fused(dvc_plan*, const void* in_f16, int B, int H, int W, int C_in, const float* wdw, const float* bdw,
                             const void* wpw_f16, const float* bpw, int C_out, void* out_f16);

@@ -256,7 +256,7 @@ def test_engine_state_cache_eviction_and_close(monkeypatch):
     e.close()                                             # idempotent (also what __del__ calls)
 
 
-def _recorded_plan(monkeypatch, fuse):
+def _recorded_plan(monkeypatch, fuse, implicit=True):
     """NativeEngine._build_plan against a recording stand-in for the native library (no GPU needed)."""
     import ctypes as C
     import types
@@ -266,6 +266,7 @@ def _recorded_plan(monkeypatch, fuse):
     from distributedvolunteercomputing_b200.models.mobilenet_ssd import SSDGraph
     from distributedvolunteercomputing_b200.ops import lib as Lmod
     monkeypatch.setenv("DVC_FUSE_DWPW", "1" if fuse else "0")
+    monkeypatch.setenv("DVC_IMPLICIT_CONV", "1" if implicit else "0")
     e = NativeEngine.__new__(NativeEngine)
     e.graph, e.cfg, e.device = SSDGraph.random(seed=1), Config(), torch.device("cpu")
     calls = []
@@ -300,16 +301,23 @@ def _recorded_plan(monkeypatch, fuse):
 
 
 def test_plan_construction_default_and_fused(monkeypatch):
-    """The launch sequence the engine asks the native executor for: 46 ops by default (stem, 13 dw + 13 pw, 4 x (1x1,
-    im2col, 3x3) extras, 6 heads, detection); with the experimental switch the three stride-1 pairs whose pointwise
-    has <= 256 outputs (conv1, conv3, conv5) become one fused op each and nothing else moves."""
+    """The launch sequence the engine asks the native executor for: 42 ops by default (stem, 13 dw + 13 pw, 4 x (1x1,
+    implicit 3x3) extras, 6 heads, detection), 46 with DVC_IMPLICIT_CONV=0 (an im2col op in front of each 3x3 extra);
+    with the experimental switch the three stride-1 pairs whose pointwise has <= 256 outputs (conv1, conv3, conv5)
+    become one fused op each and nothing else moves."""
     calls, n = _recorded_plan(monkeypatch, fuse=False)
     kinds = [c[0] for c in calls]
-    assert n == 46 and kinds[0] == "preproc_conv0" and kinds[-1] == "detection"
-    assert kinds.count("dwconv") == 13 and kinds.count("im2col") == 4 and kinds.count("gemm") == 13 + 8 + 6 and "dwpw_fused" not in kinds
+    assert n == 42 and kinds[0] == "preproc_conv0" and kinds[-1] == "detection"
+    assert kinds.count("dwconv") == 13 and kinds.count("im2col") == 0 and kinds.count("conv3x3s2") == 4
+    assert kinds.count("gemm") == 13 + 4 + 6 and "dwpw_fused" not in kinds
+    assert [c[1:5] for c in calls if c[0] == "conv3x3s2"] == [(64, 10, 10, 256), (64, 5, 5, 128), (64, 3, 3, 128), (64, 2, 2, 64)]
+    explicit, ne = _recorded_plan(monkeypatch, fuse=False, implicit=False)
+    ek = [c[0] for c in explicit]
+    assert ne == 46 and ek.count("im2col") == 4 and ek.count("gemm") == 13 + 8 + 6 and "conv3x3s2" not in ek
+    assert [k for k in ek if k != "im2col"] == [("gemm" if k == "conv3x3s2" else k) for k in kinds]
     fused, nf = _recorded_plan(monkeypatch, fuse=True)
     fk = [c[0] for c in fused]
-    assert nf == 43 and fk.count("dwpw_fused") == 3 and fk.count("dwconv") == 10 and fk.count("gemm") == 13 + 8 + 6 - 3
+    assert nf == 39 and fk.count("dwpw_fused") == 3 and fk.count("dwconv") == 10 and fk.count("gemm") == 13 + 4 + 6 - 3
     assert [c[1:] for c in fused if c[0] == "dwpw_fused"] == [(64, 150, 150, 32, 64), (64, 75, 75, 128, 128), (64, 38, 38, 256, 256)]
     assert [k for k in fk if k != "dwpw_fused"] == [k for i, k in enumerate(kinds) if not (
         (k == "dwconv" and calls[i][1:] in {(64, 150, 150, 32, 1, 1), (64, 75, 75, 128, 1, 1), (64, 38, 38, 256, 1, 1)})

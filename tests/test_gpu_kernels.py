@@ -136,6 +136,42 @@ def test_im2col_matches_unfold(K, B, H, W, C):
     assert torch.equal(col.float(), u)
 
 
+@pytest.mark.parametrize("B,H,W,C", [(3, 19, 19, 256), (5, 10, 10, 128), (2, 5, 5, 128), (70, 3, 3, 64), (64, 2, 2, 64)])
+def test_im2col_tma_tile_matches_patch_rows(K, B, H, W, C):
+    """The im2col-mode tensor map of the implicit 3x3/s2 convolution: every operand tile the GEMM producer would fetch
+    (128 consecutive output pixels x 64 channels of one tap) equals the matching block of the explicit patch matrix,
+    including tiles that start mid-row, span several images, touch the padding halo and run past the last image (those rows are never stored)."""
+    x = _rand((B, H, W, C), 1.0, 20).half().to(DEV)
+    col = K.im2col3x3s2(x)
+    M = col.shape[0]
+    m_tiles = (M + 127) // 128
+    kbs = sorted({0, 1, 4 * C // 64, 9 * C // 64 - 1, 5 * C // 64 + (C // 64 - 1)})
+    for mt in sorted({0, m_tiles // 2, m_tiles - 1}):
+        for kb in kbs:
+            tile, status = K.debug_im2col_tile(x, mt * 128, kb)
+            assert status == 0, (mt, kb, status)
+            rows = min(128, M - mt * 128)
+            assert torch.equal(tile[:rows], col[mt * 128:mt * 128 + rows, kb * 64:(kb + 1) * 64]), (mt, kb)
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(64, 10, 10, 256, 512), (64, 5, 5, 128, 256), (64, 3, 3, 128, 256), (64, 2, 2, 64, 128),
+                                            (64, 19, 19, 256, 512), (3, 19, 19, 256, 512), (1, 3, 3, 64, 128)])
+def test_conv3x3s2_implicit_gemm(K, B, H, W, Cin, Cout):
+    """SSD extras conv14_2 .. conv17_2 (prototxt:922-1146) without the patch buffer: bit-identical to im2col + GEMM (same
+    operand tiles, same accumulation order) and within fp16 tolerance of an fp32 convolution."""
+    x = _rand((B, H, W, Cin), 1.0, 21).half().to(DEV)
+    w = _rand((Cout, Cin, 3, 3), 0.05, 22)
+    b = _rand((Cout,), 0.2, 23).to(DEV)
+    wt = w.permute(0, 2, 3, 1).reshape(Cout, 9 * Cin).contiguous().half().to(DEV)        # (kh, kw, cin)
+    y = K.conv3x3s2_f16(x, wt, b, relu=True)
+    two = K.gemm_f16(K.im2col3x3s2(x), wt, b, relu=True).view_as(y)
+    torch.cuda.synchronize()
+    assert torch.equal(y, two)
+    ref = F.relu(F.conv2d(x.float().permute(0, 3, 1, 2), wt.float().view(Cout, 3, 3, Cin).permute(0, 3, 1, 2), b, stride=2, padding=1))
+    ref = ref.permute(0, 2, 3, 1)
+    assert (y.float() - ref).abs().max().item() <= 3e-3 * max(1.0, ref.abs().max().item()) + 2e-3
+
+
 @pytest.mark.parametrize("H,W", [(300, 300), (480, 640), (720, 1280), (600, 800), (1080, 1920), (333, 517), (240, 320), (200, 301), (150, 202), (97, 399)])
 def test_resize_area_matches_cv2(K, H, W):
     cv2 = pytest.importorskip("cv2")
