@@ -311,3 +311,51 @@ def test_chunk_given_up_by_the_pool_reaches_the_requester_as_a_gap(tmp_path):
         a.exit_threads(); b.exit_threads(); r.exit_threads()
     finally:
         srv.exit_threads()
+
+
+def test_long_live_stream_keeps_the_servers_tables_bounded():
+    """`request live` never ends (worker.py:96,114): after 20 000 chunks (160 000 frames) through the coordinator's
+    ingest / dispatch / completion bookkeeping every table is as small as after the first chunk and the Python heap
+    did not grow with the stream - only counters did."""
+    import queue
+    import tracemalloc
+    srv = coordinator("127.0.0.1", _cfg(_udp_port()), start=False)
+    srv.running = True
+    req, wrk = "10.0.0.1:5554", "10.0.0.2:5554"
+    for a in (req, wrk):
+        srv.sched.join(a)
+    srv.sched.become_requester(req)
+    srv.results[req] = queue.Queue()
+    img = np.zeros((2, 8 * 2, 3), np.uint8)
+
+    def one_chunk(i):
+        frames = list(range(i * 8 + 1, i * 8 + 9))
+        srv._on_chunk(proto.Header(req, "request", frames, 2, 2).encode(), img, req)
+        batch, worker, _ = srv.sched.next_dispatch()
+        assert worker.addr == wrk and list(batch.frame_ids) == frames
+        # results come back in two half-chunks, the second one twice (a re-sent reply)
+        srv._on_chunk(proto.Header(req, "processed", frames[:4], 2, 2).encode(), img, wrk)
+        srv._on_chunk(proto.Header(req, "processed", frames[4:], 2, 2).encode(), img, wrk)
+        srv._on_chunk(proto.Header(req, "processed", frames[4:], 2, 2).encode(), img, wrk)
+        assert srv.results[req].qsize() == 2
+        srv.results[req].get_nowait(), srv.results[req].get_nowait()
+
+    def sizes():
+        return (len(srv.frame_owner[req]), len(srv.missing), len(srv.sched.inflight), srv.sched.pending(), len(srv.sched.dropped),
+                len(srv.sched.done), len(srv.sched.members.workers))
+
+    for i in range(200):
+        one_chunk(i)
+    base = sizes()
+    tracemalloc.start()
+    snap0 = tracemalloc.take_snapshot()
+    n = 20000
+    for i in range(200, 200 + n):
+        one_chunk(i)
+    snap1 = tracemalloc.take_snapshot()
+    tracemalloc.stop()
+    assert sizes() == base == (0, 0, 0, 0, 0, 1, 2)
+    assert srv.sched.done[req] == 200 + n and srv.sched.stats["completed"] == 200 + n
+    assert srv.metrics.counters["frames_in"] == 8 * (200 + n) and srv.metrics.counters["duplicate_chunks"] == 200 + n
+    grown = sum(s.size_diff for s in snap1.compare_to(snap0, "filename") if s.size_diff > 0)
+    assert grown < 256 * 1024, f"{grown} bytes retained over {n} chunks"
