@@ -11,8 +11,8 @@ worker.py:180).  The protocol is written down in csrc/mailbox.cu and DESIGN.md Â
     K1a pulls the frames with peer loads (scatter), the network runs, K9 pushes the rows with peer stores and its
     last CTA publishes the done word (gather).  The client's wait kernel polls the done word and the stream goes on
     to the device->host copy of the slot.  No collective, no host round trip, every wait bounded by a time-out.
-  * Workers are independent: processes started with torchrun, processes spawned at any time, or threads driving other
-    GPUs of the same process.  None of them takes part in any collective, so one that stalls, leaves or is killed
+  * Workers are independent processes: started with torchrun or spawned at any time (the client's own GPU serves
+    inline, `ClientBox.attach_local`).  None of them takes part in any collective, so one that stalls, leaves or is killed
     only costs its own in-flight batches, which `ElasticBox` re-dispatches (scheduler.py).
 
 `ClientBox`     client-side memory + dispatch / poll primitives (thin over the native calls)
@@ -24,7 +24,6 @@ from __future__ import annotations
 import collections
 import ctypes as C
 import dataclasses
-import threading
 import time
 from typing import Any, Callable, Deque, Dict, List, Optional, Sequence, Tuple
 
@@ -428,9 +427,6 @@ class ClientBox:
                                 "desc_addr_arr": (C.c_void_p * 1)(lay.desc_addr(self.ctl.ptr, w, l)),
                                 "done_addr_arr": (C.c_void_p * 1)(lay.done_addr(self.ctl.ptr, w, l)),
                                 "seq_arr": (C.c_uint32 * 1)(0)})
-        # one process driving several GPUs from several threads must re-select the device in the library's own CUDA
-        # runtime on every call; a process that only ever uses the client's GPU (torchrun, spawned workers) need not
-        self._set_device_each_call = False
         self._local_gexec: Dict[Tuple[int, int], int] = {}
         n_ev = max_workers * lanes
         self._ev_arr = (C.c_void_p * n_ev)(*[self.events[k].cuda_event for k in range(n_ev)])
@@ -533,8 +529,6 @@ class ClientBox:
             src_ptr, src_bytes = (host_src.data_ptr(), host_src.numel()) if host_src is not None else (None, 0)
             if host_src is not None:
                 assert lay.raw_stride == lay.H * lay.W * 3, "host upload needs a dense frame pitch"
-            if self._set_device_each_call:
-                L.set_device(self.dev)
             rc = self.lib.dvc_mbx_dispatch(src_ptr, self.arena.ptr + desc.src_off, src_bytes, c["desc_addr"], c["desc_ref"],
                                            c["done_addr"], hs, tmo, res, c["h_res"] if fetch else None, lay.copy_bytes,
                                            c["event"], c["stream"])
@@ -880,7 +874,7 @@ class ElasticBox:
         self.procs.clear()
 
 
-# ====================================================================================== process / thread front-ends
+# ====================================================================================== process front-end
 def worker_process_main(export: Dict[str, Any], worker: int, device_index: int, graph, cfg, conn=None,
                         stall_after: Optional[int] = None, local_feed_spec: Optional[Tuple] = None, delay_ms: float = 0.0):
     """Entry point of a spawned worker process (multiprocessing 'spawn'): map the client's box, adopt its weights,
@@ -923,30 +917,3 @@ def worker_process_main(export: Dict[str, Any], worker: int, device_index: int, 
             return
         if msg != "rejoin":
             return
-
-
-class ThreadWorker:
-    """A worker on ANOTHER GPU of the client's own process (one process driving several GPUs): same lanes, same
-    kernels, same words; the client's buffers are reached through peer access instead of IPC handles."""
-
-    def __init__(self, client: ClientBox, engine, worker: int):
-        with torch.cuda.device(engine.device):
-            L.set_device(engine.device)
-            if engine.device != client.dev:
-                L.check(client.lib.dvc_p2p_enable_peer(client.dev.index or 0), "enable_peer")
-            self.lanes = WorkerLanes(engine, client.layout, *client.bases(), worker)
-        self._stop = threading.Event()
-        self.ready = threading.Event()          # set once the lanes' position is read: add the worker after this
-        self.thread = threading.Thread(target=self._run, daemon=True, name=f"mbx-worker-{worker}")
-        self.hang = False
-
-    def start(self):
-        self.thread.start()
-        return self
-
-    def _run(self):
-        self.lanes.serve(should_stop=self._stop.is_set, on_ready=self.ready.set)
-
-    def stop(self, join_s: float = 10.0):
-        self._stop.set()
-        self.thread.join(join_s)
