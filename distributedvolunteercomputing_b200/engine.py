@@ -178,9 +178,6 @@ class NativeEngine:
             t = (self.w if kind == "w" else self.b)[key]
             t.view(torch.uint8).reshape(-1).copy_(flat[off:off + n])
 
-    def weight_bytes(self) -> int:
-        return sum(t.numel() * t.element_size() for t in list(self.w.values()) + list(self.b.values()))
-
     # ------------------------------------------------------------------ per-shape state
     def state(self, B: int, H: int, W: int, requester_id: Optional[str] = None, slot: int = 0) -> _ShapeState:
         rid = self.requester_id if requester_id is None else requester_id

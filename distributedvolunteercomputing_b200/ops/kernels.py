@@ -215,10 +215,6 @@ def dwpw_fused(x: torch.Tensor, wdw_9c: torch.Tensor, bdw: torch.Tensor, wpw: to
     return out
 
 
-def dwpw_fused_s1(x, wdw_9c, bdw, wpw, bpw, out=None, stream=None) -> torch.Tensor:
-    return dwpw_fused(x, wdw_9c, bdw, wpw, bpw, 1, out, stream)
-
-
 # ------------------------------------------------------------------------------------ K6..K10
 def priorbox(specs, img_hw: Tuple[int, int], device) -> Tuple[torch.Tensor, torch.Tensor]:
     total = sum(s.count for s in specs)
