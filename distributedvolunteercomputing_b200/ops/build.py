@@ -80,5 +80,43 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB_PATH
 
 
+def build_tsan(force: bool = False) -> str:
+    """ThreadSanitizer build of the library's HOST code plus the harness tests/native/tsan_host.cpp (no GPU needed: the
+    harness drives every entry point up to the first driver call).  Everything lands under build/tsan/ - the product
+    library is untouched.  Returns the path of the harness executable."""
+    out = os.path.join(ROOT, "build", "tsan")
+    os.makedirs(out, exist_ok=True)
+    lib = os.path.join(out, "libdvc_b200_tsan.so")
+    exe = os.path.join(out, "tsan_host")
+    stamp = os.path.join(out, "stamp")
+    harness = os.path.join(ROOT, "tests", "native", "tsan_host.cpp")
+    h = hashlib.sha256((_digest() + open(harness).read()).encode()).hexdigest()
+    if not force and os.path.exists(exe) and os.path.exists(stamp) and open(stamp).read().strip() == h:
+        return exe
+    nvcc = nvcc_path()
+    flags = ["-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-g", "-std=c++17", "--expt-relaxed-constexpr",
+             "-Xcompiler", "-fPIC,-fsanitize=thread,-fno-omit-frame-pointer"]
+    procs, objs = [], []
+    for src in sources():
+        obj = os.path.join(out, os.path.basename(src) + ".o")
+        objs.append(obj)
+        procs.append((src, subprocess.Popen([nvcc, *flags, "-I", INCLUDE, "-c", src, "-o", obj], stdout=subprocess.PIPE,
+                                            stderr=subprocess.STDOUT, text=True)))
+    for src, p in procs:
+        text, _ = p.communicate()
+        if p.returncode != 0:
+            raise RuntimeError(f"tsan build of {os.path.basename(src)} failed:\n{text}")
+    subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fsanitize=thread", "-o", lib, *objs],
+                   check=True)
+    subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer", "-I", INCLUDE, harness,
+                    "-o", exe, "-L", out, "-ldvc_b200_tsan", f"-Wl,-rpath,{out}", "-lpthread"], check=True)
+    with open(stamp, "w") as f:
+        f.write(h)
+    return exe
+
+
 if __name__ == "__main__":
+    if "--tsan" in sys.argv:
+        exe = build_tsan(force="--force" in sys.argv)
+        sys.exit(subprocess.run([exe], env={**os.environ, "TSAN_OPTIONS": "halt_on_error=0 exitcode=66"}).returncode)
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
