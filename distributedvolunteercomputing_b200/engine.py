@@ -99,6 +99,8 @@ import threading
 # CUDA-graph capture is process-global state: engines on different GPUs driven from different threads
 # must not capture at the same time, and other threads' CUDA calls must not invalidate a capture.
 _CAPTURE_LOCK = threading.Lock()
+# which MobileNet blocks run as ONE fused depthwise + pointwise launch when DVC_FUSE_DWPW is not set ("0": none)
+FUSE_DWPW_DEFAULT = "0"
 
 
 class _ShapeState:
@@ -295,7 +297,11 @@ class NativeEngine:
                                           w.shape[1], w.shape[1], 1, None, 0, 0, C.byref(head), 0), h.tap + "_mbox")
 
         assert body[0].name == "conv0" and body[0].k == 3 and body[0].cout == 32, "first layer must be the 3x3/s2 stem"
-        fuse = os.environ.get("DVC_FUSE_DWPW", "0") == "1"       # experimental fused dw -> pw launches (csrc/dwpw_fused.cu)
+        # fused dw -> pw launches (csrc/dwpw_fused.cu): "0" none, "1" every eligible block, or a comma list of the
+        # pointwise layers' names ("conv3": only that block)
+        fuse_env = os.environ.get("DVC_FUSE_DWPW", FUSE_DWPW_DEFAULT)
+        fuse = fuse_env not in ("", "0")
+        fuse_only = None if fuse_env in ("0", "1", "") else {n.strip() for n in fuse_env.split(",")}
 
         def fusable(dw, pw):
             return (dw.depthwise and dw.stride == 1 and dw.relu and pw.k == 1 and not pw.depthwise and pw.relu
@@ -312,7 +318,7 @@ class NativeEngine:
             while li <= split_idx:
                 c = body[li]
                 nxt = body[li + 1] if li + 1 <= split_idx else None
-                if fuse and nxt is not None and fusable(c, nxt):
+                if fuse and nxt is not None and fusable(c, nxt) and (fuse_only is None or nxt.name in fuse_only):
                     # EXPERIMENTAL (DVC_FUSE_DWPW=1): depthwise + pointwise of one block as a single launch
                     dst = L.ptr(st.fA) + b0 * per_frame[li + 1] * esz if li + 1 == split_idx else L.ptr(other)
                     L.check(lib.dvc_plan_add_dwpw_fused(plan, L.ptr(cur), nb, c.in_hw[0], c.in_hw[1], c.cin, L.ptr(self.w[c.name]),
