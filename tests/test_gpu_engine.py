@@ -118,6 +118,30 @@ def test_sub_batch_invariance(graph):
         assert np.array_equal(o.det, outs[0].det) and np.array_equal(o.frames400, outs[0].frames400)
 
 
+def test_plan_variants_are_bit_identical(graph, monkeypatch):
+    """The plan switches only change HOW the same arithmetic is launched: the extras as implicit GEMMs (im2col-mode TMA
+    loads, the default) or through an explicit patch buffer, and one or all eligible blocks as fused depthwise +
+    pointwise launches.  Detections and annotated frames must be bit-identical in every combination."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    frames = _frames(8, 300, 300, seed=17)
+    outs = {}
+    for name, env in [("default", {}), ("explicit_im2col", {"DVC_IMPLICIT_CONV": "0"}), ("fuse_conv3", {"DVC_FUSE_DWPW": "conv3"}),
+                      ("fuse_all", {"DVC_FUSE_DWPW": "1"})]:
+        for k in ("DVC_IMPLICIT_CONV", "DVC_FUSE_DWPW"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        e = NativeEngine(graph, "cuda:0", Config(use_cuda_graph=False))
+        outs[name] = (e.process(frames).numpy(), e.state(8, 300, 300).n_ops)
+        e.close()
+    ref, n_ref = outs["default"]
+    assert outs["explicit_im2col"][1] == n_ref + 4 and outs["fuse_conv3"][1] == n_ref - 1 and outs["fuse_all"][1] == n_ref - 3
+    for name, (o, _) in outs.items():
+        assert np.array_equal(o.det, ref.det) and np.array_equal(o.det_count, ref.det_count), name
+        assert np.array_equal(o.frames400, ref.frames400), name
+
+
 @pytest.mark.parametrize("B,H,W", [(6, 300, 300), (2, 720, 1280)])
 def test_detections_are_exact_given_the_engine_logits(engines, graph, B, H, W):
     """Strict parity where it can be strict: the detections the engine delivers must equal, row for row, the
