@@ -77,6 +77,9 @@ def run_native(args):
 
     rank, world, local = dist_env()
     assert world == args.gpus or world == 1, f"WORLD_SIZE={world} but --gpus {args.gpus}"
+    if not torch.cuda.is_available():
+        # the product has no CPU fallback on this path: say so instead of dying inside torch's lazy CUDA init
+        sys.exit("bench.py --impl native needs a CUDA device (sm_100a); on a CPU box only `--impl reference` runs")
     torch.cuda.set_device(local)
     dev = f"cuda:{local}"
     multi = world > 1

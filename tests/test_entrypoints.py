@@ -82,3 +82,28 @@ def test_new_clients_against_unmodified_reference_server(tmp_path):
             srv.wait(timeout=10)                               # its fixed ports are free again for the next test
         except Exception:
             pass
+
+
+def test_bench_contract_without_a_gpu():
+    """bench.py on a CPU box: the native arm refuses with one clear line (no CPU fallback posing as a number), the
+    reference arm prints exactly one JSON line with the contract's keys (or the documented `unavailable` line)."""
+    import json
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CPU-box behaviour")
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "0"], cwd=ROOT, env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert p.returncode != 0 and "needs a CUDA device" in p.stderr and p.stdout.strip() == ""
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [ln for ln in p.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference"
+    if "unavailable" not in d:
+        for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                    "vs_baseline", "dtype", "data", "config"):
+            assert key in d, key
+        assert d["value"] > 0 and d["unit"] == "frames/s" and d["config"]["global_batch"] == 64 and d["data"] == "synthetic"
